@@ -1,0 +1,6 @@
+"""B200-native (sm_100a) solver for the two hot paths of gianmarcopicarella/area-diameter-algorithm.
+
+Layout: csrc/ = CUDA kernels + the C ABI (include/adk.h), host/ = C++ mirror of the reference's namespace MT,
+capi.py = ctypes plumbing used by tests/ and bench.py.
+"""
+from .capi import Solver, AdkError, load_library, LIB_PATH, EXPORTS, KMAX_INF  # noqa: F401

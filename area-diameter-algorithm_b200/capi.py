@@ -1,0 +1,256 @@
+"""ctypes binding of the C ABI in include/adk.h (libadk.so).
+
+This is plumbing for tests/ and bench.py; the product boundary is the C ABI itself and the C++ mirror of the
+reference's namespace MT in host/.  There is no CPU fallback: without the built library or without a CUDA device
+every entry point raises.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libadk.so")
+
+ADK_OK, ADK_ERR_CUDA, ADK_ERR_ARG, ADK_ERR_NOMEM = 0, 1, 2, 3
+FLAG_RECONSTRUCT, FLAG_COUNTERS = 1, 2
+KMAX_INF = 2**64 - 1
+
+
+class AdkResult(ctypes.Structure):
+    _fields_ = [
+        ("found", ctypes.c_int32), ("count", ctypes.c_uint32), ("area", ctypes.c_double),
+        ("hull_len", ctypes.c_uint32), ("diam_valid", ctypes.c_uint32), ("diam", ctypes.c_uint32 * 2),
+        ("entries_alloc", ctypes.c_int64), ("entries_required", ctypes.c_int64),
+        ("cells_nominal", ctypes.c_uint64), ("cells_executed", ctypes.c_uint64),
+        ("states", ctypes.c_uint64), ("pairs", ctypes.c_uint64),
+        ("kernel_ms", ctypes.c_double), ("dp_ms", ctypes.c_double),
+    ]
+
+
+class AdkPartial(ctypes.Structure):
+    _fields_ = [
+        ("found", ctypes.c_int32), ("count", ctypes.c_uint32), ("area", ctypes.c_double),
+        ("tie_key", ctypes.c_uint64), ("w0", ctypes.c_uint32), ("w1", ctypes.c_uint32),
+    ]
+
+
+class AdkStats(ctypes.Structure):
+    _fields_ = [
+        ("cells_nominal", ctypes.c_uint64), ("cells_executed", ctypes.c_uint64),
+        ("states", ctypes.c_uint64), ("pairs", ctypes.c_uint64),
+        ("kernel_ms", ctypes.c_double), ("dp_ms", ctypes.c_double),
+        ("launches", ctypes.c_uint64), ("arena_bytes", ctypes.c_uint64),
+    ]
+
+
+EXPORTS = [
+    "adk_create", "adk_destroy", "adk_last_error", "adk_set_memory_budget",
+    "adk_solve_area", "adk_solve_area_diameter",
+    "adk_area_partial", "adk_area_finish", "adk_area_diameter_partial", "adk_area_diameter_finish",
+    "adk_merge", "adk_area_partial_dev", "adk_area_diameter_partial_dev",
+    "adk_count_tables", "adk_points_in_triangle", "adk_cw_order", "adk_slope_order", "adk_lune_lists",
+]
+
+
+class AdkError(RuntimeError):
+    pass
+
+
+def load_library():
+    if not os.path.exists(LIB_PATH):
+        raise AdkError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "(there is no CPU fallback)")
+    return ctypes.CDLL(LIB_PATH)
+
+
+def _darr(v):
+    return (ctypes.c_double * len(v))(*[float(t) for t in v])
+
+
+def _k(kmax):
+    return KMAX_INF if kmax is None or kmax >= KMAX_INF else int(kmax)
+
+
+class Solver:
+    """One context = one GPU.  Mirrors the reference's call shapes; returns plain dicts."""
+
+    def __init__(self, device=-1):
+        self.lib = load_library()
+        L = self.lib
+        L.adk_last_error.restype = ctypes.c_char_p
+        L.adk_last_error.argtypes = [ctypes.c_void_p]
+        L.adk_create.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int]
+        L.adk_destroy.argtypes = [ctypes.c_void_p]
+        L.adk_set_memory_budget.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
+        self.ctx = ctypes.c_void_p()
+        rc = L.adk_create(ctypes.byref(self.ctx), int(device))
+        if rc != ADK_OK:
+            msg = L.adk_last_error(None)
+            raise AdkError(f"adk_create failed ({rc}): {msg.decode() if msg else ''}")
+
+    def close(self):
+        if self.ctx:
+            self.lib.adk_destroy(self.ctx)
+            self.ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != ADK_OK:
+            msg = self.lib.adk_last_error(self.ctx)
+            raise AdkError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def set_memory_budget(self, nbytes):
+        self._check(self.lib.adk_set_memory_budget(self.ctx, ctypes.c_uint64(int(nbytes))), "adk_set_memory_budget")
+
+    @staticmethod
+    def _pack(res, hull):
+        return {
+            "found": int(res.found), "count": int(res.count), "area": float(res.area),
+            "hull": [int(hull[i]) for i in range(res.hull_len)],
+            "diam": [int(res.diam[0]), int(res.diam[1])] if res.diam_valid else None,
+            "entries_alloc": int(res.entries_alloc), "entries_required": int(res.entries_required),
+            "cells_nominal": int(res.cells_nominal), "cells_executed": int(res.cells_executed),
+            "states": int(res.states), "pairs": int(res.pairs),
+            "kernel_ms": float(res.kernel_ms), "dp_ms": float(res.dp_ms),
+        }
+
+    @staticmethod
+    def _part(p):
+        return {"found": int(p.found), "count": int(p.count), "area": float(p.area), "tie_key": int(p.tie_key),
+                "w0": int(p.w0), "w1": int(p.w1)}
+
+    @staticmethod
+    def _unpart(d):
+        return AdkPartial(d["found"], d["count"], d["area"], d["tie_key"], d["w0"], d["w1"])
+
+    @staticmethod
+    def _stats(s):
+        return {k: (float(getattr(s, k)) if k.endswith("_ms") else int(getattr(s, k))) for k, _ in AdkStats._fields_}
+
+    # ---- whole solves -------------------------------------------------------------------------------------------
+    def solve_area(self, x, y, kmax=None, amax=float("inf"), reconstruct=True, counters=False):
+        n = len(x)
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        flags = (FLAG_RECONSTRUCT if reconstruct else 0) | (FLAG_COUNTERS if counters else 0)
+        rc = self.lib.adk_solve_area(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), ctypes.c_uint64(_k(kmax)),
+                                     ctypes.c_double(amax), ctypes.c_uint32(flags), ctypes.byref(res), hull)
+        self._check(rc, "adk_solve_area")
+        return self._pack(res, hull)
+
+    def solve_area_diameter(self, x, y, kmax=None, amax=float("inf"), dmax=float("inf"), reconstruct=True, counters=False):
+        n = len(x)
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        flags = (FLAG_RECONSTRUCT if reconstruct else 0) | (FLAG_COUNTERS if counters else 0)
+        rc = self.lib.adk_solve_area_diameter(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), ctypes.c_uint64(_k(kmax)),
+                                              ctypes.c_double(amax), ctypes.c_double(dmax), ctypes.c_uint32(flags),
+                                              ctypes.byref(res), hull)
+        self._check(rc, "adk_solve_area_diameter")
+        return self._pack(res, hull)
+
+    # ---- sharded solves ------------------------------------------------------------------------------------------
+    def area_partial(self, x, y, kmax, amax, shard, nshards):
+        p, s = AdkPartial(), AdkStats()
+        rc = self.lib.adk_area_partial(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(len(x)), ctypes.c_uint64(_k(kmax)),
+                                       ctypes.c_double(amax), ctypes.c_uint32(shard), ctypes.c_uint32(nshards),
+                                       ctypes.byref(p), ctypes.byref(s))
+        self._check(rc, "adk_area_partial")
+        return self._part(p), self._stats(s)
+
+    def area_diameter_partial(self, x, y, kmax, amax, dmax, shard, nshards):
+        p, s = AdkPartial(), AdkStats()
+        rc = self.lib.adk_area_diameter_partial(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(len(x)),
+                                                ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_double(dmax),
+                                                ctypes.c_uint32(shard), ctypes.c_uint32(nshards), ctypes.byref(p), ctypes.byref(s))
+        self._check(rc, "adk_area_diameter_partial")
+        return self._part(p), self._stats(s)
+
+    def area_partial_dev(self, d_x, d_y, n, kmax, amax, shard=0, nshards=1):
+        p, s = AdkPartial(), AdkStats()
+        rc = self.lib.adk_area_partial_dev(self.ctx, ctypes.c_void_p(d_x), ctypes.c_void_p(d_y), ctypes.c_uint32(n),
+                                           ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_uint32(shard),
+                                           ctypes.c_uint32(nshards), ctypes.byref(p), ctypes.byref(s))
+        self._check(rc, "adk_area_partial_dev")
+        return self._part(p), self._stats(s)
+
+    def area_diameter_partial_dev(self, d_x, d_y, n, kmax, amax, dmax, shard=0, nshards=1):
+        p, s = AdkPartial(), AdkStats()
+        rc = self.lib.adk_area_diameter_partial_dev(self.ctx, ctypes.c_void_p(d_x), ctypes.c_void_p(d_y), ctypes.c_uint32(n),
+                                                    ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_double(dmax),
+                                                    ctypes.c_uint32(shard), ctypes.c_uint32(nshards), ctypes.byref(p),
+                                                    ctypes.byref(s))
+        self._check(rc, "adk_area_diameter_partial_dev")
+        return self._part(p), self._stats(s)
+
+    def merge(self, parts):
+        arr = (AdkPartial * len(parts))(*[self._unpart(p) for p in parts])
+        out = AdkPartial()
+        self._check(self.lib.adk_merge(arr, ctypes.c_uint32(len(parts)), ctypes.byref(out)), "adk_merge")
+        return self._part(out)
+
+    def area_finish(self, x, y, kmax, amax, best, reconstruct=True):
+        n = len(x)
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        b = self._unpart(best)
+        rc = self.lib.adk_area_finish(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), ctypes.c_uint64(_k(kmax)),
+                                      ctypes.c_double(amax), ctypes.byref(b), ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0),
+                                      ctypes.byref(res), hull)
+        self._check(rc, "adk_area_finish")
+        return self._pack(res, hull)
+
+    def area_diameter_finish(self, x, y, kmax, amax, dmax, best, reconstruct=True):
+        n = len(x)
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        b = self._unpart(best)
+        rc = self.lib.adk_area_diameter_finish(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), ctypes.c_uint64(_k(kmax)),
+                                               ctypes.c_double(amax), ctypes.c_double(dmax), ctypes.byref(b),
+                                               ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0), ctypes.byref(res), hull)
+        self._check(rc, "adk_area_diameter_finish")
+        return self._pack(res, hull)
+
+    # ---- precompute stages ---------------------------------------------------------------------------------------
+    def count_tables(self, x, y):
+        n = len(x)
+        below = (ctypes.c_int32 * (n * n))()
+        coll = (ctypes.c_int32 * (n * n))()
+        rb = (ctypes.c_int32 * n)()
+        self._check(self.lib.adk_count_tables(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), below, coll, rb), "adk_count_tables")
+        return list(below), list(coll), list(rb)
+
+    def points_in_triangle(self, x, y, triples):
+        m = len(triples)
+        flat = (ctypes.c_uint32 * (3 * m))(*[v for t in triples for v in t])
+        out = (ctypes.c_int32 * m)()
+        self._check(self.lib.adk_points_in_triangle(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(len(x)), flat,
+                                                    ctypes.c_uint32(m), out), "adk_points_in_triangle")
+        return list(out)
+
+    def cw_order(self, x, y):
+        n = len(x)
+        out = (ctypes.c_int32 * (n * (n - 1)))()
+        self._check(self.lib.adk_cw_order(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), out), "adk_cw_order")
+        return [[out[i * (n - 1) + p] for p in range(n - 1)] for i in range(n)]
+
+    def slope_order(self, x, y, i, j):
+        n = len(x)
+        out = (ctypes.c_int32 * (n + 4))()
+        ln = ctypes.c_uint32()
+        self._check(self.lib.adk_slope_order(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), ctypes.c_uint32(i),
+                                             ctypes.c_uint32(j), out, ctypes.byref(ln)), "adk_slope_order")
+        return [out[t] for t in range(ln.value)]
+
+    def lune_lists(self, x, y, s, t):
+        n = len(x)
+        left = (ctypes.c_int32 * (n + 4))()
+        right = (ctypes.c_int32 * (n + 4))()
+        nl, nr = ctypes.c_uint32(), ctypes.c_uint32()
+        self._check(self.lib.adk_lune_lists(self.ctx, _darr(x), _darr(y), ctypes.c_uint32(n), ctypes.c_uint32(s),
+                                            ctypes.c_uint32(t), left, ctypes.byref(nl), right, ctypes.byref(nr)), "adk_lune_lists")
+        return [left[i] for i in range(nl.value)], [right[i] for i in range(nr.value)]

@@ -1,0 +1,740 @@
+// adk_area.cu — path A: area-bounded largest convex subset (MT::EppsteinAlgorithm*, Eppstein.cpp:128-277) on sm_100a.
+//
+// B200-first reformulation (DESIGN.md "Path A"):
+//   * Everything that does not depend on the level m is hoisted into a per-anchor PREP kernel: slope lists
+//     (rotations of the per-centre direction-mod-pi order), triangle counts c(i,j,l), triangle areas, the
+//     left-of-line mask.  The reference recomputes all of it K-2 times (Eppstein.cpp:199-201,209-214).
+//   * Only "source" cells (left of pi->pj, area <= A) can ever change a row's running minimum, and only
+//     positions right of the line are ever read back, so each row stores its prefix minimum at its sources
+//     only (compact table T[level][row base + k]); the read T[m-c][l][j] becomes one precomputed gather index.
+//   * Levels form a wavefront; one CTA owns an anchor, one warp owns a row, the prefix minimum is a warp
+//     shuffle scan with a carried running value.  Levels live in a ring of (c_max + 1) slots; the sweep over m
+//     stops as soon as no deeper level can be finite.
+#include "adk_internal.h"
+#include "adk_device.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace adk
+{
+
+struct SrcRec { double area; uint32_t gidx; uint16_t c; uint16_t c3; };   // 16 B, one per source cell
+constexpr uint32_t kNoPrev = 0xffffffffu;   // nothing before the read position: level 2 reads 0, deeper levels read +inf
+
+struct AnchorInfo
+{
+    int32_t pt;            // anchor point index
+    int32_t a;             // capacity: |Above(pt)|
+    uint32_t order;        // rank in the reference's anchor order (y ascending)
+    uint32_t rows;         // rows actually present (j loop of Eppstein.cpp:196)
+    uint64_t meta_off;     // first SrcRec / srcl entry of this anchor (row stride = a)
+    uint64_t row_off;      // first rowpt / nsrc / rowbase entry
+    uint64_t t_off;        // first T entry
+    uint32_t U;            // total sources
+    uint32_t cmax;         // largest c over sources
+    uint32_t W;            // ring slots
+    uint32_t best_m;       // 0 = nothing found
+    double best_area;
+    int32_t best_row;
+    uint32_t levels_run;
+    uint64_t list_cells;   // sum of slope-list lengths = reference cells per level
+    uint64_t nonempty_rows;
+};
+
+// --------------------------------------------------------------------------------------------- PREP kernel
+
+constexpr int kPrepThreads = 256;
+
+__global__ void __launch_bounds__(kPrepThreads)
+k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
+            const int32_t* __restrict__ cw, const int32_t* __restrict__ modpi, const uint16_t* __restrict__ rank,
+            AnchorInfo* __restrict__ info, uint32_t first, uint32_t count,
+            SrcRec* __restrict__ recs, uint16_t* __restrict__ srcl, int32_t* __restrict__ rowpt,
+            uint32_t* __restrict__ nsrc, uint32_t* __restrict__ rowbase,
+            uint16_t* __restrict__ qscratch, uint32_t qstride, uint64_t K, double amax)
+{
+    extern __shared__ uint16_t slot_of[];    // n entries: point -> row slot, 0xffff = not above the anchor
+    __shared__ uint32_t s_start, s_rows, s_cmax, s_total;
+    __shared__ unsigned long long s_cells, s_nonempty;
+    __shared__ int32_t s_def[kPrepThreads / 32][32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const uint32_t len = n - 1;
+    uint16_t* Q = qscratch + (size_t) blockIdx.x * qstride;
+
+    for (uint32_t idx = first + blockIdx.x; idx < first + count; idx += gridDim.x)
+    {
+        AnchorInfo& A = info[idx];
+        const int i = A.pt;
+        const uint32_t acap = (uint32_t) A.a;
+        const double ix = x[i], iy = y[i];
+        const int32_t* ring_i = cw + (size_t) i * len;
+        SrcRec* arec = recs + A.meta_off;
+        uint16_t* asrc = srcl + A.meta_off;
+        int32_t* arowpt = rowpt + A.row_off;
+        uint32_t* ansrc = nsrc + A.row_off;
+        uint32_t* abase = rowbase + A.row_off;
+
+        if (threadIdx.x == 0) { s_start = len; s_rows = len; s_cmax = 0; s_total = 0; s_cells = 0; s_nonempty = 0; }
+        for (uint32_t p = threadIdx.x; p < n; p += blockDim.x) slot_of[p] = 0xffff;
+        __syncthreads();
+        // Phase 0a: first clockwise position whose predecessor is below the anchor (Eppstein.cpp:32-42)
+        for (uint32_t t = threadIdx.x; t + 1 < len; t += blockDim.x)
+            if (y[ring_i[t]] < iy && y[ring_i[t + 1]] >= iy) atomicMin(&s_start, t + 1);
+        __syncthreads();
+        const uint32_t start = s_start == len ? 0u : s_start;
+        // Phase 0b: the j loop runs while the clockwise neighbour stays above the anchor (Eppstein.cpp:196)
+        for (uint32_t t = threadIdx.x; t < len; t += blockDim.x)
+            if (y[ring_i[(start + t) % len]] < iy) atomicMin(&s_rows, t);
+        __syncthreads();
+        const uint32_t rows = min(s_rows, acap);
+        for (uint32_t t = threadIdx.x; t < rows; t += blockDim.x)
+        {
+            const int p = ring_i[(start + t) % len];
+            arowpt[t] = p;
+            slot_of[p] = (uint16_t) t;
+        }
+        for (size_t t = threadIdx.x; t < (size_t) rows * rows; t += blockDim.x) Q[t] = 0xffff;
+        __syncthreads();
+
+        // Phase 1: one warp per row.  Walk the centre's direction-mod-pi ring starting just after the anchor.
+        for (uint32_t jj = warp; jj < rows; jj += nwarps)
+        {
+            const int j = arowpt[jj];
+            const double jx = x[j], jy = y[j];
+            const int32_t* ring_j = modpi + (size_t) j * len;
+            const uint32_t r0 = rank[(size_t) j * n + i];
+            const int cij = T.C(i, j);
+            uint32_t ns = 0, kept = 0, ndef = 0;
+            SrcRec* rrec = arec + (size_t) jj * acap;
+            uint16_t* rsrc = asrc + (size_t) jj * acap;
+            for (uint32_t base = 1; base < len; base += 32)
+            {
+                const uint32_t t = base + lane;
+                bool keep = false, src = false, defer = false;
+                int p = -1; uint32_t sl = 0xffff;
+                double area = 0.0; uint32_t cfull = 0, c3 = 0;
+                if (t < len)
+                {
+                    p = ring_j[(r0 + t) % len];
+                    sl = slot_of[p];
+                    if (sl != 0xffff)
+                    {
+                        const double px = x[p], py = y[p];
+                        const double s = signed_area(ix, iy, jx, jy, px, py);
+                        if (near_zero(s)) defer = py > jy;              // Eppstein.cpp:76-82
+                        else
+                        {
+                            keep = true;
+                            if (s > 0.0)
+                            {   // left of pi->pj: a candidate predecessor (Eppstein.cpp:209-214)
+                                area = fabs(s);
+                                const int cnt = cij + T.C(j, p) + points_in_triangle(T, i, ix, iy, j, jx, jy, p, px, py);
+                                cfull = 1u + (uint32_t) cnt;
+                                c3 = cfull + (uint32_t) T.C(p, i);      // the m == 3 extra term (Eppstein.cpp:25-28)
+                                src = area <= amax && (uint64_t) cfull <= K;
+                            }
+                        }
+                    }
+                }
+                const uint32_t km = __ballot_sync(0xffffffffu, keep), sm = __ballot_sync(0xffffffffu, src);
+                const uint32_t dm = __ballot_sync(0xffffffffu, defer);
+                const uint32_t lt = (1u << lane) - 1u;
+                if (keep) Q[(size_t) jj * rows + sl] = (uint16_t) (ns + __popc(sm & lt));
+                if (src)
+                {
+                    const uint32_t k = ns + __popc(sm & lt);
+                    rsrc[k] = (uint16_t) sl;
+                    rrec[k] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) c3};
+                }
+                if (defer)
+                {
+                    const uint32_t d = ndef + __popc(dm & lt);
+                    if (d < 32) s_def[warp][d] = p;
+                }
+                ns += __popc(sm); kept += __popc(km); ndef = min(32u, ndef + __popc(dm));
+            }
+            __syncwarp();
+            if (ndef && lane == 0)
+            {   // points collinear with pi, pj beyond pj close the list, nearer first (Eppstein.cpp:78-81, Utils.cpp:301-306)
+                for (uint32_t u = 1; u < ndef; ++u)
+                {
+                    const int p = s_def[warp][u]; const double dp = dist2(jx, jy, x[p], y[p]);
+                    uint32_t v = u;
+                    while (v > 0 && dist2(jx, jy, x[s_def[warp][v - 1]], y[s_def[warp][v - 1]]) > dp) { s_def[warp][v] = s_def[warp][v - 1]; --v; }
+                    s_def[warp][v] = p;
+                }
+                for (uint32_t u = 0; u < ndef; ++u)
+                {
+                    const int p = s_def[warp][u];
+                    const uint32_t sl = slot_of[p];
+                    Q[(size_t) jj * rows + sl] = (uint16_t) ns;
+                    const double area = fabs(signed_area(ix, iy, jx, jy, x[p], y[p]));
+                    const uint32_t cfull = 1u + (uint32_t) (cij + T.C(j, p));   // PointsInTriangle = 0 for a collinear triple
+                    if (area <= amax && (uint64_t) cfull <= K)
+                    {
+                        rsrc[ns] = (uint16_t) sl;
+                        rrec[ns] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) cfull};
+                        ++ns;
+                    }
+                    ++kept;
+                }
+            }
+            ns = __shfl_sync(0xffffffffu, ns, 0); kept = __shfl_sync(0xffffffffu, kept, 0);
+            if (lane == 0)
+            {
+                ansrc[jj] = ns;
+                atomicAdd(&s_cells, (unsigned long long) kept);
+                if (kept) atomicAdd(&s_nonempty, 1ull);
+            }
+        }
+        __syncthreads();
+        // Phase 2a: exclusive scan of the per-row source counts (one warp, chunked)
+        if (warp == 0)
+        {
+            const uint32_t chunk = (rows + 31) / 32;
+            const uint32_t lo = min(rows, lane * chunk), hi = min(rows, lo + chunk);
+            uint32_t sum = 0;
+            for (uint32_t r = lo; r < hi; ++r) sum += ansrc[r];
+            uint32_t incl = sum;
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((int) lane >= o) incl += v; }
+            uint32_t run = incl - sum;
+            for (uint32_t r = lo; r < hi; ++r) { abase[r] = run; run += ansrc[r]; }
+            if (lane == 31) s_total = incl;
+        }
+        __syncthreads();
+        // Phase 2b: the read T[m-c][l][j] as an index into row l's compact prefix-minimum array
+        uint32_t cm = 0;
+        for (uint32_t jj = warp; jj < rows; jj += nwarps)
+        {
+            const uint32_t ns = ansrc[jj];
+            SrcRec* rrec = arec + (size_t) jj * acap;
+            const uint16_t* rsrc = asrc + (size_t) jj * acap;
+            for (uint32_t k = lane; k < ns; k += 32)
+            {
+                const uint32_t lp = rsrc[k];
+                const uint32_t q = Q[(size_t) lp * rows + jj];
+                rrec[k].gidx = (q == 0xffff || q == 0) ? kNoPrev : abase[lp] + q - 1;
+                cm = max(cm, (uint32_t) rrec[k].c);
+            }
+        }
+        atomicMax(&s_cmax, cm);
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            A.rows = rows; A.U = s_total; A.cmax = s_cmax; A.list_cells = s_cells; A.nonempty_rows = s_nonempty;
+            A.best_m = 0; A.best_area = 0.0; A.best_row = -1; A.levels_run = 0;
+        }
+        __syncthreads();
+    }
+}
+
+// --------------------------------------------------------------------------------------------- DP kernel
+
+constexpr int kDpThreads = 512;
+
+__device__ __forceinline__ double warp_prefix_min(double v, uint32_t lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1)
+    {
+        const double u = __shfl_up_sync(0xffffffffu, v, o);
+        if ((int) lane >= o) v = fmin(v, u);
+    }
+    return v;
+}
+
+// One CTA per anchor (dynamic queue, heaviest anchor first), one warp per row, wavefront over levels.
+__global__ void __launch_bounds__(kDpThreads)
+k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
+          const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc, const uint32_t* __restrict__ rowbase,
+          double* __restrict__ Tbuf, uint64_t K, double amax)
+{
+    __shared__ unsigned long long s_lvl[3];
+    __shared__ unsigned int s_next;
+    __shared__ int s_row;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (;;)
+    {
+        if (threadIdx.x == 0) s_next = atomicAdd(queue, 1u);
+        __syncthreads();
+        const uint32_t q = s_next;
+        if (q >= count) break;
+        AnchorInfo& A = info[first + q];
+        const uint32_t rows = A.rows, U = A.U, W = A.W, acap = (uint32_t) A.a, cmax = A.cmax;
+        const SrcRec* arec = recs + A.meta_off;
+        const uint32_t* ansrc = nsrc + A.row_off;
+        const uint32_t* abase = rowbase + A.row_off;
+        double* T = Tbuf + A.t_off;
+        uint32_t top = 2, levels = 0;
+        double best_area = 0.0;
+        if (threadIdx.x == 0) { s_lvl[0] = s_lvl[1] = s_lvl[2] = kInfBits; s_row = 0x7fffffff; }
+        __syncthreads();
+        if (U > 0)
+        {
+            for (uint64_t m = 3; m <= K; ++m)
+            {
+                if (threadIdx.x == 0) s_lvl[(m + 1) % 3] = kInfBits;
+                double* Tm = T + (size_t) (m % W) * U;
+                for (uint32_t jj = warp; jj < rows; jj += nwarps)
+                {
+                    const uint32_t ns = ansrc[jj];
+                    if (ns == 0) continue;
+                    const SrcRec* rrec = arec + (size_t) jj * acap;
+                    double* out = Tm + abase[jj];
+                    double carry = INFINITY;
+                    for (uint32_t k0 = 0; k0 < ns; k0 += 32)
+                    {
+                        const uint32_t k = k0 + lane;
+                        double val = INFINITY;
+                        if (k < ns)
+                        {
+                            const SrcRec r = rrec[k];
+                            const uint64_t c = m == 3 ? r.c3 : r.c;
+                            if (c + 2 <= m)
+                            {   // Eppstein.cpp:210-216 with T[0], T[1] = +inf and T[2] = 0
+                                const uint64_t lvl = m - c;
+                                double prev;
+                                if (lvl == 2) prev = 0.0;
+                                else prev = r.gidx == kNoPrev ? INFINITY : T[(size_t) (lvl % W) * U + r.gidx];
+                                const double cur = __dadd_rn(prev, r.area);
+                                if (cur <= amax) val = cur;
+                            }
+                        }
+                        val = fmin(warp_prefix_min(val, lane), carry);
+                        if (k < ns) out[k] = val;                                   // Eppstein.cpp:234
+                        carry = __shfl_sync(0xffffffffu, val, 31);
+                    }
+                    if (lane == 0 && carry < INFINITY) atomicMin(&s_lvl[m % 3], area_bits(carry));
+                }
+                __syncthreads();
+                ++levels;
+                const unsigned long long lb = s_lvl[m % 3];
+                if (lb != kInfBits) { top = (uint32_t) m; best_area = bits_area(lb); }
+                if (m >= (uint64_t) top + cmax) break;      // no deeper level can be finite
+            }
+            if (top > 2)
+            {   // first row (in j order) that attains the best area at the best level (Eppstein.cpp:219-224)
+                const double* Tt = T + (size_t) (top % W) * U;
+                for (uint32_t jj = threadIdx.x; jj < rows; jj += blockDim.x)
+                {
+                    const uint32_t ns = ansrc[jj];
+                    if (ns && Tt[abase[jj] + ns - 1] == best_area) atomicMin(&s_row, (int) jj);
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            A.levels_run = levels;
+            if (top > 2) { A.best_m = top; A.best_area = best_area; A.best_row = s_row; }
+        }
+        __syncthreads();
+    }
+}
+
+struct AreaBest { int32_t found; uint32_t m; double area; uint32_t order; int32_t row; int32_t pt; int32_t jpt;
+                  uint64_t cells_nominal, cells_executed; };
+
+// Lexicographic best over anchors: m desc, area asc, reference anchor order asc (Eppstein.cpp:219-224).
+__global__ void k_area_reduce(const AnchorInfo* __restrict__ info, uint32_t count, const int32_t* __restrict__ rowpt,
+                              uint64_t K, AreaBest* __restrict__ out)
+{
+    __shared__ unsigned long long s_cn, s_ce;
+    __shared__ uint32_t s_m; __shared__ unsigned long long s_area; __shared__ uint32_t s_order;
+    if (threadIdx.x == 0) { s_cn = 0; s_ce = 0; s_m = 0; s_area = kInfBits; s_order = 0xffffffffu; }
+    __syncthreads();
+    unsigned long long cn = 0, ce = 0; uint32_t bm = 0;
+    for (uint32_t t = threadIdx.x; t < count; t += blockDim.x)
+    {
+        cn += info[t].list_cells * (K - 2);
+        ce += (unsigned long long) info[t].levels_run * info[t].U;
+        bm = max(bm, info[t].best_m);
+    }
+    atomicAdd(&s_cn, cn); atomicAdd(&s_ce, ce); atomicMax(&s_m, bm);
+    __syncthreads();
+    const uint32_t m = s_m;
+    if (m > 0)
+    {
+        for (uint32_t t = threadIdx.x; t < count; t += blockDim.x)
+            if (info[t].best_m == m) atomicMin(&s_area, area_bits(info[t].best_area));
+        __syncthreads();
+        for (uint32_t t = threadIdx.x; t < count; t += blockDim.x)
+            if (info[t].best_m == m && area_bits(info[t].best_area) == s_area) atomicMin(&s_order, info[t].order);
+        __syncthreads();
+    }
+    for (uint32_t t = threadIdx.x; t < count; t += blockDim.x)
+        if (m > 0 && info[t].best_m == m && area_bits(info[t].best_area) == s_area && info[t].order == s_order)
+        {
+            out->found = 1; out->m = m; out->area = info[t].best_area; out->order = info[t].order;
+            out->row = info[t].best_row; out->pt = info[t].pt; out->jpt = rowpt[info[t].row_off + info[t].best_row];
+        }
+    if (threadIdx.x == 0)
+    {
+        if (m == 0) { out->found = 0; out->m = 0; out->area = 0.0; out->order = 0; out->row = -1; out->pt = -1; out->jpt = -1; }
+        out->cells_nominal = s_cn; out->cells_executed = s_ce;
+    }
+}
+
+// --------------------------------------------------------------------------------------------- reconstruction
+
+// Rotating calipers over the hull cycle (Utils.h:57-109) feeding the farthest-pair search of Utils.cpp:318-338.
+__device__ void hull_diameter_dev(const double* x, const double* y, const int32_t* hull, uint32_t cnt, uint32_t* out)
+{
+    double best = 0.0; uint32_t ba = 0, bb = 0;
+#define ADK_HA(p, q, r) signed_area(x[hull[p]], y[hull[p]], x[hull[q]], y[hull[q]], x[hull[r]], y[hull[r]])
+#define ADK_NX(v) (((v) + 1) % cnt)
+#define ADK_VISIT(p, q) { const double d = dist2(x[hull[p]], y[hull[p]], x[hull[q]], y[hull[q]]); if (d > best) { best = d; ba = (p); bb = (q); } }
+    if (cnt > 2)
+    {
+        uint32_t pi = cnt - 1, qi = 0;
+        while (ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)) > ADK_HA(pi, ADK_NX(pi), qi)) qi = ADK_NX(qi);
+        const uint32_t q0 = qi;
+        while (qi != 0)
+        {
+            pi = ADK_NX(pi);
+            ADK_VISIT(pi, qi)
+            while (ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)) > ADK_HA(pi, ADK_NX(pi), qi))
+            {
+                qi = ADK_NX(qi);
+                if (pi != q0 || qi != 0) ADK_VISIT(pi, qi)
+                else break;
+            }
+            const double diff = __dsub_rn(ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)), ADK_HA(pi, ADK_NX(pi), qi));
+            if (near_zero(diff))
+            {
+                if (pi != q0 || qi != cnt - 1) { const uint32_t qn = ADK_NX(qi); ADK_VISIT(pi, qn) }
+                else break;
+            }
+        }
+    }
+    out[0] = (uint32_t) hull[ba]; out[1] = (uint32_t) hull[bb];
+#undef ADK_HA
+#undef ADK_NX
+#undef ADK_VISIT
+}
+
+struct AreaHull { uint32_t len; uint32_t diam[2]; uint32_t ok; };
+
+// Walk back from (m*, anchor, row*) over the anchor's full table (Eppstein.cpp:240-270).  One thread: <= k steps.
+__global__ void k_area_backtrack(const double* __restrict__ x, const double* __restrict__ y,
+                                 const AnchorInfo* __restrict__ info, const SrcRec* __restrict__ recs,
+                                 const uint16_t* __restrict__ srcl, const int32_t* __restrict__ rowpt,
+                                 const uint32_t* __restrict__ nsrc, const uint32_t* __restrict__ rowbase,
+                                 const double* __restrict__ Tbuf, uint32_t best_m, int32_t best_row,
+                                 int32_t* __restrict__ hull, AreaHull* __restrict__ out)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const AnchorInfo& A = info[0];
+    const uint32_t U = A.U, W = A.W, acap = (uint32_t) A.a;
+    const SrcRec* arec = recs + A.meta_off;
+    const uint16_t* asrc = srcl + A.meta_off;
+    const int32_t* arowpt = rowpt + A.row_off;
+    const uint32_t* ansrc = nsrc + A.row_off;
+    const uint32_t* abase = rowbase + A.row_off;
+    const double* T = Tbuf + A.t_off;
+    uint32_t m = best_m, h = 0, ok = 1;
+    int row = best_row;
+    hull[h++] = A.pt;
+    while (m > 2)
+    {
+        const int last = hull[h - 1], j = arowpt[row];
+        const uint32_t ns = ansrc[row];
+        const double* Tm = T + (size_t) (m % W) * U + abase[row];
+        int pick = -1;
+        for (uint32_t k = ns; k-- > 0;)
+        {
+            const double v = Tm[k], vp = k ? Tm[k - 1] : INFINITY;
+            if (v == vp) continue;                              // the running minimum did not change here
+            const int l = arowpt[asrc[(size_t) row * acap + k]];
+            if (orientation(x[last], y[last], x[j], y[j], x[l], y[l]) >= 0) { pick = (int) k; break; }
+        }
+        if (pick < 0) { ok = 0; break; }
+        const SrcRec r = arec[(size_t) row * acap + pick];
+        m -= m == 3 ? r.c3 : r.c;
+        hull[h++] = j;
+        row = (int) asrc[(size_t) row * acap + pick];
+    }
+    hull[h++] = arowpt[row];
+    out->len = h; out->ok = ok;
+    hull_diameter_dev(x, y, hull, h, out->diam);
+}
+
+// Test hook: the slope list of (anchor i, centre j) exactly as k_area_prep walks it.
+__global__ void k_slope_list(const double* __restrict__ x, const double* __restrict__ y, uint32_t n,
+                             const int32_t* __restrict__ modpi, const uint16_t* __restrict__ rank,
+                             int i, int j, int32_t* __restrict__ out, uint32_t* __restrict__ out_len)
+{
+    __shared__ int32_t s_def[32];
+    const uint32_t lane = threadIdx.x, len = n - 1;
+    const double ix = x[i], iy = y[i], jx = x[j], jy = y[j];
+    const int32_t* ring_j = modpi + (size_t) j * len;
+    const uint32_t r0 = rank[(size_t) j * n + i];
+    uint32_t kept = 0, ndef = 0;
+    for (uint32_t base = 1; base < len; base += 32)
+    {
+        const uint32_t t = base + lane;
+        bool keep = false, defer = false; int p = -1;
+        if (t < len)
+        {
+            p = ring_j[(r0 + t) % len];
+            if (y[p] >= iy)
+            {
+                const double s = signed_area(ix, iy, jx, jy, x[p], y[p]);
+                if (near_zero(s)) defer = y[p] > jy; else keep = true;
+            }
+        }
+        const uint32_t km = __ballot_sync(0xffffffffu, keep), dm = __ballot_sync(0xffffffffu, defer);
+        const uint32_t lt = (1u << lane) - 1u;
+        if (keep) out[kept + __popc(km & lt)] = p;
+        if (defer) { const uint32_t d = ndef + __popc(dm & lt); if (d < 32) s_def[d] = p; }
+        kept += __popc(km); ndef = min(32u, ndef + __popc(dm));
+    }
+    __syncwarp();
+    if (lane == 0)
+    {
+        for (uint32_t u = 1; u < ndef; ++u)
+        {
+            const int p = s_def[u]; const double dp = dist2(jx, jy, x[p], y[p]);
+            uint32_t v = u;
+            while (v > 0 && dist2(jx, jy, x[s_def[v - 1]], y[s_def[v - 1]]) > dp) { s_def[v] = s_def[v - 1]; --v; }
+            s_def[v] = p;
+        }
+        for (uint32_t u = 0; u < ndef; ++u) out[kept++] = s_def[u];
+        *out_len = kept;
+    }
+}
+
+// --------------------------------------------------------------------------------------------- host side
+
+namespace
+{
+struct AreaPlan
+{
+    std::vector<AnchorInfo> info;
+    uint64_t meta_total = 0, row_total = 0;
+    uint32_t amax_rows = 0;
+};
+
+struct SmallOut { unsigned int queue; unsigned int pad; AreaBest best; AreaHull hull; };
+
+int area_fetch_yorder(Ctx* c, std::vector<int32_t>& yorder, std::vector<int32_t>& above)
+{
+    const uint32_t n = c->n;
+    ADK_TRY(run_yorder(c));
+    ADK_TRY(ensure_pinned(c, sizeof(int32_t) * 2 * (size_t) n));
+    int32_t* h = static_cast<int32_t*>(c->h_pinned);
+    ADK_CUDA(c, cudaMemcpyAsync(h, c->yorder.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaMemcpyAsync(h + n, c->above.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    yorder.assign(h, h + n);
+    above.assign(h + n, h + 2 * n);
+    return ADK_OK;
+}
+
+void area_plan_add(AreaPlan& P, int32_t pt, int32_t a, uint32_t order)
+{
+    AnchorInfo A;
+    std::memset(&A, 0, sizeof(A));
+    A.pt = pt; A.a = a; A.order = order;
+    A.meta_off = P.meta_total; A.row_off = P.row_total;
+    P.meta_total += (uint64_t) a * (uint64_t) a;
+    P.row_total += (uint64_t) a;
+    P.amax_rows = std::max<uint32_t>(P.amax_rows, (uint32_t) a);
+    P.info.push_back(A);
+}
+
+// Runs PREP for every anchor in the plan, then the DP in memory-bounded batches.  full_m != 0: keep every
+// level up to full_m (reconstruction); otherwise ring buffers of (c_max + 1) levels.
+int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, float* dp_ms)
+{
+    const uint32_t n = c->n;
+    const uint32_t cnt = (uint32_t) P.info.size();
+    if (dp_ms) *dp_ms = 0.f;
+    if (cnt == 0) return ADK_OK;
+    ADK_TRY(ensure(c, c->scratch0, sizeof(AnchorInfo) * cnt));
+    ADK_TRY(ensure(c, c->scratch1, sizeof(SrcRec) * std::max<uint64_t>(P.meta_total, 1)));
+    ADK_TRY(ensure(c, c->scratch2, sizeof(uint16_t) * std::max<uint64_t>(P.meta_total, 1)));
+    ADK_TRY(ensure(c, c->scratch3, sizeof(int32_t) * 3 * std::max<uint64_t>(P.row_total, 1)));
+    const uint32_t prep_grid = std::min<uint32_t>(cnt, (uint32_t) c->sm_count * 4);
+    const uint32_t qstride = P.amax_rows * P.amax_rows;
+    ADK_TRY(ensure(c, c->scratch4, sizeof(uint16_t) * std::max<uint64_t>((uint64_t) qstride * prep_grid, 1)));
+    ADK_TRY(ensure(c, c->small, sizeof(SmallOut)));
+    AnchorInfo* d_info = c->scratch0.as<AnchorInfo>();
+    SrcRec* d_recs = c->scratch1.as<SrcRec>();
+    uint16_t* d_srcl = c->scratch2.as<uint16_t>();
+    int32_t* d_rowpt = c->scratch3.as<int32_t>();
+    uint32_t* d_nsrc = reinterpret_cast<uint32_t*>(d_rowpt + P.row_total);
+    uint32_t* d_rowbase = d_nsrc + P.row_total;
+    Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), n};
+
+    ADK_CUDA(c, cudaMemcpyAsync(d_info, P.info.data(), sizeof(AnchorInfo) * cnt, cudaMemcpyHostToDevice, c->stream));
+    if (P.amax_rows > 0)
+    {
+        k_area_prep<<<prep_grid, kPrepThreads, sizeof(uint16_t) * n, c->stream>>>(
+            c->x.as<double>(), c->y.as<double>(), n, T, c->cw.as<int32_t>(), c->modpi.as<int32_t>(), c->rank.as<uint16_t>(),
+            d_info, 0, cnt, d_recs, d_srcl, d_rowpt, d_nsrc, d_rowbase, c->scratch4.as<uint16_t>(), qstride, K, amax);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+    }
+    ADK_CUDA(c, cudaMemcpyAsync(P.info.data(), d_info, sizeof(AnchorInfo) * cnt, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+
+    // table plan: ring of (cmax + 1) levels, or every level up to full_m
+    const uint64_t budget_entries = std::max<uint64_t>(c->budget / sizeof(double), 1u << 20);
+    uint32_t b0 = 0;
+    while (b0 < cnt)
+    {
+        uint64_t total = 0;
+        uint32_t b1 = b0;
+        while (b1 < cnt)
+        {
+            AnchorInfo& A = P.info[b1];
+            const uint64_t levels = K >= 3 ? K - 2 : 0;
+            uint64_t W = full_m ? (uint64_t) full_m + 1 : std::min<uint64_t>((uint64_t) A.cmax + 1, std::max<uint64_t>(levels, 1));
+            if (W < 1) W = 1;
+            const uint64_t need = W * (uint64_t) A.U;
+            if (b1 > b0 && total + need > budget_entries) break;
+            if (need > budget_entries) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
+            A.W = (uint32_t) W; A.t_off = total;
+            total += need;
+            ++b1;
+        }
+        ADK_TRY(ensure(c, c->scratch5, sizeof(double) * std::max<uint64_t>(total, 1)));
+        ADK_CUDA(c, cudaMemcpyAsync(d_info + b0, P.info.data() + b0, sizeof(AnchorInfo) * (b1 - b0), cudaMemcpyHostToDevice, c->stream));
+        ADK_CUDA(c, cudaMemsetAsync(c->small.p, 0, sizeof(unsigned int) * 2, c->stream));
+        const uint32_t grid = std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 2);
+        ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
+        k_area_dp<<<grid, kDpThreads, 0, c->stream>>>(d_info, b0, b1 - b0, &c->small.as<SmallOut>()->queue, d_recs, d_nsrc, d_rowbase,
+                                                      c->scratch5.as<double>(), K, amax);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+        ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
+        if (dp_ms || b1 < cnt)
+        {
+            ADK_CUDA(c, cudaEventSynchronize(c->ev3));
+            float ms = 0.f;
+            ADK_CUDA(c, cudaEventElapsedTime(&ms, c->ev2, c->ev3));
+            if (dp_ms) *dp_ms += ms;
+        }
+        b0 = b1;
+    }
+    return ADK_OK;
+}
+}  // namespace
+
+int area_partial(Ctx* c, uint64_t kmax, double amax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* st)
+{
+    std::memset(out, 0, sizeof(*out));
+    if (st) std::memset(st, 0, sizeof(*st));
+    const uint32_t n = c->n;
+    if (nshards == 0 || shard >= nshards) { c->err = "shard out of range"; return ADK_ERR_ARG; }
+    if (n < 3 || kmax < 3) return ADK_OK;            // Eppstein.cpp:137-140
+    const uint64_t K = std::min<uint64_t>(kmax, n);  // Eppstein.cpp:162
+    ADK_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    ADK_TRY(run_angles_and_orders(c, true, true));
+    ADK_TRY(run_count_tables(c));
+    std::vector<int32_t> yorder, above;
+    ADK_TRY(area_fetch_yorder(c, yorder, above));
+    // anchors in the reference's order are also in decreasing-cost order: deal them round-robin to the shards
+    AreaPlan P;
+    for (uint32_t r = shard; r < n; r += nshards)
+    {
+        const int32_t pt = yorder[r];
+        if (above[pt] >= 2) area_plan_add(P, pt, above[pt], r);
+    }
+    float dp_ms = 0.f;
+    ADK_TRY(area_run(c, P, K, amax, 0, &dp_ms));
+    const uint32_t cnt = (uint32_t) P.info.size();
+    AreaBest hb;
+    std::memset(&hb, 0, sizeof(hb));
+    if (cnt)
+    {
+        SmallOut* so = c->small.as<SmallOut>();
+        k_area_reduce<<<1, 256, 0, c->stream>>>(c->scratch0.as<AnchorInfo>(), cnt, c->scratch3.as<int32_t>(), K, &so->best);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+        ADK_CUDA(c, cudaMemcpyAsync(&hb, &so->best, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
+    }
+    ADK_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    ADK_CUDA(c, cudaEventSynchronize(c->ev1));
+    float ms = 0.f;
+    ADK_CUDA(c, cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    if (hb.found)
+    {
+        out->found = 1; out->count = hb.m; out->area = hb.area;
+        out->tie_key = ((uint64_t) hb.order << 32) | (uint32_t) hb.row;
+        out->w0 = (uint32_t) hb.pt; out->w1 = (uint32_t) hb.jpt;
+    }
+    if (st)
+    {
+        st->cells_nominal = hb.cells_nominal; st->cells_executed = hb.cells_executed;
+        st->kernel_ms = ms; st->dp_ms = dp_ms; st->launches = c->launches;
+        st->arena_bytes = c->scratch1.cap + c->scratch2.cap + c->scratch3.cap + c->scratch4.cap + c->scratch5.cap;
+    }
+    return ADK_OK;
+}
+
+int area_finish(Ctx* c, uint64_t kmax, double amax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull)
+{
+    const uint32_t n = c->n;
+    out->found = best->found;
+    if (!best->found) return ADK_OK;
+    out->count = best->count; out->area = best->area;
+    if (!(flags & ADK_FLAG_RECONSTRUCT)) return ADK_OK;
+    const uint64_t K = std::min<uint64_t>(kmax, n);
+    ADK_TRY(run_angles_and_orders(c, true, true));
+    ADK_TRY(run_count_tables(c));
+    std::vector<int32_t> yorder, above;
+    ADK_TRY(area_fetch_yorder(c, yorder, above));
+    if (best->w0 >= n) { c->err = "area_finish: bad witness"; return ADK_ERR_ARG; }
+    AreaPlan P;
+    area_plan_add(P, (int32_t) best->w0, above[best->w0], (uint32_t) (best->tie_key >> 32));
+    // re-run the winning anchor keeping every level up to m*, then walk back (Eppstein.cpp:240-274)
+    ADK_TRY(area_run(c, P, std::min<uint64_t>(K, best->count), amax, best->count, nullptr));
+    ADK_TRY(ensure(c, c->scratch6, sizeof(int32_t) * ((size_t) n + 4)));
+    SmallOut* so = c->small.as<SmallOut>();
+    int32_t* d_rowpt = c->scratch3.as<int32_t>();
+    uint32_t* d_nsrc = reinterpret_cast<uint32_t*>(d_rowpt + P.row_total);
+    uint32_t* d_rowbase = d_nsrc + P.row_total;
+    k_area_backtrack<<<1, 32, 0, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->scratch0.as<AnchorInfo>(),
+                                             c->scratch1.as<SrcRec>(), c->scratch2.as<uint16_t>(), d_rowpt, d_nsrc, d_rowbase,
+                                             c->scratch5.as<double>(), best->count, (int32_t) (best->tie_key & 0xffffffffu),
+                                             c->scratch6.as<int32_t>(), &so->hull);
+    ++c->launches;
+    ADK_CUDA(c, cudaGetLastError());
+    AreaHull hh;
+    ADK_TRY(ensure_pinned(c, sizeof(int32_t) * ((size_t) n + 4)));
+    ADK_CUDA(c, cudaMemcpyAsync(&hh, &so->hull, sizeof(hh), cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaMemcpyAsync(c->h_pinned, c->scratch6.p, sizeof(int32_t) * ((size_t) n + 4), cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!hh.ok) { c->err = "area_finish: reconstruction walked off the table"; return ADK_ERR_ARG; }
+    out->hull_len = hh.len;
+    const int32_t* hp = static_cast<const int32_t*>(c->h_pinned);
+    for (uint32_t t = 0; t < hh.len && t < n; ++t) hull[t] = (uint32_t) hp[t];
+    out->diam_valid = 1; out->diam[0] = hh.diam[0]; out->diam[1] = hh.diam[1];   // Eppstein.cpp:271-273
+    return ADK_OK;
+}
+
+int area_slope_order(Ctx* c, uint32_t i, uint32_t j, int32_t* h_out, uint32_t* h_len)
+{
+    const uint32_t n = c->n;
+    if (n < 3 || i >= n || j >= n || i == j) { c->err = "slope_order: bad indices"; return ADK_ERR_ARG; }
+    ADK_TRY(run_angles_and_orders(c, false, true));
+    ADK_TRY(ensure(c, c->scratch6, sizeof(int32_t) * ((size_t) n + 4)));
+    ADK_TRY(ensure(c, c->small, sizeof(SmallOut)));
+    k_slope_list<<<1, 32, 0, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->modpi.as<int32_t>(), c->rank.as<uint16_t>(),
+                                          (int) i, (int) j, c->scratch6.as<int32_t>(), &c->small.as<SmallOut>()->queue);
+    ++c->launches;
+    ADK_CUDA(c, cudaGetLastError());
+    unsigned int len = 0;
+    ADK_CUDA(c, cudaMemcpyAsync(&len, &c->small.as<SmallOut>()->queue, sizeof(len), cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    ADK_CUDA(c, cudaMemcpyAsync(h_out, c->scratch6.p, sizeof(int32_t) * len, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    *h_len = len;
+    return ADK_OK;
+}
+
+}  // namespace adk

@@ -1,0 +1,295 @@
+// adk_capi.cu — the C ABI (include/adk.h): context management and the thin entry points over the kernels.
+#include "adk_internal.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+namespace adk
+{
+
+int set_cuda_error(Ctx* c, cudaError_t e, const char* what)
+{
+    if (c)
+    {
+        c->err = std::string("CUDA error: ") + cudaGetErrorString(e) + " at " + what;
+    }
+    return ADK_ERR_CUDA;
+}
+
+int ensure(Ctx* c, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return ADK_OK;
+    if (b.p) { cudaError_t e = cudaFree(b.p); b.p = nullptr; b.cap = 0; if (e != cudaSuccess) return set_cuda_error(c, e, "cudaFree"); }
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess)
+    {
+        cudaGetLastError();
+        want = bytes;
+        e = cudaMalloc(&b.p, want);
+        if (e != cudaSuccess) { b.p = nullptr; cudaGetLastError(); c->err = "device allocation failed"; return ADK_ERR_NOMEM; }
+    }
+    b.cap = want;
+    return ADK_OK;
+}
+
+int ensure_pinned(Ctx* c, size_t bytes)
+{
+    if (bytes <= c->h_pinned_cap) return ADK_OK;
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    c->h_pinned = nullptr; c->h_pinned_cap = 0;
+    const size_t want = std::max<size_t>(bytes * 2, 1 << 16);
+    ADK_CUDA(c, cudaMallocHost(&c->h_pinned, want));
+    c->h_pinned_cap = want;
+    return ADK_OK;
+}
+
+static void free_buf(DevBuf& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+
+}  // namespace adk
+
+using adk::Ctx;
+
+struct adk_ctx { Ctx c; };
+
+static thread_local std::string g_create_error;
+
+extern "C" {
+
+int adk_create(adk_ctx** out_ctx, int device)
+{
+    if (!out_ctx) return ADK_ERR_ARG;
+    *out_ctx = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+    {
+        g_create_error = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        cudaGetLastError();
+        return ADK_ERR_CUDA;   // there is no CPU fallback
+    }
+    if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) return ADK_ERR_CUDA; }
+    if (device >= ndev) return ADK_ERR_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return ADK_ERR_CUDA;
+    adk_ctx* h = new (std::nothrow) adk_ctx();
+    if (!h) return ADK_ERR_NOMEM;
+    Ctx* c = &h->c;
+    c->device = device;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return ADK_ERR_CUDA; }
+    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1); cudaEventCreate(&c->ev2); cudaEventCreate(&c->ev3);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->budget = (uint64_t) (free_b * 0.6);
+    else c->budget = 8ull << 30;
+    *out_ctx = h;
+    return ADK_OK;
+}
+
+void adk_destroy(adk_ctx* h)
+{
+    if (!h) return;
+    Ctx* c = &h->c;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
+                           &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
+                           &c->scratch6, &c->arena, &c->small};
+    for (adk::DevBuf* b : bufs) adk::free_buf(*b);
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->ev2) cudaEventDestroy(c->ev2);
+    if (c->ev3) cudaEventDestroy(c->ev3);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete h;
+}
+
+const char* adk_last_error(const adk_ctx* h) { return h ? h->c.err.c_str() : g_create_error.c_str(); }
+
+int adk_set_memory_budget(adk_ctx* h, uint64_t bytes)
+{
+    if (!h || bytes < (1ull << 20)) return ADK_ERR_ARG;
+    h->c.budget = bytes;
+    return ADK_OK;
+}
+
+#define ADK_ENTER(h) if (!(h)) return ADK_ERR_ARG; Ctx* c = &(h)->c; c->err.clear(); c->launches = 0; \
+    if (cudaSetDevice(c->device) != cudaSuccess) return ADK_ERR_CUDA
+
+static void fill_result_from(adk_result* out, const adk_stats& st, uint32_t flags)
+{
+    out->cells_nominal = st.cells_nominal; out->cells_executed = st.cells_executed;
+    out->states = st.states; out->pairs = st.pairs; out->kernel_ms = st.kernel_ms; out->dp_ms = st.dp_ms;
+    out->entries_alloc = -1; out->entries_required = -1;
+    (void) flags;
+}
+
+int adk_area_partial(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                     uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats)
+{
+    ADK_ENTER(h);
+    if (!out) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::area_partial(c, kmax, amax, shard, nshards, out, stats);
+}
+
+int adk_area_partial_dev(adk_ctx* h, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                         uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats)
+{
+    ADK_ENTER(h);
+    if (!out) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
+    return adk::area_partial(c, kmax, amax, shard, nshards, out, stats);
+}
+
+int adk_area_finish(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                    const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull)
+{
+    ADK_ENTER(h);
+    if (!out || !best || ((flags & ADK_FLAG_RECONSTRUCT) && !hull)) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    out->entries_alloc = -1; out->entries_required = -1;
+    if (!best->found) return ADK_OK;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::area_finish(c, kmax, amax, best, flags, out, hull);
+}
+
+int adk_solve_area(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, uint32_t flags,
+                   adk_result* out, uint32_t* hull)
+{
+    ADK_ENTER(h);
+    if (!out || ((flags & ADK_FLAG_RECONSTRUCT) && !hull)) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    out->entries_alloc = -1; out->entries_required = -1;
+    if (n < 3 || kmax < 3) return ADK_OK;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    adk_partial part; adk_stats st;
+    ADK_TRY(adk::area_partial(c, kmax, amax, 0, 1, &part, &st));
+    const uint64_t launches = c->launches;
+    ADK_TRY(adk::area_finish(c, kmax, amax, &part, flags, out, hull));
+    (void) launches;
+    fill_result_from(out, st, flags);
+    if (flags & ADK_FLAG_COUNTERS)
+    {   // Eppstein.cpp:171-175: the reference's dense table size; "required" is reported by the DP kernels
+        const uint64_t K = std::min<uint64_t>(kmax, n);
+        out->entries_alloc = (int64_t) ((K + 1) * 2 * (uint64_t) n * n);
+    }
+    return ADK_OK;
+}
+
+int adk_area_diameter_partial(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                              double dmax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats)
+{
+    ADK_ENTER(h);
+    if (!out) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::ad_partial(c, kmax, amax, dmax, shard, nshards, out, stats);
+}
+
+int adk_area_diameter_partial_dev(adk_ctx* h, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                                  double dmax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats)
+{
+    ADK_ENTER(h);
+    if (!out) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
+    return adk::ad_partial(c, kmax, amax, dmax, shard, nshards, out, stats);
+}
+
+int adk_area_diameter_finish(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                             double dmax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull)
+{
+    ADK_ENTER(h);
+    if (!out || !best || ((flags & ADK_FLAG_RECONSTRUCT) && !hull)) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    out->entries_alloc = -1; out->entries_required = -1;
+    if (!best->found) return ADK_OK;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
+}
+
+int adk_solve_area_diameter(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                            double dmax, uint32_t flags, adk_result* out, uint32_t* hull)
+{
+    ADK_ENTER(h);
+    if (!out || ((flags & ADK_FLAG_RECONSTRUCT) && !hull)) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    out->entries_alloc = -1; out->entries_required = -1;
+    if (std::min<uint64_t>(n, kmax) < 3) return ADK_OK;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    adk_partial part; adk_stats st;
+    ADK_TRY(adk::ad_partial(c, kmax, amax, dmax, 0, 1, &part, &st));
+    ADK_TRY(adk::ad_finish(c, kmax, amax, dmax, &part, flags, out, hull));
+    fill_result_from(out, st, flags);
+    if (flags & ADK_FLAG_COUNTERS) { out->entries_alloc = (int64_t) st.states; out->entries_required = (int64_t) st.states; }
+    return ADK_OK;
+}
+
+int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out)
+{
+    if (!parts || !out) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    for (uint32_t i = 0; i < count; ++i)
+    {
+        const adk_partial& p = parts[i];
+        if (!p.found) continue;
+        const bool better = !out->found || p.count > out->count ||
+                            (p.count == out->count && (p.area < out->area || (p.area == out->area && p.tie_key < out->tie_key)));
+        if (better) *out = p;
+    }
+    return ADK_OK;
+}
+
+int adk_count_tables(adk_ctx* h, const double* x, const double* y, uint32_t n, int32_t* below, int32_t* coll, int32_t* right_below)
+{
+    ADK_ENTER(h);
+    if (!below || !coll || !right_below) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::run_count_tables(c));
+    ADK_CUDA(c, cudaMemcpyAsync(below, c->below.p, sizeof(int32_t) * (size_t) n * n, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaMemcpyAsync(coll, c->coll.p, sizeof(int32_t) * (size_t) n * n, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaMemcpyAsync(right_below, c->rb.p, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ADK_OK;
+}
+
+int adk_points_in_triangle(adk_ctx* h, const double* x, const double* y, uint32_t n, const uint32_t* triples, uint32_t m, int32_t* out)
+{
+    ADK_ENTER(h);
+    if (!triples || !out) return ADK_ERR_ARG;
+    for (uint32_t t = 0; t < 3 * m; ++t) if (triples[t] >= n) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::run_pit_query(c, triples, m, out);
+}
+
+int adk_cw_order(adk_ctx* h, const double* x, const double* y, uint32_t n, int32_t* order)
+{
+    ADK_ENTER(h);
+    if (!order || n < 2) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::run_angles_and_orders(c, true, false));
+    ADK_CUDA(c, cudaMemcpyAsync(order, c->cw.p, sizeof(int32_t) * (size_t) n * (n - 1), cudaMemcpyDeviceToHost, c->stream));
+    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ADK_OK;
+}
+
+int adk_slope_order(adk_ctx* h, const double* x, const double* y, uint32_t n, uint32_t i, uint32_t j, int32_t* out, uint32_t* len)
+{
+    ADK_ENTER(h);
+    if (!out || !len) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::area_slope_order(c, i, j, out, len);
+}
+
+int adk_lune_lists(adk_ctx* h, const double* x, const double* y, uint32_t n, uint32_t s, uint32_t t,
+                   int32_t* left, uint32_t* nleft, int32_t* right, uint32_t* nright)
+{
+    ADK_ENTER(h);
+    if (!left || !right || !nleft || !nright || s >= n || t >= n || s == t) return ADK_ERR_ARG;
+    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::ad_lune_lists(c, s, t, left, nleft, right, nright);
+}
+
+}  // extern "C"

@@ -1,0 +1,77 @@
+// adk_internal.h — host-side context and launcher declarations shared by the .cu files.  Not installed.
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+
+#include "../../include/adk.h"
+
+namespace adk
+{
+// A grow-only device buffer.
+struct DevBuf
+{
+    void* p = nullptr;
+    size_t cap = 0;
+    template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct Ctx
+{
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+    std::string err;
+    uint64_t budget = 0;           // DP workspace cap in bytes
+    uint64_t launches = 0;         // kernels launched by the current call
+
+    // point set currently resident
+    uint32_t n = 0;
+    DevBuf x, y;
+    // precompute products
+    DevBuf ang, d2c;               // n*n double: angle / squared distance of p seen from centre c
+    DevBuf cw;                     // n*(n-1) int32: clockwise neighbour lists
+    DevBuf modpi;                  // n*(n-1) int32: neighbours by direction mod pi (descending), ties nearer first
+    DevBuf rank;                   // n*n uint16: rank[c*n+p] = position of p in modpi[c]
+    DevBuf below, coll, rb;        // count tables (int32)
+    DevBuf yorder, above;          // n int32: points by ascending y; above[i] = #points with y >= y_i (excluding i)
+    bool have_cw = false, have_modpi = false, have_tables = false, have_yorder = false;
+
+    // scratch / arenas
+    DevBuf scratch0, scratch1, scratch2, scratch3, scratch4, scratch5, scratch6;
+    DevBuf arena;                  // AD dense layer tables (kept clean between calls)
+    uint64_t ad_V = 0, ad_Q = 0;   // per-slice capacities the arena was initialised for (grow-only)
+    uint32_t ad_L = 0, ad_slices = 0;
+    size_t ad_slice_bytes = 0;
+    DevBuf small;                  // small result records
+    void* h_pinned = nullptr;      // pinned host staging
+    size_t h_pinned_cap = 0;
+};
+
+int set_cuda_error(Ctx* c, cudaError_t e, const char* what);
+int ensure(Ctx* c, DevBuf& b, size_t bytes);
+int ensure_pinned(Ctx* c, size_t bytes);
+#define ADK_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return adk::set_cuda_error((ctx), e__, #call); } while (0)
+#define ADK_TRY(call) do { int r__ = (call); if (r__ != ADK_OK) return r__; } while (0)
+
+// ---- precompute (adk_precompute.cu) ----
+int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool device_ptrs);
+int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi);
+int run_count_tables(Ctx* c);
+int run_yorder(Ctx* c);
+int run_pit_query(Ctx* c, const uint32_t* h_triples, uint32_t m, int32_t* h_out);
+
+// ---- area path (adk_area.cu) ----
+int area_partial(Ctx* c, uint64_t kmax, double amax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* st);
+int area_finish(Ctx* c, uint64_t kmax, double amax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
+int area_slope_order(Ctx* c, uint32_t i, uint32_t j, int32_t* h_out, uint32_t* h_len);
+
+// ---- area+diameter path (adk_ad.cu) ----
+int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* st);
+int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
+int ad_lune_lists(Ctx* c, uint32_t s, uint32_t t, int32_t* h_left, uint32_t* nl, int32_t* h_right, uint32_t* nr);
+
+}  // namespace adk

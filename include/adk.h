@@ -1,0 +1,134 @@
+/* adk.h — C ABI of the B200-native (sm_100a) area / area+diameter bounded largest-convex-subset solver.
+ *
+ * This is the drop-in boundary for the two hot paths of gianmarcopicarella/area-diameter-algorithm.
+ * Everything above it (the C++ mirror of namespace MT in area-diameter-algorithm_b200/host/, the reference's own
+ * src/bench, src/test, src/main, src/py-binding) stays host code; everything below it is hand-written CUDA.
+ * Plain pointers and sizes only: no C++ types, no torch types, no ownership transfer.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo):
+ *   adk_solve_area            <- MT::EppsteinAlgorithmWithBenchmarkInfo           src/common/Eppstein.h:17-23,  Eppstein.cpp:128-277
+ *   adk_solve_area_diameter   <- MT::AntipodalOptimizedAlgorithmWithBenchmarkInfo  src/common/AntipodalOptimized.h:18-25, AntipodalOptimized.cpp:452-545
+ *                                MT::AntipodalAlgorithmWithBenchmarkInfo           src/common/Antipodal.h:18-25 (served by the same kernels)
+ *   adk_*_partial / adk_merge / adk_*_finish : the same two solves split into "my shard of anchors / candidate pairs",
+ *                                a host-side lexicographic merge and the witness reconstruction, for one-process-per-GPU sharding.
+ *   adk_count_tables          <- MT::CountPointsBelowAllSegments                  src/common/Utils.h:41-43,   Utils.cpp:74-143
+ *   adk_points_in_triangle    <- MT::PointsInTriangle                             src/common/Utils.h:45-49,   Utils.cpp:251-293
+ *   adk_cw_order              <- MT::SortPointsClockWiseAroundPoint               src/common/Utils.h:53,      Utils.cpp:311-316
+ *
+ * There is NO CPU fallback behind these entry points: without a CUDA device adk_create fails with ADK_ERR_CUDA.
+ */
+#ifndef ADK_H
+#define ADK_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ADK_VERSION 1
+
+/* status codes */
+#define ADK_OK 0
+#define ADK_ERR_CUDA 1        /* a CUDA runtime call failed; adk_last_error() has the text */
+#define ADK_ERR_ARG 2         /* bad argument (NULL, n too large, shard out of range, ...) */
+#define ADK_ERR_NOMEM 3       /* the instance needs more device memory than the budget allows */
+
+/* flags */
+#define ADK_FLAG_RECONSTRUCT 1u   /* fill hull[] (and, for the area path, the hull's diameter pair) */
+#define ADK_FLAG_COUNTERS 2u      /* fill the BenchmarkInfo-style counters */
+
+#define ADK_KMAX_INF UINT64_MAX   /* aMaxPointsCount = (size_t) -1 */
+#define ADK_MAX_POINTS 4096u
+
+typedef struct adk_ctx adk_ctx;
+
+/* One solve's answer: mirrors MT::ConvexArea (Utils.h:20-26) + MT::BenchmarkInfo (Utils.h:35-39). */
+typedef struct adk_result
+{
+    int32_t found;              /* 0 = std::nullopt */
+    uint32_t count;             /* myPointsCount */
+    double area;                /* myHullArea */
+    uint32_t hull_len;          /* number of entries written to hull[] (0 unless ADK_FLAG_RECONSTRUCT) */
+    uint32_t diam_valid;        /* myDiameterOpt.has_value() */
+    uint32_t diam[2];           /* myFirstIndex, mySecondIndex */
+    int64_t entries_alloc;      /* myAllocatedEntriesCount (-1 when not requested) */
+    int64_t entries_required;   /* myRequiredEntriesCount  (-1 when not requested) */
+    uint64_t cells_nominal;     /* DP cell updates the reference executes for this call */
+    uint64_t cells_executed;    /* DP cell updates the kernels executed */
+    uint64_t states;            /* area+diameter path: DP states created (reference "entries") */
+    uint64_t pairs;             /* area+diameter path: candidate pairs within the diameter bound */
+    double kernel_ms;           /* device time of the whole call (CUDA events on the solver's stream) */
+    double dp_ms;               /* device time of the dominant DP kernel alone */
+} adk_result;
+
+/* A rank's local best: what is exchanged between GPUs (32 bytes). */
+typedef struct adk_partial
+{
+    int32_t found;
+    uint32_t count;
+    double area;
+    uint64_t tie_key;           /* iteration-order key: smaller = met earlier by the reference */
+    uint32_t w0, w1;            /* witness: area path (anchor, last vertex); area+diameter path (s, t) */
+} adk_partial;
+
+/* Run statistics of a partial solve (all device-side counts). */
+typedef struct adk_stats
+{
+    uint64_t cells_nominal, cells_executed, states, pairs;
+    double kernel_ms, dp_ms;
+    uint64_t launches;          /* kernels launched by the call */
+    uint64_t arena_bytes;       /* device workspace in use */
+} adk_stats;
+
+/* ---- context ------------------------------------------------------------------------------------------------ */
+int adk_create(adk_ctx** out_ctx, int device);        /* device = CUDA ordinal; -1 = current device */
+void adk_destroy(adk_ctx* ctx);
+const char* adk_last_error(const adk_ctx* ctx);       /* text of the last failure on this context */
+int adk_set_memory_budget(adk_ctx* ctx, uint64_t bytes);   /* cap for DP workspaces (default: 60 % of free memory) */
+
+/* ---- whole solves (host buffers in, host buffers out; H2D/D2H inside) ------------------------------------------ */
+int adk_solve_area(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
+                   uint64_t kmax, double amax, uint32_t flags, adk_result* out, uint32_t* hull /* capacity n */);
+
+int adk_solve_area_diameter(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
+                            uint64_t kmax, double amax, double dmax, uint32_t flags, adk_result* out, uint32_t* hull);
+
+/* ---- sharded solves: shard `shard` of `nshards` takes every nshards-th unit of the cost-ordered work list ------- */
+int adk_area_partial(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                     uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats);
+int adk_area_finish(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                    const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
+
+int adk_area_diameter_partial(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                              double dmax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats);
+int adk_area_diameter_finish(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                             double dmax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
+
+/* Lexicographic best of `count` partials: count desc, area asc, tie_key asc (host side, no device work). */
+int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out);
+
+/* ---- device-resident variants (pointers are DEVICE pointers; used by bench.py's kernel-only timing) ------------ */
+int adk_area_partial_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                         uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats);
+int adk_area_diameter_partial_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax,
+                                  double amax, double dmax, uint32_t shard, uint32_t nshards, adk_partial* out,
+                                  adk_stats* stats);
+
+/* ---- precompute stages, exposed for parity tests ---------------------------------------------------------------- */
+int adk_count_tables(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
+                     int32_t* below /* n*n */, int32_t* coll /* n*n */, int32_t* right_below /* n */);
+int adk_points_in_triangle(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
+                           const uint32_t* triples /* 3*m */, uint32_t m, int32_t* out /* m */);
+int adk_cw_order(adk_ctx* ctx, const double* x, const double* y, uint32_t n, int32_t* order /* n*(n-1) */);
+/* slope order around centre j for anchor i (Eppstein.cpp:62-114); out capacity n; *len receives the length */
+int adk_slope_order(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint32_t i, uint32_t j,
+                    int32_t* out, uint32_t* len);
+/* lune lists of the candidate pair (s,t) (AntipodalOptimized.cpp:39-109); capacities n+2 */
+int adk_lune_lists(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint32_t s, uint32_t t,
+                   int32_t* left, uint32_t* nleft, int32_t* right, uint32_t* nright);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
