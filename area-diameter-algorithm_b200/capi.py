@@ -43,7 +43,8 @@ class AdkStats(ctypes.Structure):
 
 
 EXPORTS = [
-    "adk_create", "adk_destroy", "adk_last_error", "adk_set_memory_budget",
+    "adk_create", "adk_destroy", "adk_last_error", "adk_set_memory_budget", "adk_set_stream", "adk_launch_count",
+    "adk_area_finish_dev", "adk_area_diameter_finish_dev",
     "adk_solve_area", "adk_solve_area_diameter",
     "adk_area_partial", "adk_area_finish", "adk_area_diameter_partial", "adk_area_diameter_finish",
     "adk_merge", "adk_area_partial_dev", "adk_area_diameter_partial_dev",
@@ -102,6 +103,16 @@ class Solver:
         if rc != ADK_OK:
             msg = self.lib.adk_last_error(self.ctx)
             raise AdkError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def set_stream(self, cuda_stream):
+        """Run on the caller's stream (an integer cudaStream_t handle, 0 = legacy default stream)."""
+        self.lib.adk_set_stream.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        self._check(self.lib.adk_set_stream(self.ctx, ctypes.c_void_p(int(cuda_stream))), "adk_set_stream")
+
+    def launch_count(self):
+        self.lib.adk_launch_count.restype = ctypes.c_uint64
+        self.lib.adk_launch_count.argtypes = [ctypes.c_void_p]
+        return int(self.lib.adk_launch_count(self.ctx))
 
     def set_memory_budget(self, nbytes):
         self._check(self.lib.adk_set_memory_budget(self.ctx, ctypes.c_uint64(int(nbytes))), "adk_set_memory_budget")
@@ -213,6 +224,27 @@ class Solver:
                                                ctypes.c_double(amax), ctypes.c_double(dmax), ctypes.byref(b),
                                                ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0), ctypes.byref(res), hull)
         self._check(rc, "adk_area_diameter_finish")
+        return self._pack(res, hull)
+
+    def area_diameter_finish_dev(self, d_x, d_y, n, kmax, amax, dmax, best, reconstruct=True):
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        b = self._unpart(best)
+        rc = self.lib.adk_area_diameter_finish_dev(self.ctx, ctypes.c_void_p(d_x), ctypes.c_void_p(d_y), ctypes.c_uint32(n),
+                                                   ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_double(dmax),
+                                                   ctypes.byref(b), ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0),
+                                                   ctypes.byref(res), hull)
+        self._check(rc, "adk_area_diameter_finish_dev")
+        return self._pack(res, hull)
+
+    def area_finish_dev(self, d_x, d_y, n, kmax, amax, best, reconstruct=True):
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        b = self._unpart(best)
+        rc = self.lib.adk_area_finish_dev(self.ctx, ctypes.c_void_p(d_x), ctypes.c_void_p(d_y), ctypes.c_uint32(n),
+                                          ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.byref(b),
+                                          ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0), ctypes.byref(res), hull)
+        self._check(rc, "adk_area_finish_dev")
         return self._pack(res, hull)
 
     # ---- precompute stages ---------------------------------------------------------------------------------------

@@ -103,7 +103,7 @@ void adk_destroy(adk_ctx* h)
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->ev2) cudaEventDestroy(c->ev2);
     if (c->ev3) cudaEventDestroy(c->ev3);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->stream && c->own_stream) cudaStreamDestroy(c->stream);
     delete h;
 }
 
@@ -116,7 +116,21 @@ int adk_set_memory_budget(adk_ctx* h, uint64_t bytes)
     return ADK_OK;
 }
 
-#define ADK_ENTER(h) if (!(h)) return ADK_ERR_ARG; Ctx* c = &(h)->c; c->err.clear(); c->launches = 0; \
+int adk_set_stream(adk_ctx* h, void* cuda_stream)
+{
+    if (!h) return ADK_ERR_ARG;
+    Ctx* c = &h->c;
+    if (cudaSetDevice(c->device) != cudaSuccess) return ADK_ERR_CUDA;
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->stream && c->own_stream) cudaStreamDestroy(c->stream);
+    c->stream = static_cast<cudaStream_t>(cuda_stream);
+    c->own_stream = false;
+    return ADK_OK;
+}
+
+uint64_t adk_launch_count(const adk_ctx* h) { return h ? h->c.total_launches + h->c.launches : 0; }
+
+#define ADK_ENTER(h) if (!(h)) return ADK_ERR_ARG; Ctx* c = &(h)->c; c->err.clear(); c->total_launches += c->launches; c->launches = 0; \
     if (cudaSetDevice(c->device) != cudaSuccess) return ADK_ERR_CUDA
 
 static void fill_result_from(adk_result* out, const adk_stats& st, uint32_t flags)
@@ -154,6 +168,18 @@ int adk_area_finish(adk_ctx* h, const double* x, const double* y, uint32_t n, ui
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
     ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::area_finish(c, kmax, amax, best, flags, out, hull);
+}
+
+int adk_area_finish_dev(adk_ctx* h, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                        const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull)
+{
+    ADK_ENTER(h);
+    if (!out || !best || ((flags & ADK_FLAG_RECONSTRUCT) && !hull)) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    out->entries_alloc = -1; out->entries_required = -1;
+    if (!best->found) return ADK_OK;
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
     return adk::area_finish(c, kmax, amax, best, flags, out, hull);
 }
 
@@ -207,6 +233,18 @@ int adk_area_diameter_finish(adk_ctx* h, const double* x, const double* y, uint3
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
     ADK_TRY(adk::upload_points(c, x, y, n, false));
+    return adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
+}
+
+int adk_area_diameter_finish_dev(adk_ctx* h, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                                 double dmax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull)
+{
+    ADK_ENTER(h);
+    if (!out || !best || ((flags & ADK_FLAG_RECONSTRUCT) && !hull)) return ADK_ERR_ARG;
+    std::memset(out, 0, sizeof(*out));
+    out->entries_alloc = -1; out->entries_required = -1;
+    if (!best->found) return ADK_OK;
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
     return adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
 }
 

@@ -27,6 +27,8 @@ struct Ctx
     std::string err;
     uint64_t budget = 0;           // DP workspace cap in bytes
     uint64_t launches = 0;         // kernels launched by the current call
+    uint64_t total_launches = 0;   // ... by all earlier calls
+    bool own_stream = true;
 
     // point set currently resident
     uint32_t n = 0;

@@ -1,0 +1,57 @@
+"""Multi-GPU plumbing: one process per GPU, shards of anchors / candidate pairs, one tiny all-gather at the end.
+
+The data path has no collective: every rank solves its own shard (adk_*_partial).  The single exchange is the
+32-byte (count, area, tie key, witness) record per rank, gathered with torch.distributed (NCCL over NVLink on GPUs,
+gloo in the CPU tests) and merged lexicographically by adk_merge on every rank.
+"""
+import struct
+
+import torch
+import torch.distributed as dist
+
+_FMT = "<iIdQII"     # adk_partial: found, count, area, tie_key, w0, w1  (32 bytes)
+RECORD_BYTES = struct.calcsize(_FMT)
+
+
+def pack_partial(p):
+    return struct.pack(_FMT, p["found"], p["count"], p["area"], p["tie_key"], p["w0"], p["w1"])
+
+
+def unpack_partial(b):
+    f, c, a, k, w0, w1 = struct.unpack(_FMT, bytes(b))
+    return {"found": f, "count": c, "area": a, "tie_key": k, "w0": w0, "w1": w1}
+
+
+def merge_partials(parts):
+    """Host-side lexicographic best: count desc, area asc, tie_key asc (same rule as adk_merge)."""
+    best = None
+    for p in parts:
+        if not p["found"]:
+            continue
+        if best is None or p["count"] > best["count"] or (p["count"] == best["count"] and (
+                p["area"] < best["area"] or (p["area"] == best["area"] and p["tie_key"] < best["tie_key"]))):
+            best = p
+    return best if best is not None else {"found": 0, "count": 0, "area": 0.0, "tie_key": 0, "w0": 0, "w1": 0}
+
+
+def gather_partials(partial, device=None, group=None):
+    """All-gather of one 32-byte record per rank; returns the list of every rank's partial."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return [partial]
+    world = dist.get_world_size(group)
+    dev = device if device is not None else torch.device("cpu")
+    mine = torch.frombuffer(bytearray(pack_partial(partial)), dtype=torch.uint8).to(dev)
+    out = torch.empty(world * RECORD_BYTES, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(out, mine, group=group)
+    raw = out.cpu().numpy().tobytes()
+    return [unpack_partial(raw[r * RECORD_BYTES:(r + 1) * RECORD_BYTES]) for r in range(world)]
+
+
+def gather_stats_sum(values, device=None, group=None):
+    """Sum of a few per-rank counters (cells, states) and max of times, for reporting only."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return list(values)
+    dev = device if device is not None else torch.device("cpu")
+    t = torch.tensor(list(values), dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t.cpu().tolist()

@@ -1,0 +1,3 @@
+// CustomMath.h — forwarding header: the reference's src/common/CustomMath.h surface lives in adk_mt.hpp (GPU-backed).
+#pragma once
+#include "adk_mt.hpp"

@@ -1,0 +1,3 @@
+// Utils.h — forwarding header: the reference's src/common/Utils.h surface lives in adk_mt.hpp (GPU-backed).
+#pragma once
+#include "adk_mt.hpp"

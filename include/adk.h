@@ -86,6 +86,8 @@ int adk_create(adk_ctx** out_ctx, int device);        /* device = CUDA ordinal; 
 void adk_destroy(adk_ctx* ctx);
 const char* adk_last_error(const adk_ctx* ctx);       /* text of the last failure on this context */
 int adk_set_memory_budget(adk_ctx* ctx, uint64_t bytes);   /* cap for DP workspaces (default: 60 % of free memory) */
+int adk_set_stream(adk_ctx* ctx, void* cuda_stream);       /* run on the caller's cudaStream_t (NULL = legacy default stream) */
+uint64_t adk_launch_count(const adk_ctx* ctx);             /* kernels launched by this context since adk_create */
 
 /* ---- whole solves (host buffers in, host buffers out; H2D/D2H inside) ------------------------------------------ */
 int adk_solve_area(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
@@ -114,6 +116,11 @@ int adk_area_partial_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uin
 int adk_area_diameter_partial_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax,
                                   double amax, double dmax, uint32_t shard, uint32_t nshards, adk_partial* out,
                                   adk_stats* stats);
+
+int adk_area_finish_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                        const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
+int adk_area_diameter_finish_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
+                                 double dmax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
 
 /* ---- precompute stages, exposed for parity tests ---------------------------------------------------------------- */
 int adk_count_tables(adk_ctx* ctx, const double* x, const double* y, uint32_t n,

@@ -1,0 +1,39 @@
+#!/usr/bin/env bash
+# Builds the reference's UNMODIFIED gtest (src/test/main.cpp) and pybind module (src/py-binding/main.cpp) against this
+# repo's GPU-backed libadk_host.so instead of the reference's src/common solver sources.  Proves the drop-in boundary:
+# same headers (the reference's own declarations), our definitions at link time.  Only Parser.cpp (JSON I/O, not on the
+# solver path) is taken from the reference.  Needs /root/reference; outputs go to tests/dropin/_build (git-ignored).
+set -euo pipefail
+here="$(cd "$(dirname "$0")" && pwd)"
+root="$(cd "$here/../.." && pwd)"
+ref="${ADK_REFERENCE_ROOT:-/root/reference}"
+[ -d "$ref/src/test" ] || { echo "build_dropin.sh: $ref not present, keeping prebuilt files" >&2; exit 0; }
+out="$here/_build"; mkdir -p "$out"
+json_inc="$(python - <<'PY'
+import os, sys
+for p in sys.path:
+    q = os.path.join(p, "include", "cudnn_frontend", "thirdparty")
+    if os.path.exists(os.path.join(q, "nlohmann", "json.hpp")):
+        print(q); break
+PY
+)"
+[ -n "$json_inc" ] || { echo "nlohmann/json.hpp not found" >&2; exit 1; }
+gt="$ref/external/googletest/googletest"
+pkg="$root/area-diameter-algorithm_b200"
+common=(-std=c++17 -O2 -w -include "$here/dropin_compat.h" -I"$json_inc")
+if [ ! -f "$out/gtest-all.o" ]; then
+  g++ -std=c++17 -O1 -w -I"$gt/include" -I"$gt" -c "$gt/src/gtest-all.cc" -o "$out/gtest-all.o" &
+  g++ -std=c++17 -O1 -w -I"$gt/include" -I"$gt" -c "$gt/src/gtest_main.cc" -o "$out/gtest_main.o" &
+fi
+g++ "${common[@]}" -c "$ref/src/common/Parser.cpp" -o "$out/Parser.o" &
+g++ "${common[@]}" -I"$gt/include" -c "$ref/src/test/main.cpp" -o "$out/ref_test_main.o" &
+wait
+g++ "$out/ref_test_main.o" "$out/Parser.o" "$out/gtest-all.o" "$out/gtest_main.o" -o "$out/ref_test_dropin" \
+    -L"$pkg" -ladk_host -ladk -Wl,-rpath,"$pkg" -Wl,-rpath,'$ORIGIN/../../../area-diameter-algorithm_b200' -lpthread
+# the reference's pybind11 module `thesis`, same treatment
+pyinc="$(python -c 'import sysconfig; print(sysconfig.get_paths()["include"])')"
+pbinc="$(python -c 'import pybind11; print(pybind11.get_include())')"
+ext="$(python -c 'import sysconfig; print(sysconfig.get_config_var("EXT_SUFFIX"))')"
+g++ "${common[@]}" -fPIC -shared -I"$pyinc" -I"$pbinc" "$ref/src/py-binding/main.cpp" -o "$out/thesis$ext" \
+    -L"$pkg" -ladk_host -ladk -Wl,-rpath,"$pkg" -Wl,-rpath,'$ORIGIN/../../../area-diameter-algorithm_b200'
+echo "built $out/ref_test_dropin $out/thesis$ext"

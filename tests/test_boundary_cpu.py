@@ -1,0 +1,111 @@
+"""The drop-in boundary, checked without a GPU: the C ABI library loads and exports what include/adk.h declares,
+fails loudly without a device, and the C++ mirror defines the reference's public symbols."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    with open(os.path.join(ROOT, "include", "adk.h")) as f:
+        text = f.read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(adk_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    lib = pkg.load_library()
+    names = _declared_symbols()
+    assert len(names) >= 18
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    assert sorted(pkg.EXPORTS) == names
+
+
+def test_no_cpu_fallback_without_a_device(pkg):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present; the loud-failure path is covered on CPU-only machines")
+    with pytest.raises(pkg.AdkError) as e:
+        pkg.Solver(0)
+    assert "adk_create failed" in str(e.value)
+
+
+def test_merge_is_lexicographic(pkg):
+    lib = pkg.load_library()
+    from importlib import import_module
+    capi = import_module("area_diameter_algorithm_b200.capi")
+    parts = [
+        dict(found=0, count=99, area=0.1, tie_key=0, w0=0, w1=0),
+        dict(found=1, count=7, area=3.0, tie_key=5, w0=1, w1=2),
+        dict(found=1, count=8, area=3.5, tie_key=9, w0=3, w1=4),
+        dict(found=1, count=8, area=3.25, tie_key=7, w0=5, w1=6),
+        dict(found=1, count=8, area=3.25, tie_key=6, w0=7, w1=8),
+    ]
+    arr = (capi.AdkPartial * len(parts))(*[capi.AdkPartial(p["found"], p["count"], p["area"], p["tie_key"], p["w0"], p["w1"]) for p in parts])
+    out = capi.AdkPartial()
+    assert lib.adk_merge(arr, ctypes.c_uint32(len(parts)), ctypes.byref(out)) == 0
+    assert (out.found, out.count, out.area, out.tie_key, out.w0, out.w1) == (1, 8, 3.25, 6, 7, 8)
+    dist = import_module("area_diameter_algorithm_b200.dist")
+    assert dist.merge_partials(parts) == parts[4]
+    assert dist.unpack_partial(dist.pack_partial(parts[3])) == parts[3]
+    assert dist.RECORD_BYTES == ctypes.sizeof(capi.AdkPartial) == 32
+
+
+def test_host_mirror_defines_the_reference_entry_points(built):
+    so = os.path.join(ROOT, "area-diameter-algorithm_b200", "libadk_host.so")
+    out = subprocess.run("nm -D --defined-only '%s' | c++filt" % so, shell=True, capture_output=True, text=True, check=True).stdout
+    for sym in ["MT::EppsteinAlgorithm(", "MT::EppsteinAlgorithmWithBenchmarkInfo(", "MT::AntipodalAlgorithm(",
+                "MT::AntipodalAlgorithmWithBenchmarkInfo(", "MT::AntipodalOptimizedAlgorithm(",
+                "MT::AntipodalOptimizedAlgorithmWithBenchmarkInfo(", "MT::CM::Distance2(", "MT::CM::AreCollinear(",
+                "MT::CM::Orientation(", "MT::CM::SignedArea(", "MT::Diameter::operator==(", "MT::CountPointsBelowAllSegments(",
+                "MT::SortPointsClockWiseAroundPoint(", "MT::ComputeDiameter("]:
+        assert sym in out, sym
+
+
+def test_reference_callers_build_unmodified_against_this_library(built):
+    """src/test/main.cpp and src/py-binding/main.cpp of the reference, compiled as they are, link against libadk_host.so."""
+    if not os.path.isdir("/root/reference/src/test"):
+        pytest.skip("the reference tree is only present in the build container")
+    subprocess.run([os.path.join(ROOT, "tests", "dropin", "build_dropin.sh")], check=True, capture_output=True)
+    assert os.path.exists(os.path.join(ROOT, "tests", "dropin", "_build", "ref_test_dropin"))
+
+
+def _gloo_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    ge.load_package()
+    from importlib import import_module
+    d = import_module("area_diameter_algorithm_b200.dist")
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    mine = [dict(found=1, count=9, area=2.5, tie_key=40, w0=4, w1=5), dict(found=1, count=9, area=2.5, tie_key=17, w0=1, w1=7)][rank]
+    parts = d.gather_partials(mine)
+    best = d.merge_partials(parts)
+    tot = d.gather_stats_sum([10.0 * (rank + 1), 1.0])
+    dist.destroy_process_group()
+    q.put((rank, best, len(parts), tot))
+
+
+def test_two_rank_gather_and_merge_over_gloo(built):
+    """The only exchange of the multi-GPU path (one 32-byte record per rank), world_size 2 on CPU."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, best, nparts, tot in got:
+        assert nparts == 2
+        assert best == dict(found=1, count=9, area=2.5, tie_key=17, w0=1, w1=7)
+        assert tot == [30.0, 2.0]

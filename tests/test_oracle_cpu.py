@@ -1,0 +1,110 @@
+"""The oracle (oracle/adk_oracle.c) pinned against the reference's golden vectors and live reference outputs.
+CPU only; this is what makes the oracle trustworthy as the checker of the CUDA path."""
+import random
+
+import pytest
+
+from util import xy, assert_same_solution, float32_equal, same_cycle
+
+
+def test_oracle_reproduces_reference_known_answers_path_A(golden, oracle):
+    """data/samples/tests/*/results.json, the assertions of src/test/main.cpp:93-101, all 100 instances."""
+    for name, t in golden["ref_tests"].items():
+        x, y = xy(golden["points"][name])
+        r = oracle.solve_area(x, y, t["max_count"], t["max_area"], True)
+        ca = t["convex_area"]
+        assert bool(r["found"]) == (ca is not None), name
+        if ca:
+            assert r["count"] == ca["count"], name
+            assert sorted(r["diam"]) == sorted(ca["diameter_indices"]), name
+            assert float32_equal(r["area"], ca["area"]), (name, r["area"], ca["area"])
+            assert same_cycle(ca["hull_indices"], r["hull"]), name
+
+
+def test_oracle_matches_live_reference_path_A_with_counters(golden, oracle):
+    for r in golden["runs"]["test.A"]:
+        x, y = xy(golden["points"][r["name"]])
+        g = oracle.solve_area(x, y, r["kmax"], r["amax"], True)
+        assert_same_solution(g, r, r["name"])
+        assert g["entries_alloc"] == r["entries_alloc"] and g["entries_required"] == r["entries_required"], r["name"]
+
+
+@pytest.mark.parametrize("tag,nmax", [("test.ADopt", 70), ("bind.ADopt.50", 80), ("bind.ADopt.75", 70)])
+def test_oracle_matches_live_reference_path_AD(golden, oracle, tag, nmax):
+    """Non-binding diameter (src/test/main.cpp:113) and binding diameters (no upstream golden: live reference runs)."""
+    for r in golden["runs"][tag]:
+        n = int(r["name"].split("/")[1])
+        if n > nmax:
+            continue
+        x, y = xy(golden["points"][r["name"]])
+        g = oracle.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], True)
+        assert_same_solution(g, r, (tag, r["name"]))
+        assert g["entries_required"] == r["entries_required"], (tag, r["name"])
+
+
+def test_oracle_matches_reference_bench_call_shape(golden, oracle):
+    """K = inf, A = 4, the diameter sweep of src/bench/main.cpp:57-59 on the shipped uniform / gaussian / real sets."""
+    for r in golden["runs"]["bench.ADopt"] + golden["runs"]["real.ADopt.d1"]:
+        if r["solve_ms"] > 400:
+            continue
+        x, y = xy(golden["points"][r["name"]])
+        g = oracle.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], True)
+        assert_same_solution(g, r, (r["name"], r["dmax"]))
+        assert g["entries_required"] == r["entries_required"]
+    for r in golden["runs"]["bench.A"][:3]:
+        x, y = xy(golden["points"][r["name"]])
+        g = oracle.solve_area(x, y, r["kmax"], r["amax"], True)
+        assert_same_solution(g, r, r["name"])
+        assert g["entries_required"] == r["entries_required"]
+
+
+def test_sweep_tables_equal_their_definitions(golden, oracle):
+    """Utils.cpp:74-143 (sweep) against the definitions of the reference's own disabled self-check (Utils.cpp:145-223),
+    including the real sets with equal-x / equal-y pairs and an eps-collinear triple."""
+    for name in ["tests/10/0", "tests/40/2", "tests/100/1", "uniform/10/0", "real/9/0", "real/6/0", "real/8/0"]:
+        x, y = xy(golden["points"][name])
+        assert oracle.count_tables(x, y) == oracle.count_tables_bruteforce(x, y), name
+
+
+def test_oracle_against_reference_library_on_random_inputs(oracle):
+    """Direct differential test against oracle/_ref (only where the reference was built, i.e. the build container)."""
+    from oracle.refpy import RefLib, ref_available
+    if not ref_available("x87"):
+        pytest.skip("oracle/_ref not built on this machine")
+    ref = RefLib("x87")
+    rng = random.Random(11)
+    for trial in range(12):
+        n = rng.choice([3, 4, 7, 15, 25, 40])
+        x = [rng.uniform(0, 10) for _ in range(n)]
+        y = [rng.uniform(0, 10) for _ in range(n)]
+        k = rng.choice([None, 3, 5, n])
+        a = rng.choice([2.0, 8.0, 30.0, float("inf")])
+        d = rng.choice([1.5, 4.0, 20.0])
+        assert_same_solution(oracle.solve_area(x, y, k, a, True), ref.solve(0, x, y, k, a, float("inf"), True), ("A", trial))
+        assert_same_solution(oracle.solve_area_diameter(x, y, k, a, d, True), ref.solve(2, x, y, k, a, d, True), ("AD", trial))
+        assert oracle.cw_order(x, y) == ref.cw_order(x, y)
+        assert oracle.count_tables(x, y) == ref.count_tables(x, y)
+
+
+def test_binary64_reference_variant_agrees_with_x87(golden):
+    """The tie-sensitivity detector: the reference compiled with 64-bit long double gives the same answers."""
+    from oracle.refpy import RefLib, ref_available
+    if not (ref_available("x87") and ref_available("f64")):
+        pytest.skip("oracle/_ref not built on this machine")
+    f64 = RefLib("f64")
+    for r in golden["runs"]["test.A"]:
+        if int(r["name"].split("/")[1]) > 40:
+            continue
+        x, y = xy(golden["points"][r["name"]])
+        assert_same_solution(f64.solve(0, x, y, r["kmax"], r["amax"], float("inf"), True), r, r["name"])
+
+
+def test_edge_cases(oracle):
+    assert oracle.solve_area([0, 1], [0, 1])["found"] == 0
+    assert oracle.solve_area([0, 1, 0], [0, 0, 1], 2)["found"] == 0
+    r = oracle.solve_area([0, 1, 0], [0, 0, 1], 3, 10.0)
+    assert r["found"] and r["count"] == 3 and abs(r["area"] - 0.5) < 1e-15
+    assert oracle.solve_area([0, 1, 0], [0, 0, 1], 3, 0.4)["found"] == 0
+    r = oracle.solve_area_diameter([0, 1, 0], [0, 0, 1], 3, 10.0, 10.0)
+    assert r["found"] and r["count"] == 3
+    assert oracle.solve_area_diameter([0, 1, 0], [0, 0, 1], 3, 10.0, 1.2)["found"] == 0

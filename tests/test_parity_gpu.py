@@ -1,0 +1,224 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle, the reference's golden vectors and the live
+reference outputs frozen in tests/golden/.  Integer results bit-exact; area within 1e-9 relative (north_star)."""
+import importlib
+import math
+import os
+import random
+import subprocess
+import sys
+
+import pytest
+
+from util import ROOT, xy, assert_same_solution, float32_equal, same_cycle, check_witness, write_reference_layout
+
+pytestmark = pytest.mark.gpu
+
+
+# ------------------------------------------------------------------------------------------------ precompute stages
+STAGE_SETS = ["tests/10/0", "tests/30/3", "tests/60/1", "tests/100/2", "uniform/10/0", "gaussian/0/0", "real/9/0", "real/6/0", "real/0/0"]
+
+
+@pytest.mark.parametrize("name", STAGE_SETS)
+def test_count_tables_and_orders(golden, solver, oracle, name):
+    x, y = xy(golden["points"][name])
+    assert solver.count_tables(x, y) == oracle.count_tables(x, y)          # Utils.cpp:74-143
+    if len(x) <= 400:
+        assert solver.cw_order(x, y) == oracle.cw_order(x, y)              # Utils.cpp:311-316
+    rng = random.Random(5)
+    n = len(x)
+    tri = [tuple(rng.sample(range(n), 3)) for _ in range(300)]
+    assert solver.points_in_triangle(x, y, tri) == oracle.points_in_triangle(x, y, tri)   # Utils.cpp:251-293
+
+
+@pytest.mark.parametrize("name", ["tests/20/0", "tests/50/4", "uniform/0/3", "real/9/0", "real/6/0"])
+def test_slope_order_and_lune_lists(golden, solver, oracle, name):
+    x, y = xy(golden["points"][name])
+    n = len(x)
+    rng = random.Random(9)
+    for _ in range(80):
+        i, j = rng.sample(range(n), 2)
+        if y[j] < y[i]:
+            i, j = j, i
+        assert solver.slope_order(x, y, i, j) == oracle.slope_order(x, y, i, j), (i, j)   # Eppstein.cpp:62-114
+    for _ in range(60):
+        s, t = sorted(rng.sample(range(n), 2))
+        gl, gr = solver.lune_lists(x, y, s, t)
+        ol, orr = oracle.lune_lists(x, y, s, t)                                                # AntipodalOptimized.cpp:39-109
+        assert (gl, gr) == (ol, orr), (s, t)
+
+
+# ------------------------------------------------------------------------------------------------ path A
+def test_area_path_reference_known_answers(golden, solver):
+    """The reference's own test (src/test/main.cpp:93-101) on all 100 golden instances."""
+    for name, t in golden["ref_tests"].items():
+        x, y = xy(golden["points"][name])
+        r = solver.solve_area(x, y, t["max_count"], t["max_area"], True)
+        ca = t["convex_area"]
+        assert bool(r["found"]) == (ca is not None), name
+        if ca:
+            assert r["count"] == ca["count"], name
+            assert sorted(r["diam"]) == sorted(ca["diameter_indices"]), name
+            assert float32_equal(r["area"], ca["area"]), name
+            assert same_cycle(ca["hull_indices"], r["hull"]), name
+
+
+def test_area_path_against_live_reference(golden, solver):
+    for r in golden["runs"]["test.A"] + golden["runs"]["bench.A"]:
+        x, y = xy(golden["points"][r["name"]])
+        g = solver.solve_area(x, y, r["kmax"], r["amax"], True)
+        assert_same_solution(g, r, r["name"])
+        n = len(x)
+        k = min(r["kmax"], n)
+        assert g["cells_nominal"] == (k - 2) * n * (n - 1) * (n - 2) // 3, r["name"]   # SURVEY 8d closed form
+
+
+def test_area_path_survey_recorded_n200(golden, solver):
+    r = [s for s in golden["ref_outputs"]["survey_recorded"] if s["tag"] == "survey.bench.A"][0]
+    x, y = xy(golden["points"][r["name"]])
+    g = solver.solve_area(x, y, None, 4.0, True)
+    assert_same_solution(g, r, r["name"])
+
+
+# ------------------------------------------------------------------------------------------------ path AD
+@pytest.mark.parametrize("tag", ["test.ADopt", "bind.ADopt.50", "bind.ADopt.75", "bench.ADopt", "real.ADopt", "real.ADopt.d1"])
+def test_area_diameter_path_against_live_reference(golden, solver, tag):
+    for r in golden["runs"][tag]:
+        x, y = xy(golden["points"][r["name"]])
+        g = solver.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], True)
+        assert_same_solution(g, r, (tag, r["name"], r["dmax"]))
+
+
+@pytest.mark.parametrize("tag", ["test.ADbasic", "bind.ADbasic.75"])
+def test_basic_variant_answers_are_served_by_the_same_kernels(golden, solver, tag):
+    """MT::AntipodalAlgorithm (Antipodal.cpp) live outputs vs the GPU path (SURVEY 8a row AD-basic)."""
+    for r in golden["runs"][tag]:
+        x, y = xy(golden["points"][r["name"]])
+        g = solver.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], True)
+        assert_same_solution(g, r, (tag, r["name"]))
+
+
+def test_survey_recorded_heavy_instances(golden, solver):
+    """gaussian/0 (114 s and 156 s on the CPU) and the densest real slide real/0 (61.6 min on the CPU)."""
+    for r in golden["ref_outputs"]["survey_recorded"]:
+        if r["algo"] != 2:
+            continue
+        x, y = xy(golden["points"][r["name"]])
+        g = solver.solve_area_diameter(x, y, None, r["amax"], r["dmax"], True)
+        assert_same_solution(g, r, (r["name"], r["dmax"]))
+
+
+def test_oracle_differential_on_seeded_random_inputs(solver, oracle):
+    rng = random.Random(2024)
+    for trial in range(40):
+        n = rng.choice([3, 4, 5, 8, 13, 21, 34, 55])
+        x = [rng.uniform(0, 12) for _ in range(n)]
+        y = [rng.uniform(0, 12) for _ in range(n)]
+        k = rng.choice([None, 3, 4, 6, n])
+        a = rng.choice([0.5, 3.0, 12.0, 60.0, float("inf")])
+        d = rng.choice([1.0, 3.0, 7.0, float("inf")])
+        assert_same_solution(solver.solve_area(x, y, k, a, True), oracle.solve_area(x, y, k, a, True), ("A", trial))
+        assert_same_solution(solver.solve_area_diameter(x, y, k, a, d, True), oracle.solve_area_diameter(x, y, k, a, d, True), ("AD", trial))
+
+
+def test_device_counters_match_the_oracle(golden, solver, oracle):
+    """AD cell updates (iterations of AntipodalOptimized.cpp:198,225,271,298) counted in-kernel == instrumented oracle."""
+    for name, d in [("tests/30/0", 9.0), ("tests/40/1", 12.0), ("uniform/0/0", 5.0), ("gaussian/12/0", 4.0)]:
+        x, y = xy(golden["points"][name])
+        g = solver.solve_area_diameter(x, y, None, 4.0 if "/0/" in name or "gaussian" in name else 60.0, d, False)
+        o = oracle.solve_area_diameter(x, y, None, 4.0 if "/0/" in name or "gaussian" in name else 60.0, d, False)
+        assert g["cells_executed"] == o["cells"], name
+        assert g["pairs"] == o["pairs"], name
+
+
+def test_edge_cases(solver):
+    assert solver.solve_area([0, 1], [0, 1])["found"] == 0                              # n < 3
+    assert solver.solve_area([0, 1, 0], [0, 0, 1], 2)["found"] == 0                     # K < 3
+    r = solver.solve_area([0, 1, 0], [0, 0, 1], 3, 10.0)
+    assert r["found"] and r["count"] == 3 and abs(r["area"] - 0.5) < 1e-15 and sorted(r["hull"]) == [0, 1, 2]
+    assert solver.solve_area([0, 1, 0], [0, 0, 1], 3, 0.4)["found"] == 0                # area bound excludes everything
+    r = solver.solve_area_diameter([0, 1, 0], [0, 0, 1], 3, 10.0, 10.0)
+    assert r["found"] and r["count"] == 3 and sorted(r["hull"]) == [0, 1, 2]
+    assert solver.solve_area_diameter([0, 1, 0], [0, 0, 1], 3, 10.0, 1.2)["found"] == 0  # diameter bound excludes everything
+    assert solver.solve_area_diameter([0, 1], [0, 1], None, 1.0, 1.0)["found"] == 0
+
+
+# ------------------------------------------------------------------------------------------------ sharding
+@pytest.mark.parametrize("nshards", [2, 3, 8])
+def test_shards_merge_to_the_whole_solve(golden, solver, nshards):
+    for name, a, d in [("tests/60/2", 80.0, 14.0), ("uniform/0/1", 4.0, 6.0)]:
+        x, y = xy(golden["points"][name])
+        whole = solver.solve_area(x, y, None, a, True)
+        parts = [solver.area_partial(x, y, None, a, s, nshards)[0] for s in range(nshards)]
+        fin = solver.area_finish(x, y, None, a, solver.merge(parts), True)
+        assert_same_solution(fin, whole, ("A", name))
+        whole = solver.solve_area_diameter(x, y, None, a, d, True)
+        ps = [solver.area_diameter_partial(x, y, None, a, d, s, nshards) for s in range(nshards)]
+        fin = solver.area_diameter_finish(x, y, None, a, d, solver.merge([p[0] for p in ps]), True)
+        assert_same_solution(fin, whole, ("AD", name))
+        assert sum(p[1]["cells_executed"] for p in ps) == whole["cells_executed"]
+
+
+# ------------------------------------------------------------------------------------------------ full-size properties
+def _synth():
+    import __graft_entry__ as ge
+    ge.load_package()
+    return importlib.import_module("area_diameter_algorithm_b200.synth")
+
+
+def test_full_size_properties_config4_n200(solver):
+    """BASELINE config 4 (synthetic n = 200, diameter sweep): witness validity and monotonicity in D, no oracle needed."""
+    pts = _synth().gaussian_points(200, 2.0, 200)
+    x, y = xy(pts)
+    ra = solver.solve_area(x, y, None, 4.0, True)
+    check_witness(x, y, ra, 4.0)
+    prev = 0
+    for d in (2.0, 3.0, 4.0, 5.0, 6.0):
+        r = solver.solve_area_diameter(x, y, None, 4.0, d, True)
+        check_witness(x, y, r, 4.0, d)
+        assert prev <= r["count"] <= ra["count"]
+        prev = r["count"]
+    big = solver.solve_area_diameter(x, y, None, 4.0, 1e9, True)
+    assert big["count"] == ra["count"] and abs(big["area"] - ra["area"]) <= 1e-9 * ra["area"]
+
+
+def test_full_size_properties_config3_n1000(solver, oracle):
+    """BASELINE config 3 (clustered n = 1000, area path): witness validity at full size; oracle parity with K capped at 16."""
+    pts = _synth().gaussian_points(1000, 2.0, 1000)
+    x, y = xy(pts)
+    r = solver.solve_area(x, y, None, 4.0, True)
+    check_witness(x, y, r, 4.0)
+    capped = solver.solve_area(x, y, 16, 4.0, True)
+    assert capped["count"] == 16
+    check_witness(x, y, capped, 4.0)
+    sub = 300
+    assert_same_solution(solver.solve_area(x[:sub], y[:sub], 16, 4.0, True), oracle.solve_area(x[:sub], y[:sub], 16, 4.0, True), "n300 K16")
+
+
+# ------------------------------------------------------------------------------------------------ drop-in callers
+def test_reference_gtest_binary_runs_against_the_gpu_library(golden, built):
+    """The reference's own src/test/main.cpp, compiled unmodified in the build container against libadk_host.so
+    (tests/dropin/build_dropin.sh), replayed here on the GPU: its assertions are the parity gate of SURVEY section 4."""
+    exe = os.path.join(ROOT, "tests", "dropin", "_build", "ref_test_dropin")
+    if not os.path.exists(exe):
+        pytest.skip("tests/dropin/_build not present (built only where /root/reference exists)")
+    write_reference_layout(golden, os.path.join(ROOT, "tests", "dropin", "_data"))
+    p = subprocess.run([exe], capture_output=True, text=True, timeout=1500, cwd=ROOT)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "[  PASSED  ] 1 test" in p.stdout
+
+
+def test_reference_pybind_module_runs_against_the_gpu_library(golden, built):
+    bdir = os.path.join(ROOT, "tests", "dropin", "_build")
+    if not any(f.startswith("thesis") for f in (os.listdir(bdir) if os.path.isdir(bdir) else [])):
+        pytest.skip("tests/dropin/_build not present")
+    code = (
+        "import sys, json; sys.path.insert(0, %r); import thesis;"
+        "pts=json.load(open(%r))['tests/20/0']; pts=[(p[0],p[1]) for p in pts];"
+        "print(json.dumps([thesis.AreaOnlyAlgorithm(pts, 18, 1e9, True), thesis.AreaDiameterAlgorithmOptimized(pts, 18, 1e9, 1e9, True),"
+        " thesis.AreaDiameterAlgorithm(pts, 2, 1.0, 1.0)]))" % (bdir, os.path.join(ROOT, "tests", "golden", "points.json")))
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    import json
+    a, ad, none = json.loads(p.stdout.strip().splitlines()[-1])
+    assert a[1] == ad[1] and abs(a[0] - ad[0]) < 1e-9 * a[0] and none is None
+    assert same_cycle(a[2], ad[2])
