@@ -9,7 +9,8 @@ import sys
 
 import pytest
 
-from util import ROOT, xy, assert_same_solution, float32_equal, same_cycle, check_witness, write_reference_layout
+from util import (ROOT, xy, assert_same_solution, float32_equal, same_cycle, check_witness, write_reference_layout,
+                  polygon_area)
 
 pytestmark = pytest.mark.gpu
 
@@ -94,7 +95,14 @@ def test_basic_variant_answers_are_served_by_the_same_kernels(golden, solver, ta
     for r in golden["runs"][tag]:
         x, y = xy(golden["points"][r["name"]])
         g = solver.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], True)
-        assert_same_solution(g, r, (tag, r["name"]))
+        # Antipodal.cpp's own reconstruction is not always self-consistent at a binding D: on tests/20/5 it returns a
+        # cycle whose polygon area (268.17) is not the area it reports (303.19) and whose diameter exceeds the bound.
+        # The witness is compared only where the reference's cycle really has the reported area; count, area and the
+        # diameter pair are always compared.
+        ref_hull_ok = (not r["found"]) or abs(polygon_area(x, y, r["hull"]) - r["area"]) <= 1e-7 * max(1.0, r["area"])
+        assert_same_solution(g, r, (tag, r["name"]), check_hull=ref_hull_ok)
+        if r["found"]:
+            check_witness(x, y, g, r["amax"], r["dmax"])
 
 
 def test_survey_recorded_heavy_instances(golden, solver):
