@@ -247,6 +247,44 @@ class Solver:
         self._check(rc, "adk_area_finish_dev")
         return self._pack(res, hull)
 
+    # ---- raw host-pointer variants (bench.py: pinned host buffers go straight through the C ABI) ------------------
+    def solve_area_diameter_host(self, px, py, n, kmax, amax, dmax, reconstruct=True):
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        rc = self.lib.adk_solve_area_diameter(self.ctx, ctypes.c_void_p(px), ctypes.c_void_p(py), ctypes.c_uint32(n),
+                                              ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_double(dmax),
+                                              ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0), ctypes.byref(res), hull)
+        self._check(rc, "adk_solve_area_diameter")
+        return self._pack(res, hull)
+
+    def solve_area_host(self, px, py, n, kmax, amax, reconstruct=True):
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        rc = self.lib.adk_solve_area(self.ctx, ctypes.c_void_p(px), ctypes.c_void_p(py), ctypes.c_uint32(n),
+                                     ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax),
+                                     ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0), ctypes.byref(res), hull)
+        self._check(rc, "adk_solve_area")
+        return self._pack(res, hull)
+
+    def area_diameter_partial_host(self, px, py, n, kmax, amax, dmax, shard, nshards):
+        p, s = AdkPartial(), AdkStats()
+        rc = self.lib.adk_area_diameter_partial(self.ctx, ctypes.c_void_p(px), ctypes.c_void_p(py), ctypes.c_uint32(n),
+                                                ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_double(dmax),
+                                                ctypes.c_uint32(shard), ctypes.c_uint32(nshards), ctypes.byref(p), ctypes.byref(s))
+        self._check(rc, "adk_area_diameter_partial")
+        return self._part(p), self._stats(s)
+
+    def area_diameter_finish_host(self, px, py, n, kmax, amax, dmax, best, reconstruct=True):
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n + 4, 4))()
+        b = self._unpart(best)
+        rc = self.lib.adk_area_diameter_finish(self.ctx, ctypes.c_void_p(px), ctypes.c_void_p(py), ctypes.c_uint32(n),
+                                               ctypes.c_uint64(_k(kmax)), ctypes.c_double(amax), ctypes.c_double(dmax),
+                                               ctypes.byref(b), ctypes.c_uint32(FLAG_RECONSTRUCT if reconstruct else 0),
+                                               ctypes.byref(res), hull)
+        self._check(rc, "adk_area_diameter_finish")
+        return self._pack(res, hull)
+
     # ---- precompute stages ---------------------------------------------------------------------------------------
     def count_tables(self, x, y):
         n = len(x)

@@ -574,7 +574,7 @@ int ad_prepare_arena(Ctx* c, unsigned long long V, uint32_t L, unsigned long lon
     const unsigned long long nV = std::max<unsigned long long>(V, c->ad_V), nQ = std::max<unsigned long long>(Q, c->ad_Q);
     const uint32_t nL = std::max<uint32_t>(L, c->ad_L);
     const size_t sb = slice_bytes_for(nV, nQ, nL);
-    uint64_t max_slices = std::max<uint64_t>(c->budget / sb, 0);
+    uint64_t max_slices = workspace_budget(c, c->arena) / sb;
     if (max_slices == 0) { c->err = "area+diameter path: one candidate's layer tables exceed the memory budget"; return ADK_ERR_NOMEM; }
     uint32_t slices = (uint32_t) std::min<uint64_t>(want_slices, max_slices);
     const bool same_layout = nV == c->ad_V && nQ == c->ad_Q && nL == c->ad_L && c->ad_slice_bytes == sb;

@@ -582,7 +582,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     ADK_CUDA(c, cudaStreamSynchronize(c->stream));
 
     // table plan: ring of (cmax + 1) levels, or every level up to full_m
-    const uint64_t budget_entries = std::max<uint64_t>(c->budget / sizeof(double), 1u << 20);
+    const uint64_t budget_entries = std::max<uint64_t>(workspace_budget(c, c->scratch5) / sizeof(double), 1u << 20);
     uint32_t b0 = 0;
     while (b0 < cnt)
     {

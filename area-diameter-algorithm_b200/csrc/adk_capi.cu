@@ -18,6 +18,34 @@ int set_cuda_error(Ctx* c, cudaError_t e, const char* what)
     return ADK_ERR_CUDA;
 }
 
+// Frees the large workspaces that the buffer being grown does not depend on: the AD arena (area path growing) or the
+// area path's tables (AD path growing).  cudaFree synchronises, so nothing in flight still reads them.
+void release_idle(Ctx* c, const DevBuf* keep)
+{
+    auto drop = [&](DevBuf& b) { if (&b != keep && b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; } };
+    if (keep == &c->arena) { drop(c->scratch5); drop(c->scratch4); drop(c->scratch2); drop(c->scratch1); }
+    else if (c->arena.p)
+    {
+        drop(c->arena);
+        c->ad_V = c->ad_Q = 0; c->ad_L = 0; c->ad_slices = 0; c->ad_slice_bytes = 0;
+    }
+}
+
+// Bytes a workspace may grow to right now: the configured budget, capped by what the device really has free
+// (counting the buffer's own current allocation), after releasing the other path's idle workspaces if needed.
+uint64_t workspace_budget(Ctx* c, const DevBuf& target)
+{
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); return c->budget; }
+    uint64_t avail = (uint64_t) ((free_b + target.cap) * 0.92);
+    if (avail < c->budget)
+    {
+        release_idle(c, &target);
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) avail = (uint64_t) ((free_b + target.cap) * 0.92);
+    }
+    return std::min<uint64_t>(c->budget, avail);
+}
+
 int ensure(Ctx* c, DevBuf& b, size_t bytes)
 {
     if (bytes <= b.cap) return ADK_OK;
@@ -28,6 +56,12 @@ int ensure(Ctx* c, DevBuf& b, size_t bytes)
     {
         cudaGetLastError();
         want = bytes;
+        e = cudaMalloc(&b.p, want);
+    }
+    if (e != cudaSuccess)
+    {
+        cudaGetLastError();
+        release_idle(c, &b);
         e = cudaMalloc(&b.p, want);
         if (e != cudaSuccess) { b.p = nullptr; cudaGetLastError(); c->err = "device allocation failed"; return ADK_ERR_NOMEM; }
     }

@@ -56,6 +56,8 @@ struct Ctx
 int set_cuda_error(Ctx* c, cudaError_t e, const char* what);
 int ensure(Ctx* c, DevBuf& b, size_t bytes);
 int ensure_pinned(Ctx* c, size_t bytes);
+void release_idle(Ctx* c, const DevBuf* keep);
+uint64_t workspace_budget(Ctx* c, const DevBuf& target);
 #define ADK_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return adk::set_cuda_error((ctx), e__, #call); } while (0)
 #define ADK_TRY(call) do { int r__ = (call); if (r__ != ADK_OK) return r__; } while (0)
 

@@ -1,0 +1,346 @@
+#!/usr/bin/env python3
+"""bench.py — the hot path's headline benchmark (BASELINE.json config 4: area+diameter-bounded DP, synthetic clustered
+n = 200, diameter sweep D in {2,3,4,5,6}, A = 4, K = inf, reconstruct = true — the call shape of src/bench/main.cpp:57-59,100).
+
+One STEP = the whole diameter sweep on one point set: five MT::AntipodalOptimizedAlgorithm-equivalent solves.
+Candidate diameter pairs are sharded over the ranks (adk_area_diameter_partial*, shard = rank), the only exchange is a
+32-byte record per rank per solve (all-gather), rank 0 reconstructs the witness.  Total work is fixed as N grows: "strong".
+
+  value : DP cell updates/s (one cell = one iteration of AntipodalOptimized.cpp:198,225,271,298; counted in-kernel and
+          equal to the instrumented oracle's count), inputs resident in HBM, device-timed over K steps, max over ranks.
+  e2e   : the same metric through the reference-facing C-ABI call with HOST buffers (pinned), H2D/D2H inside the timed region.
+  --impl reference : the UNMODIFIED reference (oracle/_ref/libadkref.so) on the host cores, on a bounded sample of the workload.
+
+Usage: python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--sigma S]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "dp_cell_updates_per_sec"
+UNIT = "cells/s"
+BYTES_PER_CELL = 20      # read-modify-write of the 8-byte destination area + 4-byte packed back-pointer
+FLOPS_PER_CELL = 20      # two Orientation tests (2 x 9) + area add + compare
+FP64_NOMINAL_TFLOPS = 37.2   # 148 SM x 64 FP64 lanes x 2 x 1.965 GHz (no measured FP64 entry in MEASURED_PEAKS.json)
+
+
+def load_workload(sigma):
+    with open(os.path.join(ROOT, "tests", "golden", "bench_n200.json")) as f:
+        fx = json.load(f)
+    key = str(float(sigma))
+    if key not in fx["sets"]:
+        raise SystemExit(f"--sigma {sigma}: not in tests/golden/bench_n200.json (have {sorted(fx['sets'])})")
+    st = fx["sets"][key]
+    x = [float(p[0]) for p in st["points"]]
+    y = [float(p[1]) for p in st["points"]]
+    return {"x": x, "y": y, "n": len(x), "amax": fx["amax"], "diameters": fx["diameters"], "sample": st["sample"],
+            "sigma": float(sigma), "seed": fx["seed"]}
+
+
+def workload_config(w, extra=None):
+    c = {"workload": f"area+diameter-bounded DP (AntipodalOptimized), synthetic Gaussian n={w['n']} sigma={w['sigma']} seed={w['seed']} "
+                     f"in [0,20]^2, A={w['amax']}, K=inf, reconstruct, diameter sweep D={w['diameters']} (BASELINE config 4)",
+         "n": w["n"], "sigma": w["sigma"], "amax": w["amax"], "diameters": w["diameters"],
+         "step": "one full diameter sweep (5 solves)"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms during the timed region (B200_PROFILING.md's clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(prefix="adk_clocks_", suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        try:
+            self.proc.terminate()
+            self.proc.wait(timeout=5)
+        except Exception:
+            pass
+        try:
+            rows = [r.strip().split(", ") for r in open(self.path).read().strip().splitlines() if r.strip()]
+            os.unlink(self.path)
+        except Exception:
+            return out
+        sm, reasons = [], set()
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                out["sm_max_mhz"] = float(r[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.strip().lower() == "active":
+                    reasons.add(name)
+        if sm:
+            sm.sort()
+            out["sm_mhz"] = sm[len(sm) // 2]
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------- reference arm
+def _ref_worker(args):
+    """One replica: the unmodified reference solving the sample instance (runs in its own process = its own core)."""
+    x, y, amax, dmax = args
+    from oracle.refpy import RefLib
+    lib = RefLib("x87")
+    t0 = time.perf_counter()
+    r = lib.solve(RefLib.ALGO_ANTIPODAL_OPTIMIZED, x, y, None, amax, dmax, True)
+    return time.perf_counter() - t0, r["count"], r["entries_required"]
+
+
+def _port_worker(args):
+    x, y, amax, dmax = args
+    from oracle.oraclepy import Oracle
+    o = Oracle()
+    t0 = time.perf_counter()
+    r = o.solve_area_diameter(x, y, None, amax, dmax, True)
+    return time.perf_counter() - t0, r["count"], r["states"]
+
+
+def cpu_reference_run(w, steps, warmup, cores=None):
+    """Times the reference's own CPU implementation on a bounded sample: the D = 2 solve of the sweep, one replica per host
+    core (instance-level parallelism is the only kind the single-threaded reference admits).  Returns the cpu_baseline dict."""
+    from multiprocessing import get_context
+    from oracle.refpy import ref_available
+    kind = "reference" if ref_available("x87") else "port"
+    worker = _ref_worker if kind == "reference" else _port_worker
+    smp = w["sample"][0]
+    ncores = cores or max(1, min(os.cpu_count() or 1, 32))
+    job = (w["x"], w["y"], w["amax"], smp["dmax"])
+    ctx = get_context("spawn")
+    times = []
+    with ctx.Pool(ncores) as pool:
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            res = pool.map(worker, [job] * ncores)
+            dt = time.perf_counter() - t0
+            for _, cnt, _ in res:
+                assert cnt == smp["count"], (cnt, smp["count"])
+            if it >= warmup:
+                times.append(dt)
+    total = sum(times)
+    cells = smp["cells"] * ncores * len(times)
+    return {"value": cells / total, "unit": UNIT, "cores": ncores, "kind": kind,
+            "sample": f"D={smp['dmax']} solve of the sweep ({smp['cells']} cells, {smp['states']} states), one replica per core, "
+                      f"{len(times)} timed passes, {total / len(times):.2f} s per pass",
+            "ms_per_step": 1e3 * total / len(times), "single_replica_s": min(r[0] for r in res)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    w = load_workload(args.sigma)
+    cb = cpu_reference_run(w, args.steps, args.warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f80 (x87 long double)" if cb["kind"] == "reference" else "f64", "data": "synthetic",
+            "config": workload_config(w, {"reference_step": "bounded sample: " + cb["sample"]}),
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------- B200 arm
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the host baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    pkg = ge.load_package()
+    import importlib
+    adist = importlib.import_module("area_diameter_algorithm_b200.dist")
+
+    w = load_workload(args.sigma)
+    n, amax, diams = w["n"], w["amax"], w["diameters"]
+    solver = pkg.Solver(local)
+    stream = torch.cuda.Stream(device=dev)
+    solver.set_stream(stream.cuda_stream)
+
+    d_x = torch.tensor(w["x"], dtype=torch.float64, device=dev)
+    d_y = torch.tensor(w["y"], dtype=torch.float64, device=dev)
+    h_x = torch.tensor(w["x"], dtype=torch.float64).pin_memory()
+    h_y = torch.tensor(w["y"], dtype=torch.float64).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def step(resident):
+        """One diameter sweep.  Returns (cells, states, dp_ms, launches, results) of THIS rank."""
+        cells = states = 0
+        dp_ms = 0.0
+        results = []
+        flush.zero_()                                   # L2 flush between steps (on the timed stream)
+        for d in diams:
+            if resident:
+                part, st = solver.area_diameter_partial_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, d, rank, world)
+            elif world == 1:
+                r = solver.solve_area_diameter_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, True)
+                cells += r["cells_executed"]; states += r["states"]; dp_ms += r["dp_ms"]
+                results.append(r)
+                continue
+            else:
+                part, st = solver.area_diameter_partial_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, rank, world)
+            cells += st["cells_executed"]; states += st["states"]; dp_ms += st["dp_ms"]
+            best = adist.merge_partials(adist.gather_partials(part, device=dev))
+            if rank == 0:
+                if resident:
+                    results.append(solver.area_diameter_finish_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, d, best, True))
+                else:
+                    results.append(solver.area_diameter_finish_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, best, True))
+        return cells, states, dp_ms, results
+
+    def timed(resident, steps, warmup):
+        with torch.cuda.stream(stream):
+            for _ in range(warmup):
+                step(resident)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); torch.cuda.synchronize()
+            l0 = solver.launch_count()
+            t0 = time.perf_counter()
+            ev0.record(stream)
+            cells = states = 0
+            dp_ms = 0.0
+            last = None
+            for _ in range(steps):
+                c, s, d, last = step(resident)
+                cells += c; states += s; dp_ms += d
+            ev1.record(stream)
+            torch.cuda.synchronize(); barrier()
+            wall_ms = 1e3 * (time.perf_counter() - t0)
+            dev_ms = ev0.elapsed_time(ev1)
+            launches = solver.launch_count() - l0 + steps     # + the flush memset per step
+        agg = torch.tensor([cells, states, launches], dtype=torch.float64, device=dev)
+        mx = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        return {"cells": int(agg[0].item()), "states": int(agg[1].item()), "launches": int(agg[2].item()),
+                "dev_ms": float(mx[0].item()), "wall_ms": float(mx[1].item()), "my_cells": cells, "my_dp_ms": dp_ms, "last": last}
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    res = timed(True, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e = timed(False, args.steps, max(1, args.warmup // 3))
+
+    if rank == 0:
+        secs = res["dev_ms"] / 1e3
+        value = res["cells"] / secs
+        peak, peak_src = measured_peaks()
+        # dominant kernel: k_ad_dp, timed by the library's own CUDA events on the launching stream, live in this run
+        dp_s = res["my_dp_ms"] / 1e3
+        launches_dp = args.steps * len(diams)
+        achieved = res["my_cells"] * BYTES_PER_CELL / dp_s / 1e9 if dp_s > 0 else 0.0
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("k_ad_dp_dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        fp64_tflops = res["my_cells"] * FLOPS_PER_CELL / dp_s / 1e12 if dp_s > 0 else 0.0
+        roof = {"bound": "hbm", "kernel": "k_ad_dp", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": res["my_cells"] * BYTES_PER_CELL / max(launches_dp, 1),
+                "avg_launch_ms": res["my_dp_ms"] / max(launches_dp, 1), "share_of_step": res["my_dp_ms"] / res["dev_ms"],
+                "fp64_issue": {"achieved": fp64_tflops, "peak": FP64_NOMINAL_TFLOPS, "unit": "TFLOP/s", "frac": fp64_tflops / FP64_NOMINAL_TFLOPS,
+                               "peak_source": "nominal 148 SM x 64 lanes x 2 x 1.965 GHz; 20 flop/cell (SURVEY 8d)"}}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": res["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": workload_config(w, {"parallelism": f"candidate pairs sharded over {world} rank(s)",
+                                              "l2": "256 MiB memset on the timed stream before every step; the layer-table arena also exceeds L2",
+                                              "states_per_step": res["states"] // args.steps, "cells_per_step": res["cells"] // args.steps}),
+                "solve_ms_per_instance": res["dev_ms"] / args.steps / len(diams),
+                "states_per_sec": res["states"] / secs,
+                "e2e": {"value": e2e["cells"] / (e2e["wall_ms"] / 1e3), "unit": UNIT, "ms_per_step": e2e["wall_ms"] / args.steps,
+                        "h2d_bytes_per_step": len(diams) * 2 * n * 8 * (1 if world == 1 else 2),
+                        "d2h_bytes_per_step": len(diams) * (64 + 4 * (n + 4) + 112), "timer": "host wall clock around the C-ABI calls, max over ranks"},
+                "gpu_launches": res["launches"], "roofline": roof, "clocks": clocks,
+                "answers": [{"D": d, "count": r["count"], "area": r["area"], "diam": r["diam"]} for d, r in zip(diams, res["last"])]}
+        # the sample instance must reproduce the reference's answer (the fixture holds the unmodified reference's output)
+        for smp in w["sample"]:
+            got = [r for d, r in zip(diams, res["last"]) if d == smp["dmax"]][0]
+            assert got["count"] == smp["count"] and got["hull"] == smp["hull"] and sorted(got["diam"]) == sorted(smp["diam"]), (got, smp)
+            assert abs(got["area"] - float(smp["area"])) <= 1e-9 * float(smp["area"])
+        if world == 1 and not args.no_cpu:
+            cb = cpu_reference_run(w, steps=2, warmup=0)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    solver.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--sigma", type=float, default=2.0, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.0, 0.5)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()
