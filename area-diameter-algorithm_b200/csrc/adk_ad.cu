@@ -4,15 +4,17 @@
 // B200-first reformulation (DESIGN.md "Path AD"):
 //   * Candidate diameter pairs (s,t) are independent (AntipodalOptimized.cpp:495-527): a persistent grid pulls
 //     them from a device queue, ONE CANDIDATE PER CTA.
-//   * The reference's per-layer std::unordered_map<key, Entry> becomes a dense per-layer table indexed by the
-//     state (side, o, s, ss) holding the area as an order-preserving 64-bit pattern; "insert or keep the smaller"
-//     (AntipodalOptimized.cpp:207-217) is one atomicMin, and a per-layer bitmap is the frontier.  Tables live in a
-//     per-CTA slice of an L2/HBM arena that every CTA leaves clean (each consumed state is reset), so the arena is
-//     initialised once per context, not once per candidate.
-//   * Layers are a wavefront (every transition adds c >= 1 points): bitmap scan -> CTA-local queue -> one warp per
-//     state, lanes over the candidate next vertices (the loops at AntipodalOptimized.cpp:198,225,271,298).
-//   * No back-pointers are stored: the winning candidate is re-run keeping its tables and the witness is recovered
-//     by re-deriving, for each state, the predecessor whose relaxed value equals the stored one.
+//   * A state of the reference (side, o, s, ss) is "pending edge s->ss on one chain, head o on the other chain".
+//     Grouping states by their two chain heads (a = head on L, b = head on R) gives a grid of CELLS (a,b):
+//     every transition out of cell (a,b) advances exactly one head, so cells on one anti-diagonal a+b are independent
+//     and every state vector "pending edge b->i with the other head at a" is produced ENTIRELY inside cell (a,b).
+//     The reference's per-layer unordered_map (insert-or-keep-smaller, :207-217) therefore needs no atomics and no
+//     global table: one warp owns a cell, lanes own destination vertices i, the minimum over predecessors is taken
+//     in a shared-memory accumulator acc[layer][lane] and compacted into an append-only record pool.
+//   * Geometry (the Orientation / PointLinePseudoDistance tests of :198-247, :271-324) depends on (source edge,
+//     destination vertex) only, not on the layer k: it is evaluated once per pair and reused for every layer.
+//   * The records stay in the pool, so the witness is recovered by re-running the winning candidate alone and
+//     re-deriving, for each state, the predecessor whose relaxed value equals the stored one (no back-pointers).
 #include "adk_internal.h"
 #include "adk_device.cuh"
 
@@ -31,8 +33,8 @@ struct PairStats
     unsigned int nqueued;           // candidates of this shard that can hold at least one interior point
     unsigned int max_nl, max_nr, max_lim;
     unsigned int pad;
-    unsigned long long max_cells;   // max over queued candidates of (lim + 1) * S
-    unsigned long long max_S;       // max states per layer
+    unsigned long long max_cells;   // max over queued candidates of nl * nr                      (cells of the head grid)
+    unsigned long long max_dirs;    // max over queued candidates of nl * nr * (nl + nr - 2) / 2   (directory entries)
 };
 
 struct CtaBest { uint32_t found; uint32_t count; double area; unsigned long long key; uint32_t s, t; };
@@ -95,9 +97,9 @@ __global__ void k_ad_pairs(const double* __restrict__ x, const double* __restric
             {
                 const uint32_t slot = atomicAdd(&stats->nqueued, 1u);
                 pairs[slot] = PairRec{i, j, nl, nr};
-                const unsigned long long S = (unsigned long long) nl * nr * nr + (unsigned long long) nr * nl * nl;
+                const unsigned long long cells = (unsigned long long) nl * nr;
                 atomicMax(&stats->max_nl, nl); atomicMax(&stats->max_nr, nr); atomicMax(&stats->max_lim, (unsigned int) lim);
-                atomicMax(&stats->max_S, S); atomicMax(&stats->max_cells, S * (lim + 1));
+                atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2) / 2);
             }
         }
     }
@@ -187,191 +189,448 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
     return c;
 }
 
-// Arena slice of one CTA: [vals: cells u64][bitmap: cells/32 + layers words][queue: S u32]
-struct Slice { unsigned long long* vals; unsigned int* bits; unsigned int* queue; };
 
-__device__ __forceinline__ Slice carve_slice(unsigned char* arena, size_t slice_bytes, uint32_t cta, unsigned long long max_cells,
-                                              unsigned long long max_S, uint32_t max_layers)
+// --------------------------------------------------------------------------------------------- the cell wavefront
+
+// Cell (a,b): a = index of the current vertex ("head") of the left chain in L, b = head of the right chain in R.
+//   RIGHT(a; s->b) : pending edge R[s]->R[b], left head L[a]   == reference Entry{o=a, s, ss=b, side RR/RL}
+//   LEFT (b; s->a) : pending edge L[s]->L[a], right head R[b]  == reference Entry{o=b, s, ss=a, side LL/LR}
+// Both kinds live in cell (a,b).  Expanding them (AntipodalOptimized.cpp:177-325) produces RIGHT(a; b->i), i > b
+// [cell (a,i)] and LEFT(b; a->i), i > a [cell (i,b)]: destination d of cell (a,b) is
+//   d <  nr-1-b : RIGHT(a; b -> b+1+d)          d >= nr-1-b : LEFT(b; a -> a+1+(d-(nr-1-b)))
+// and the whole layer vector of a destination is produced inside this one cell.
+
+constexpr int kCellWarps = 4;                    // warps per CTA (one candidate per CTA)
+constexpr int kCellThreads = kCellWarps * 32;
+constexpr int kBT = 32;                          // layers per accumulator tile
+constexpr int kSrcCap = 64;                      // source edges of a cell kept in shared memory (more spill to global)
+
+struct DirEnt { uint32_t off, len, kmin, kmax; };                 // records [off, off+len) of one (cell, destination), k ascending
+struct SrcRec { double tri, refd; uint32_t off; uint16_t len, sidx; uint16_t c, cx; uint32_t pad; };   // sidx bit 15: LEFT
+static_assert(sizeof(SrcRec) == 32, "SrcRec layout");
+
+// Per-CTA slice of the arena.
+struct CellSlice
 {
-    unsigned char* base = arena + (size_t) cta * slice_bytes;
-    Slice s;
-    s.vals = reinterpret_cast<unsigned long long*>(base);
-    s.bits = reinterpret_cast<unsigned int*>(base + sizeof(unsigned long long) * max_cells);
-    const size_t words = (size_t) (max_cells / 32) + max_layers + 1;
-    s.queue = s.bits + words;
-    (void) max_S;
+    unsigned char* alive;     // nl*nr flags: cell wrote its directory
+    DirEnt* dir;              // directory entries at fixed positions (dir_base)
+    double* vpool;            // record areas
+    uint16_t* kpool;          // record layers
+    SrcRec* spill;            // kCellWarps * spill_cap source records
+    uint32_t* spill_pred;     // kCellWarps * spill_cap predicate words
+};
+
+struct CellLayout { size_t off_dir, off_v, off_k, off_spill, off_pred, bytes; uint32_t cap, spill_cap; };
+
+__host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, uint32_t max_src, size_t slice_bytes)
+{
+    CellLayout Lo;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t) 255; };
+    Lo.spill_cap = max_src;
+    size_t o = up((size_t) max_cells);
+    Lo.off_dir = o; o = up(o + sizeof(DirEnt) * (size_t) max_dirs);
+    Lo.off_spill = o; o = up(o + sizeof(SrcRec) * (size_t) kCellWarps * max_src);
+    Lo.off_pred = o; o = up(o + sizeof(uint32_t) * (size_t) kCellWarps * max_src);
+    Lo.off_v = o;
+    const size_t rest = slice_bytes > o + 4096 ? slice_bytes - o - 4096 : 0;
+    const size_t cap = rest / 10;                                   // 8 B area + 2 B layer per record
+    Lo.cap = (uint32_t) (cap > 0xfffffff0ull ? 0xfffffff0ull : cap) & ~31u;
+    Lo.off_k = up(o + sizeof(double) * (size_t) Lo.cap);
+    Lo.bytes = slice_bytes;
+    return Lo;
+}
+
+__device__ __forceinline__ CellSlice carve_cells(unsigned char* arena, const CellLayout& Lo, uint32_t cta)
+{
+    unsigned char* base = arena + (size_t) cta * Lo.bytes;
+    CellSlice s;
+    s.alive = base;
+    s.dir = reinterpret_cast<DirEnt*>(base + Lo.off_dir);
+    s.vpool = reinterpret_cast<double*>(base + Lo.off_v);
+    s.kpool = reinterpret_cast<uint16_t*>(base + Lo.off_k);
+    s.spill = reinterpret_cast<SrcRec*>(base + Lo.off_spill);
+    s.spill_pred = reinterpret_cast<uint32_t*>(base + Lo.off_pred);
     return s;
 }
 
-__host__ inline size_t slice_bytes_for(unsigned long long max_cells, unsigned long long max_S, uint32_t max_layers)
+// First directory entry of cell (a,b); cells are laid out row-major, cell (a,b) has (nr-1-b) + (nl-1-a) destinations.
+__device__ __forceinline__ uint32_t dir_base(uint32_t a, uint32_t b, uint32_t nl, uint32_t nr)
 {
-    const size_t words = (size_t) (max_cells / 32) + max_layers + 1;
-    size_t b = sizeof(unsigned long long) * max_cells + sizeof(unsigned int) * (words + max_S);
-    return (b + 255) & ~(size_t) 255;
+    const uint32_t rows = a * (nr * (nr - 1) / 2) + nr * (a * (nl - 1) - a * (a - 1) / 2);
+    return rows + b * (nr - 1) - b * (b - 1) / 2 + b * (nl - 1 - a);
 }
 
-// Relax one destination state: "insert if absent, else keep the smaller area" (AntipodalOptimized.cpp:207-217).
-__device__ __forceinline__ void relax(unsigned long long* lvals, unsigned int* lbits, uint32_t idx, double area, unsigned int& new_states)
+struct CellCtx
 {
-    const unsigned long long old = atomicMin(lvals + idx, area_bits(area));
-    if (old == kInfBits) { atomicOr(lbits + (idx >> 5), 1u << (idx & 31)); ++new_states; }
+    // candidate
+    uint32_t nl, nr, lim, nlayers;
+    double Sx, Sy, Ex, Ey, seg2, amax;
+    int Sp, Ep;
+    LuneSmem S;
+    CellSlice sl;
+    uint32_t cap;
+    // warp-private shared memory
+    double* acc;            // kBT * 32
+    SrcRec* src;            // kSrcCap
+    uint32_t* pred;         // kSrcCap
+    SrcRec* spill;          // this warp's spill region
+    uint32_t* spill_pred;
+    // CTA-shared
+    unsigned int* bump;     // records allocated so far
+    unsigned int* overflow;
+};
+
+__device__ __forceinline__ SrcRec& src_at(const CellCtx& C, uint32_t i) { return i < (uint32_t) kSrcCap ? C.src[i] : C.spill[i - kSrcCap]; }
+__device__ __forceinline__ uint32_t& pred_at(const CellCtx& C, uint32_t i) { return i < (uint32_t) kSrcCap ? C.pred[i] : C.spill_pred[i - kSrcCap]; }
+
+constexpr unsigned kFull = 0xffffffffu;
+
+// Accumulates, for the 32 destinations of one tile, the layer rows [k0, k0 + rows) of acc (all +inf on entry):
+// acc[row][lane] = min over sources with a set predicate bit of (area + triangle), at layer k + c (:188-195, :207-217).
+__device__ __forceinline__ void cell_accumulate(const CellCtx& C, uint32_t P, uint32_t lane, uint32_t k0, uint32_t rows)
+{
+    for (uint32_t p = 0; p < P; ++p)
+    {
+        const uint32_t m = pred_at(C, p);
+        if (!m) continue;
+        const bool mine = (m >> lane) & 1u;
+        const SrcRec& r = src_at(C, p);
+        const uint32_t off = r.off, len = r.len, c = r.c, cx = r.cx;
+        const double tri = r.tri;
+        bool done = false;
+        for (uint32_t e0 = 0; e0 < len && !done; e0 += 32)
+        {
+            const uint32_t e = e0 + lane;
+            uint32_t kk = 0; double vv = 0.0;
+            if (e < len) { kk = C.sl.kpool[off + e]; vv = C.sl.vpool[off + e]; }
+            const uint32_t ne = min(32u, len - e0);
+            for (uint32_t t = 0; t < ne; ++t)
+            {
+                const uint32_t k = __shfl_sync(kFull, kk, t);
+                const double v = __shfl_sync(kFull, vv, t);
+                const uint32_t dst = k + c + (k == 0 ? cx : 0u);          // layer 0 carries the extra collinear term (:25-28 of the count)
+                if (dst >= C.nlayers || dst > C.lim || dst < k0) continue; // :192-195; layers beyond lim are never read
+                if (dst >= k0 + rows) { if (k > 0) { done = true; break; } continue; }   // records are k-ascending
+                const double v2 = __dadd_rn(v, tri);
+                if (!(v2 <= C.amax)) continue;                             // :203, :229, :276, :302
+                if (mine)
+                {
+                    double* q = C.acc + (dst - k0) * 32 + lane;
+                    if (v2 < *q) *q = v2;
+                }
+            }
+        }
+    }
 }
 
-template <bool KEEP>
-__global__ void __launch_bounds__(kAdThreads)
-k_ad_dp(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
-        const PairRec* __restrict__ pairs, uint32_t npairs, AdCounters* __restrict__ counters,
-        unsigned char* __restrict__ arena, size_t slice_bytes, unsigned long long max_cells, unsigned long long max_S,
-        uint32_t max_layers, uint32_t capL, uint32_t capR,
-        uint64_t kmax, uint32_t nlayers_ref, double amax, CtaBest* __restrict__ cta_best)
+// One warp expands every state of cell (a,b).  bk/bv: this lane's best terminal (layer, area).
+__device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint32_t b, uint32_t lane,
+                             uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
+{
+    const uint32_t nl = C.nl, nr = C.nr;
+    const LuneSmem& S = C.S;
+    const double Lax = S.Lx[a], Lay = S.Ly[a], Rbx = S.Rx[b], Rby = S.Ry[b];
+    const int Laidx = S.Lidx[a], Rbidx = S.Ridx[b];
+    const bool term_r = b == nr - 1, term_l = a == nl - 1;               // R[nr-1] = s, L[nl-1] = t   (:167-175)
+    const bool dead = dist2(Lax, Lay, Rbx, Rby) > C.seg2;                // :183-186 / :256-259
+    const uint32_t nDR = nr - 1 - b, nDL = nl - 1 - a, D = nDR + nDL;
+    const uint32_t lt = (1u << lane) - 1u;
+
+    // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b)
+    uint32_t P = 0, klo = 0xffffffffu, khi = 0;
+    const uint32_t npot = a + b;
+    for (uint32_t u0 = 0; u0 < npot; u0 += 32)
+    {
+        const uint32_t u = u0 + lane;
+        bool live = false, left = false;
+        uint32_t s = 0;
+        DirEnt de; de.off = 0; de.len = 0; de.kmin = 0; de.kmax = 0;
+        if (u < npot)
+        {
+            left = u >= b; s = left ? u - b : u;
+            const uint32_t pa = left ? s : a, pb = left ? b : s;
+            if (C.sl.alive[pa * nr + pb])
+            {
+                const uint32_t d = left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1);
+                de = C.sl.dir[dir_base(pa, pb, nl, nr) + d];
+                live = de.len > 0;
+            }
+        }
+        if (live && (left ? term_l : term_r))
+        {   // terminal states only report (:167-175): the deepest layer of this edge is its best
+            if (de.kmax > 0)
+            {
+                const double v = C.sl.vpool[de.off + de.len - 1];
+                if (de.kmax > bk || (de.kmax == bk && v < bv)) { bk = de.kmax; bv = v; }
+            }
+            live = false;
+        }
+        if (dead) live = false;
+        SrcRec r; r.tri = 0.0; r.refd = 0.0; r.off = de.off; r.len = (uint16_t) de.len; r.sidx = 0; r.c = 0; r.cx = 0; r.pad = 0;
+        if (live)
+        {
+            const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
+            const int pidx = left ? S.Lidx[s] : S.Ridx[s];
+            const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
+            const int hidx = left ? Laidx : Rbidx;
+            const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;      // fan apex of the edge's own chain
+            const int ap = left ? C.Ep : C.Sp;
+            const double ox = left ? Rbx : Lax, oy = left ? Rby : Lay;            // head of the other chain
+            r.tri = fabs(signed_area(apx, apy, psx, psy, hx, hy));               // :188 / :261
+            const uint32_t c = 1u + (uint32_t) tri_count_ad(T, false, pidx, psx, psy, hidx, hx, hy, ap, apx, apy);
+            const uint32_t cx = (uint32_t) T.C(pidx, ap);
+            r.c = (uint16_t) c; r.cx = (uint16_t) cx;
+            r.refd = pseudo_dist(psx, psy, hx, hy, ox, oy);                      // :222 / :295
+            r.sidx = (uint16_t) (s | (left ? 0x8000u : 0u));
+            // cell updates the reference performs for these states (:198,225,271,298), and the output layer range
+            uint32_t nvalid = de.len;
+            if (de.kmax + c + cx >= C.nlayers)
+            {
+                nvalid = 0;
+                for (uint32_t e = 0; e < de.len; ++e) { const uint32_t k = C.sl.kpool[de.off + e]; nvalid += (k + c + (k == 0 ? cx : 0u) < C.nlayers) ? 1u : 0u; }
+            }
+            my_cells += (unsigned long long) nvalid * D;
+            const uint32_t lo = de.kmin + c, hi = min(min(de.kmax + c + cx, C.lim), C.nlayers - 1);
+            if (nvalid == 0 || lo > hi || !(r.tri <= C.amax)) live = false;
+            else { klo = min(klo, lo); khi = max(khi, hi); }
+        }
+        const uint32_t lm = __ballot_sync(kFull, live);
+        if (live) src_at(C, P + __popc(lm & lt)) = r;
+        P += __popc(lm);
+    }
+    if (P == 0 || D == 0) return;
+    klo = __reduce_min_sync(kFull, klo); khi = __reduce_max_sync(kFull, khi);
+    __syncwarp();
+    const uint32_t ntiles = (khi - klo + kBT) / kBT;
+    const uint32_t dirb = dir_base(a, b, nl, nr);
+
+    for (uint32_t d0 = 0; d0 < D; d0 += 32)
+    {
+        const uint32_t d = d0 + lane;
+        const bool have = d < D, dR = d < nDR;
+        const uint32_t i = dR ? b + 1 + d : a + 1 + (d - nDR);
+        double qx = 0.0, qy = 0.0;
+        bool okR = false, okL = false;      // the part of the transition test that does not depend on the source edge
+        if (have)
+        {
+            qx = dR ? S.Rx[i] : S.Lx[i]; qy = dR ? S.Ry[i] : S.Ly[i];
+            if (dR)
+            {
+                okR = orientation(qx, qy, Rbx, Rby, C.Sx, C.Sy) >= 0;                                                        // :201 second test
+                okL = b == 0 || (orientation(Rbx, Rby, C.Sx, C.Sy, qx, qy) >= 0 && orientation(qx, qy, Rbx, Rby, C.Ex, C.Ey) >= 0);   // :301
+            }
+            else
+            {
+                okL = orientation(qx, qy, Lax, Lay, C.Ex, C.Ey) >= 0;                                                        // :274 second test
+                okR = a == 0 || (orientation(Lax, Lay, C.Ex, C.Ey, qx, qy) >= 0 && orientation(qx, qy, Lax, Lay, C.Sx, C.Sy) >= 0);   // :228
+            }
+        }
+        // per (source edge, destination) geometry, once for all layers
+        uint32_t anyp = 0;
+        for (uint32_t p = 0; p < P; ++p)
+        {
+            const SrcRec& r = src_at(C, p);
+            const uint32_t sx = r.sidx;
+            const bool left = (sx & 0x8000u) != 0;
+            const uint32_t s = sx & 0x7fffu;
+            const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
+            const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
+            bool ok = false;
+            if (have && (left ? okL : okR))
+            {
+                if (left != dR) ok = orientation(qx, qy, hx, hy, psx, psy) >= 0;     // stay on the edge's chain (:201, :274)
+                else ok = pseudo_dist(psx, psy, hx, hy, qx, qy) <= r.refd;           // switch chains (:226-227, :299-300)
+            }
+            const uint32_t m = __ballot_sync(kFull, ok);
+            if (lane == 0) pred_at(C, p) = m;
+            anyp |= m;
+        }
+        __syncwarp();
+        uint32_t cnt = 0, run = 0, kfirst = 0, klast = 0, lane_off = 0, base = 0;
+        bool fits = true;
+        if (anyp)
+        {
+            for (uint32_t pass = 0; pass < (ntiles > 1 ? 2u : 1u); ++pass)
+            {
+                const bool counting = pass == 0, emitting = ntiles == 1 || pass == 1;
+                for (uint32_t t = 0; t < ntiles; ++t)
+                {
+                    const uint32_t k0 = klo + t * kBT, rows = min((uint32_t) kBT, khi + 1 - k0);
+                    cell_accumulate(C, P, lane, k0, rows);
+                    if (counting)
+                    {
+                        for (uint32_t rr = 0; rr < rows; ++rr) cnt += C.acc[rr * 32 + lane] < INFINITY ? 1u : 0u;
+                        if (t == ntiles - 1)
+                        {   // allocate this tile's records: exclusive scan over the lanes, one bump of the CTA's pool
+                            uint32_t incl = cnt;
+                            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, o); if ((int) lane >= o) incl += v; }
+                            lane_off = incl - cnt;
+                            const uint32_t total = __shfl_sync(kFull, incl, 31);
+                            if (lane == 0 && total) base = atomicAdd(C.bump, total);
+                            base = __shfl_sync(kFull, base, 0);
+                            fits = (unsigned long long) base + total <= C.cap;
+                            if (!fits && lane == 0) *C.overflow = 1u;
+                            if (fits && lane == 0) my_states += total;
+                        }
+                    }
+                    if (emitting)
+                    {
+                        for (uint32_t rr = 0; rr < rows; ++rr)
+                        {
+                            const double v = C.acc[rr * 32 + lane];
+                            if (v < INFINITY)
+                            {
+                                if (fits) { const uint32_t at = base + lane_off + run; C.sl.vpool[at] = v; C.sl.kpool[at] = (uint16_t) (k0 + rr); }
+                                if (run == 0) kfirst = k0 + rr;
+                                klast = k0 + rr; ++run;
+                            }
+                        }
+                    }
+                    for (uint32_t rr = 0; rr < rows; ++rr) C.acc[rr * 32 + lane] = INFINITY;
+                }
+            }
+        }
+        if (have)
+        {
+            DirEnt de; de.off = base + lane_off; de.len = fits ? run : 0u; de.kmin = kfirst; de.kmax = klast;
+            C.sl.dir[dirb + d] = de;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) C.sl.alive[a * nr + b] = 1;
+}
+
+struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best terminal layer (0 = none) of one candidate
+
+__host__ __device__ inline size_t cells_warp_smem() { return sizeof(double) * kBT * 32 + sizeof(SrcRec) * kSrcCap + sizeof(uint32_t) * kSrcCap; }
+__host__ __device__ inline size_t cells_smem_bytes(uint32_t capL, uint32_t capR)
+{
+    return ((lune_smem_bytes(capL, capR, 0) + 15) & ~(size_t) 15) + kCellWarps * cells_warp_smem();
+}
+
+// Runs the whole layered DP of ONE candidate (already described by pr) inside the calling CTA's slice.
+__device__ void run_candidate(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, const Tables& T, const PairRec& pr,
+                              CellCtx& C, uint32_t* s_cnt, uint32_t* s_wk, double* s_wv, uint64_t kmax, uint32_t nlayers_ref,
+                              unsigned long long& my_cells, unsigned int& my_states, CandResult& out)
+{
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    build_lune(x, y, n, pr, C.S, s_cnt);
+    const uint32_t nl = pr.nl, nr = pr.nr;
+    const uint64_t inner = (uint64_t) nl + nr - 4;
+    C.nl = nl; C.nr = nr;
+    C.lim = (uint32_t) (kmax - 2 < inner ? kmax - 2 : inner);           // :137
+    C.nlayers = nlayers_ref;                                          // :483
+    C.Sx = C.S.Lx[0]; C.Sy = C.S.Ly[0]; C.Ex = C.S.Lx[nl - 1]; C.Ey = C.S.Ly[nl - 1];
+    C.Sp = C.S.Lidx[0]; C.Ep = C.S.Lidx[nl - 1];
+    C.seg2 = dist2(C.Sx, C.Sy, C.Ex, C.Ey);
+    // reset the slice: no cell has produced anything; cell (0,0) "produces" the layer-0 seeds (:149-160):
+    // RIGHT(0; 0->i) and LEFT(0; 0->i) all share one record (layer 0, area 0)
+    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) C.sl.alive[t] = 0;
+    const uint32_t D0 = (nr - 1) + (nl - 1);
+    for (uint32_t t = threadIdx.x; t < D0; t += blockDim.x) { DirEnt de; de.off = 0; de.len = 1; de.kmin = 0; de.kmax = 0; C.sl.dir[t] = de; }
+    if (threadIdx.x == 0) { C.sl.vpool[0] = 0.0; C.sl.kpool[0] = 0; *C.bump = 1u; *C.overflow = 0u; }
+    __syncthreads();
+    if (threadIdx.x == 0) C.sl.alive[0] = 1;
+    my_states += (threadIdx.x == 0) ? D0 : 0u;
+    uint32_t bk = 0; double bv = INFINITY;
+    __syncthreads();
+    // anti-diagonals of the head grid: every cell of diagonal a+b = d only reads cells of earlier diagonals
+    const uint32_t ndiag = nl + nr - 1;
+    for (uint32_t d = 1; d < ndiag; ++d)
+    {
+        const uint32_t alo = d > nr - 1 ? d - (nr - 1) : 0u, ahi = min(d, nl - 1);
+        for (uint32_t a = alo + warp; a <= ahi; a += kCellWarps) process_cell(C, T, a, d - a, lane, bk, bv, my_cells, my_states);
+        __syncthreads();
+    }
+    // best terminal state of the candidate: deepest layer, then smallest area (:169-173)
+    for (int o = 16; o; o >>= 1)
+    {
+        const uint32_t ok = __shfl_xor_sync(kFull, bk, o); const double ov = __shfl_xor_sync(kFull, bv, o);
+        if (ok > bk || (ok == bk && ov < bv)) { bk = ok; bv = ov; }
+    }
+    if (lane == 0) { s_wk[warp] = bk; s_wv[warp] = bv; }
+    __syncthreads();
+    uint32_t k = 0; double v = INFINITY;
+    for (int w = 0; w < kCellWarps; ++w) if (s_wk[w] > k || (s_wk[w] == k && s_wv[w] < v)) { k = s_wk[w]; v = s_wv[w]; }
+    out.kbest = k; out.area = v;
+    __syncthreads();
+}
+
+__device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, uint32_t capL, uint32_t capR, unsigned char* arena,
+                                          const CellLayout& Lo, uint32_t slice, double amax, unsigned int* bump, unsigned int* overflow)
+{
+    const uint32_t warp = threadIdx.x >> 5;
+    C.S = carve_smem(smem_raw, capL, capR);
+    unsigned char* wbase = smem_raw + ((lune_smem_bytes(capL, capR, 0) + 15) & ~(size_t) 15) + warp * cells_warp_smem();
+    C.acc = reinterpret_cast<double*>(wbase);
+    C.src = reinterpret_cast<SrcRec*>(wbase + sizeof(double) * kBT * 32);
+    C.pred = reinterpret_cast<uint32_t*>(wbase + sizeof(double) * kBT * 32 + sizeof(SrcRec) * kSrcCap);
+    C.sl = carve_cells(arena, Lo, slice);
+    C.spill = C.sl.spill + (size_t) warp * Lo.spill_cap;
+    C.spill_pred = C.sl.spill_pred + (size_t) warp * Lo.spill_cap;
+    C.cap = Lo.cap; C.amax = amax; C.bump = bump; C.overflow = overflow;
+    for (uint32_t t = threadIdx.x & 31; t < (uint32_t) kBT * 32; t += 32) C.acc[t] = INFINITY;
+}
+
+// One candidate pair per CTA, pulled from a device queue.  `order` (optional) lists the queue in processing order.
+__global__ void __launch_bounds__(kCellThreads)
+k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
+           const PairRec* __restrict__ pairs, const uint32_t* __restrict__ order, uint32_t npairs, AdCounters* __restrict__ counters,
+           unsigned char* arena, CellLayout Lo, uint32_t capL, uint32_t capR,
+           uint64_t kmax, uint32_t nlayers_ref, double amax, CtaBest* __restrict__ cta_best,
+           uint32_t* __restrict__ ovf_list, unsigned int* __restrict__ ovf_count)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
-    __shared__ unsigned int s_pair, s_qn;
-    __shared__ unsigned long long s_term;
+    __shared__ unsigned int s_pair, s_bump, s_overflow;
+    __shared__ uint32_t s_wk[kCellWarps];
+    __shared__ double s_wv[kCellWarps];
     __shared__ CtaBest s_best;
-    LuneSmem S = carve_smem(smem_raw, capL, capR);
-    const Slice sl = carve_slice(arena, slice_bytes, blockIdx.x, max_cells, max_S, max_layers);
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    CellCtx C;
+    setup_ctx(C, smem_raw, capL, capR, arena, Lo, blockIdx.x, amax, &s_bump, &s_overflow);
+    const uint32_t lane = threadIdx.x & 31;
     unsigned long long my_cells = 0; unsigned int my_states = 0;
     if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0; }
-
     for (;;)
     {
         __syncthreads();
         if (threadIdx.x == 0) s_pair = atomicAdd(&counters->queue, 1u);
         __syncthreads();
-        const uint32_t pi = s_pair;
-        if (pi >= npairs) break;
+        const uint32_t qi = s_pair;
+        if (qi >= npairs) break;
+        const uint32_t pi = order ? order[qi] : qi;
         const PairRec pr = pairs[pi];
-        build_lune(x, y, n, pr, S, s_cnt);
-        const uint32_t nl = pr.nl, nr = pr.nr;
-        const uint64_t inner = (uint64_t) nl + nr - 4;
-        const uint32_t lim = (uint32_t) (kmax - 2 < inner ? kmax - 2 : inner);
-        const uint32_t SR = nl * nr * nr, SL = nr * nl * nl, SS = SR + SL;
-        const uint32_t WD = (SS + 31) / 32;
-        const double Sx = S.Lx[0], Sy = S.Ly[0], Ex = S.Lx[nl - 1], Ey = S.Ly[nl - 1];
-        const int Sp = S.Lidx[0], Ep = S.Lidx[nl - 1];
-        const double seg2 = dist2(Sx, Sy, Ex, Ey);
-        for (uint32_t k = threadIdx.x; k <= lim; k += blockDim.x) S.lflag[k] = 0;
-        __syncthreads();
-        // layer-0 seeds (AntipodalOptimized.cpp:149-160): LL (o=0, s=0, ss=i) and RR (o=0, s=0, ss=i), area 0
-        for (uint32_t i = 1 + threadIdx.x; i < nl; i += blockDim.x)
-        {
-            const uint32_t idx = SR + i;
-            sl.vals[idx] = 0ull; atomicOr(sl.bits + (idx >> 5), 1u << (idx & 31)); ++my_states;
-        }
-        for (uint32_t i = 1 + threadIdx.x; i < nr; i += blockDim.x)
-        {
-            const uint32_t idx = i;
-            sl.vals[idx] = 0ull; atomicOr(sl.bits + (idx >> 5), 1u << (idx & 31)); ++my_states;
-        }
-        if (threadIdx.x == 0) S.lflag[0] = 1;
-        uint32_t best_k = 0; double best_area = 0.0;
-        __syncthreads();
-
-        for (uint32_t k = 0; k <= lim; ++k)
-        {
-            if (!S.lflag[k]) continue;        // uniform: written before the last barrier
-            unsigned long long* lv = sl.vals + (size_t) k * SS;
-            unsigned int* lb = sl.bits + (size_t) k * WD;
-            if (threadIdx.x == 0) { s_qn = 0; s_term = kInfBits; }
-            __syncthreads();
-            // frontier: bitmap -> queue
-            for (uint32_t w = threadIdx.x; w < WD; w += blockDim.x)
-            {
-                unsigned int bits = __ldcg(lb + w);
-                if (!bits) continue;
-                if (!KEEP) lb[w] = 0u;
-                const uint32_t cnt = __popc(bits);
-                uint32_t at = atomicAdd(&s_qn, cnt);
-                while (bits) { const int b = __ffs(bits) - 1; bits &= bits - 1; sl.queue[at++] = w * 32 + b; }
-            }
-            __syncthreads();
-            const uint32_t qn = s_qn;
-            // expand: one warp per state
-            for (uint32_t q = warp; q < qn; q += nwarps)
-            {
-                const uint32_t idx = sl.queue[q];
-                const double area0 = bits_area(__ldcg(lv + idx));
-                if (!KEEP) { if (lane == 0) lv[idx] = kInfBits; }
-                const bool right = idx < SR;
-                uint32_t o, s, ss;
-                if (right) { ss = idx % nr; const uint32_t t = idx / nr; s = t % nr; o = t / nr; }
-                else { const uint32_t v = idx - SR; ss = v % nl; const uint32_t t = v / nl; s = t % nl; o = t / nl; }
-                // terminal states (AntipodalOptimized.cpp:167-175)
-                if ((right && ss == nr - 1) || (!right && ss == nl - 1))
-                {
-                    if (k > 0 && lane == 0) atomicMin(&s_term, area_bits(area0));
-                    continue;
-                }
-                // "own" chain = the side of the pending edge; "other" chain = the opposite one
-                const double* ownx = right ? S.Rx : S.Lx; const double* owny = right ? S.Ry : S.Ly;
-                const double* othx = right ? S.Lx : S.Rx; const double* othy = right ? S.Ly : S.Ry;
-                const int32_t* owni = right ? S.Ridx : S.Lidx;
-                const uint32_t nown = right ? nr : nl, noth = right ? nl : nr;
-                const double ax = right ? Sx : Ex, ay = right ? Sy : Ey;      // fan apex of the own chain
-                const int ap = right ? Sp : Ep;
-                const double bx = right ? Ex : Sx, by = right ? Ey : Sy;      // fan apex of the other chain
-                const double ox = othx[o], oy = othy[o];                       // current vertex of the other chain
-                const double rx = ownx[s], ry = owny[s];                       // tail of the pending edge
-                const double px = ownx[ss], py = owny[ss];                     // head of the pending edge
-                if (dist2(ox, oy, px, py) > seg2) continue;                    // :183-186 / :256-259
-                const double tri = fabs(signed_area(ax, ay, rx, ry, px, py));  // :188 / :261
-                const uint32_t c = 1u + (uint32_t) tri_count_ad(T, k == 0, owni[s], rx, ry, owni[ss], px, py, ap, ax, ay);
-                const double area = __dadd_rn(area0, tri);
-                if ((uint64_t) c + k >= nlayers_ref) continue;                 // :192-195
-                my_cells += (lane == 0) ? (unsigned long long) (nown - 1 - ss) + (noth - 1 - o) : 0ull;
-                const uint32_t dst = k + c;
-                if (dst > lim || !(area <= amax)) continue;                    // deeper layers are never read; :203
-                unsigned long long* dv = sl.vals + (size_t) dst * SS;
-                unsigned int* db = sl.bits + (size_t) dst * WD;
-                bool any = false;
-                // stay on the own chain (:198-220 / :271-293): new pending edge ss -> i
-                const uint32_t base_stay = right ? (o * nr + ss) * nr : SR + (o * nl + ss) * nl;
-                for (uint32_t i = ss + 1 + lane; i < nown; i += 32)
-                {
-                    const double qx = ownx[i], qy = owny[i];
-                    if (orientation(qx, qy, px, py, rx, ry) >= 0 && orientation(qx, qy, px, py, ax, ay) >= 0)
-                    { relax(dv, db, base_stay + i, area, my_states); any = true; }
-                }
-                // switch to the other chain (:222-248 / :295-324): new pending edge o -> i there
-                const double refd = pseudo_dist(rx, ry, px, py, ox, oy);
-                const uint32_t base_sw = right ? SR + (ss * nl + o) * nl : (ss * nr + o) * nr;
-                for (uint32_t i = o + 1 + lane; i < noth; i += 32)
-                {
-                    const double qx = othx[i], qy = othy[i];
-                    const double d = pseudo_dist(rx, ry, px, py, qx, qy);
-                    if (d <= refd && (o == 0 || (orientation(ox, oy, bx, by, qx, qy) >= 0 && orientation(qx, qy, ox, oy, ax, ay) >= 0)))
-                    { relax(dv, db, base_sw + i, area, my_states); any = true; }
-                }
-                if (any) S.lflag[dst] = 1;
-            }
-            __syncthreads();
-            if (s_term != kInfBits) { best_k = k; best_area = bits_area(s_term); }
-            __syncthreads();
+        CandResult res;
+        unsigned long long cells0 = my_cells; unsigned int states0 = my_states;
+        run_candidate(x, y, n, T, pr, C, s_cnt, s_wk, s_wv, kmax, nlayers_ref, my_cells, my_states, res);
+        if (s_overflow)
+        {   // the record pool of this slice was too small: the host re-runs the candidate in a larger slice
+            my_cells = cells0; my_states = states0;
+            if (threadIdx.x == 0) ovf_list[atomicAdd(ovf_count, 1u)] = pi;
+            continue;
         }
         // candidate result (AntipodalOptimized.cpp:328-331, 512-517): count desc, area asc, first pair in (i<j) order
-        if (threadIdx.x == 0 && best_k > 0)
+        if (threadIdx.x == 0 && res.kbest > 0)
         {
-            const uint32_t cnt = best_k + 2;
+            const uint32_t cnt = res.kbest + 2;
             const unsigned long long key = (unsigned long long) pr.s * n + pr.t;
             const bool better = !s_best.found || cnt > s_best.count ||
-                                (cnt == s_best.count && (best_area < s_best.area || (best_area == s_best.area && key < s_best.key)));
-            if (better) { s_best.found = 1; s_best.count = cnt; s_best.area = best_area; s_best.key = key; s_best.s = pr.s; s_best.t = pr.t; }
+                                (cnt == s_best.count && (res.area < s_best.area || (res.area == s_best.area && key < s_best.key)));
+            if (better) { s_best.found = 1; s_best.count = cnt; s_best.area = res.area; s_best.key = key; s_best.s = pr.s; s_best.t = pr.t; }
         }
     }
-    // per-CTA totals
-    for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(0xffffffffu, my_cells, o); my_states += __shfl_xor_sync(0xffffffffu, my_states, o); }
+    for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(kFull, my_cells, o); my_states += __shfl_xor_sync(kFull, my_states, o); }
     if (lane == 0) { atomicAdd(&counters->cells, my_cells); atomicAdd(&counters->states, (unsigned long long) my_states); }
     __syncthreads();
     if (threadIdx.x == 0) cta_best[blockIdx.x] = s_best;
 }
 
-__global__ void k_ad_reduce(const CtaBest* __restrict__ in, uint32_t count, CtaBest* __restrict__ out)
+__global__ void k_ad_reduce(const CtaBest* __restrict__ in, uint32_t count, CtaBest* __restrict__ out, int merge_existing)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    CtaBest b; b.found = 0; b.count = 0; b.area = 0.0; b.key = ~0ull; b.s = b.t = 0;
+    CtaBest b;
+    if (merge_existing) b = *out;
+    else { b.found = 0; b.count = 0; b.area = 0.0; b.key = ~0ull; b.s = b.t = 0; }
     for (uint32_t i = 0; i < count; ++i)
     {
         const CtaBest c = in[i];
@@ -382,79 +641,70 @@ __global__ void k_ad_reduce(const CtaBest* __restrict__ in, uint32_t count, CtaB
     *out = b;
 }
 
-// Resets every table entry a KEEP run left behind (layers 0..lim of slice 0).
-__global__ void k_ad_clean(unsigned char* __restrict__ arena, size_t slice_bytes, unsigned long long max_cells, unsigned long long max_S,
-                           uint32_t max_layers, uint32_t SS, uint32_t lim)
-{
-    const Slice sl = carve_slice(arena, slice_bytes, 0, max_cells, max_S, max_layers);
-    const uint32_t WD = (SS + 31) / 32;
-    const size_t words = (size_t) WD * (lim + 1);
-    for (size_t w = (size_t) blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (size_t) gridDim.x * blockDim.x)
-    {
-        unsigned int bits = sl.bits[w];
-        if (!bits) continue;
-        sl.bits[w] = 0u;
-        const size_t layer = w / WD, off = (w % WD) * 32;
-        while (bits) { const int b = __ffs(bits) - 1; bits &= bits - 1; sl.vals[layer * SS + off + b] = kInfBits; }
-    }
-}
-
-__global__ void k_fill_u64(unsigned long long* __restrict__ p, size_t count, unsigned long long v)
-{
-    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (size_t) gridDim.x * blockDim.x) p[i] = v;
-}
-
-__global__ void k_ad_init_arena(unsigned char* __restrict__ arena, size_t slice_bytes, uint32_t nslices,
-                                unsigned long long V, size_t words)
-{
-    // vals <- +inf, bitmaps <- 0 for every slice
-    for (uint32_t s = blockIdx.y; s < nslices; s += gridDim.y)
-    {
-        unsigned char* base = arena + (size_t) s * slice_bytes;
-        unsigned long long* vals = reinterpret_cast<unsigned long long*>(base);
-        unsigned int* bits = reinterpret_cast<unsigned int*>(base + sizeof(unsigned long long) * V);
-        for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < V; i += (size_t) gridDim.x * blockDim.x) vals[i] = kInfBits;
-        for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (size_t) gridDim.x * blockDim.x) bits[i] = 0u;
-    }
-}
-
 // --------------------------------------------------------------------------------------------- witness recovery
 
 struct AdHull { uint32_t len; uint32_t ok; uint32_t nl, nr; };
 
+// Area pattern of the reference state Entry{o, s, ss} on the given side at layer k, or +inf if it was never reached.
+__device__ unsigned long long state_value(const CellSlice& sl, uint32_t nl, uint32_t nr, bool right, uint32_t o, uint32_t s, uint32_t ss, uint32_t k)
+{
+    uint32_t pa, pb, d;
+    if (right) { pa = o; pb = s; d = ss - s - 1; }                       // RIGHT(o; s->ss): produced by cell (o, s)
+    else { pa = s; pb = o; d = (nr - 1 - o) + (ss - s - 1); }             // LEFT (o; s->ss): produced by cell (s, o)
+    if (!sl.alive[pa * nr + pb]) return kInfBits;
+    const DirEnt de = sl.dir[dir_base(pa, pb, nl, nr) + d];
+    if (de.len == 0 || k < de.kmin || k > de.kmax) return kInfBits;
+    uint32_t lo = 0, hi = de.len;
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (sl.kpool[de.off + mid] < k) lo = mid + 1; else hi = mid; }
+    if (lo >= de.len || sl.kpool[de.off + lo] != k) return kInfBits;
+    return area_bits(sl.vpool[de.off + lo]);
+}
+
 // Re-derives the chain of states behind the best terminal state of layer kopt and emits the hull in the
 // reference's order (locReconstructHull, AntipodalOptimized.cpp:335-436): [t, left chain backwards.., s, right chain backwards..].
-__global__ void __launch_bounds__(kAdThreads)
+// Runs after k_ad_cells processed the winning candidate alone in slice 0.
+__global__ void __launch_bounds__(kCellThreads)
 k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T, PairRec pr,
-               unsigned char* __restrict__ arena, size_t slice_bytes, unsigned long long max_cells, unsigned long long max_S,
-               uint32_t max_layers, uint32_t kopt, uint32_t nlayers_ref,
+               unsigned char* arena, CellLayout Lo, uint32_t kopt,
                int32_t* __restrict__ left, int32_t* __restrict__ right, int32_t* __restrict__ hull, AdHull* __restrict__ out)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
     LuneSmem S = carve_smem(smem_raw, pr.nl, pr.nr);
     build_lune(x, y, n, pr, S, s_cnt);
-    if (threadIdx.x != 0) return;
-    const Slice sl = carve_slice(arena, slice_bytes, 0, max_cells, max_S, max_layers);
+    const CellSlice sl = carve_cells(arena, Lo, 0);
     const uint32_t nl = pr.nl, nr = pr.nr;
-    const uint32_t SR = nl * nr * nr, SL = nr * nl * nl, SS = SR + SL;
+    // best terminal state of layer kopt (:348-355): smallest area, first in (side, o, s) order; all threads scan
+    __shared__ unsigned long long s_v[kCellThreads];
+    __shared__ uint32_t s_i[kCellThreads];
+    {
+        unsigned long long bvv = kInfBits; uint32_t bi = 0xffffffffu;
+        const uint32_t nR = nl * (nr - 1), nLs = nr * (nl - 1);
+        for (uint32_t t = threadIdx.x; t < nR + nLs; t += blockDim.x)
+        {
+            const bool rt = t < nR;
+            const uint32_t u = rt ? t : t - nR;
+            const uint32_t o = rt ? u / (nr - 1) : u / (nl - 1), s = rt ? u % (nr - 1) : u % (nl - 1);
+            const unsigned long long v = state_value(sl, nl, nr, rt, o, s, rt ? nr - 1 : nl - 1, kopt);
+            if (v < bvv || (v == bvv && t < bi)) { bvv = v; bi = t; }
+        }
+        s_v[threadIdx.x] = bvv; s_i[threadIdx.x] = bi;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
     const double Sx = S.Lx[0], Sy = S.Ly[0], Ex = S.Lx[nl - 1], Ey = S.Ly[nl - 1];
     const int Sp = S.Lidx[0], Ep = S.Lidx[nl - 1];
     const double seg2 = dist2(Sx, Sy, Ex, Ey);
-    (void) nlayers_ref;
-    // best terminal state of layer kopt (:348-355)
     bool e_right = true; uint32_t eo = 0, es = 0, ess = 0; unsigned long long ev = kInfBits;
     {
-        const unsigned long long* lv = sl.vals + (size_t) kopt * SS;
-        for (uint32_t o = 0; o < nl; ++o) for (uint32_t s = 0; s + 1 < nr; ++s)
+        uint32_t bi = 0xffffffffu;
+        for (uint32_t t = 0; t < blockDim.x; ++t) if (s_v[t] < ev || (s_v[t] == ev && s_i[t] < bi)) { ev = s_v[t]; bi = s_i[t]; }
+        if (ev != kInfBits)
         {
-            const unsigned long long v = lv[(o * nr + s) * nr + (nr - 1)];
-            if (v < ev) { ev = v; e_right = true; eo = o; es = s; ess = nr - 1; }
-        }
-        for (uint32_t o = 0; o < nr; ++o) for (uint32_t s = 0; s + 1 < nl; ++s)
-        {
-            const unsigned long long v = lv[SR + (o * nl + s) * nl + (nl - 1)];
-            if (v < ev) { ev = v; e_right = false; eo = o; es = s; ess = nl - 1; }
+            const uint32_t nR = nl * (nr - 1);
+            e_right = bi < nR;
+            const uint32_t u = e_right ? bi : bi - nR;
+            eo = e_right ? u / (nr - 1) : u / (nl - 1); es = e_right ? u % (nr - 1) : u % (nl - 1); ess = e_right ? nr - 1 : nl - 1;
         }
     }
     uint32_t a = 0, b = 0, ok = ev != kInfBits ? 1u : 0u;
@@ -466,10 +716,8 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
         const double* ownx = rt ? S.Rx : S.Lx; const double* owny = rt ? S.Ry : S.Ly;
         const double* othx = rt ? S.Lx : S.Rx; const double* othy = rt ? S.Ly : S.Ry;
         const int32_t* owni = rt ? S.Ridx : S.Lidx; const int32_t* othi = rt ? S.Lidx : S.Ridx;
-        const uint32_t nown = rt ? nr : nl, noth = rt ? nl : nr;
         const double ax = rt ? Sx : Ex, ay = rt ? Sy : Ey; const int ap = rt ? Sp : Ep;        // own fan apex
         const double bx = rt ? Ex : Sx, by = rt ? Ey : Sy; const int bp = rt ? Ep : Sp;        // other fan apex
-        const uint32_t own_base = rt ? 0u : SR, oth_base = rt ? SR : 0u;
         int32_t* own_out = rt ? right : left; uint32_t& own_cnt = rt ? b : a;
         int32_t* oth_out = rt ? left : right; uint32_t& oth_cnt = rt ? a : b;
         const uint32_t o = eo, s = es, ss = ess;
@@ -487,7 +735,7 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
                     if (c > k) continue;
                     const uint32_t ks = k - c;
                     if ((z == 1) != (ks == 0)) continue;
-                    const unsigned long long sv = sl.vals[(size_t) ks * SS + own_base + (o * nown + p) * nown + s];
+                    const unsigned long long sv = state_value(sl, nl, nr, rt, o, p, s, ks);
                     if (sv == kInfBits) continue;
                     if (area_bits(__dadd_rn(bits_area(sv), tri)) != ev) continue;
                     found = true; via_switch = false; prev = p; cused = c; pv = sv;
@@ -510,7 +758,7 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
                     if (c > k) continue;
                     const uint32_t ks = k - c;
                     if ((z == 1) != (ks == 0)) continue;
-                    const unsigned long long sv = sl.vals[(size_t) ks * SS + oth_base + (s * noth + p) * noth + o];
+                    const unsigned long long sv = state_value(sl, nl, nr, !rt, s, p, o, ks);
                     if (sv == kInfBits) continue;
                     if (area_bits(__dadd_rn(bits_area(sv), tri)) != ev) continue;
                     found = true; via_switch = true; prev = p; cused = c; pv = sv;
@@ -533,7 +781,6 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
     for (uint32_t t = 0; t < b; ++t) hull[a + t] = right[t];
     out->len = a + b; out->ok = ok; out->nl = nl; out->nr = nr;
 }
-
 // Test hook: the two lune lists of a candidate pair.
 __global__ void __launch_bounds__(kAdThreads)
 k_ad_lune_lists(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, uint32_t s, uint32_t t,
@@ -566,44 +813,87 @@ k_ad_lune_lists(const double* __restrict__ x, const double* __restrict__ y, uint
 
 namespace
 {
-struct AdSmall { PairStats stats; AdCounters counters; CtaBest best; AdHull hull; uint32_t lune_cnt[2]; };
+struct AdSmall { PairStats stats; AdCounters counters; CtaBest best; AdHull hull; uint32_t lune_cnt[2]; unsigned int ovf_count[2]; };
 
-// Makes sure the arena holds `want_slices` clean slices able to take (V cells, L layers, Q queue entries).
-int ad_prepare_arena(Ctx* c, unsigned long long V, uint32_t L, unsigned long long Q, uint32_t want_slices, uint32_t* got_slices)
+constexpr uint64_t kMinPoolRecords = 1u << 16;        // smallest record pool a slice may have
+constexpr uint64_t kDefaultPoolRecords = 24u << 20;   // first-try pool per slice (overflowing candidates are re-run larger)
+
+// Launches the cell kernel over `count` queue entries (order == nullptr: pairs[0..count)) with `slices` CTAs.
+int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uint32_t count, uint32_t slices, const CellLayout& Lo,
+                    uint32_t capL, uint32_t capR, uint64_t kmax, uint32_t nlayers_ref, double amax, AdSmall* sm,
+                    CtaBest* d_cta_best, uint32_t* d_ovf_list, unsigned int* d_ovf_count)
 {
-    const unsigned long long nV = std::max<unsigned long long>(V, c->ad_V), nQ = std::max<unsigned long long>(Q, c->ad_Q);
-    const uint32_t nL = std::max<uint32_t>(L, c->ad_L);
-    const size_t sb = slice_bytes_for(nV, nQ, nL);
-    uint64_t max_slices = workspace_budget(c, c->arena) / sb;
-    if (max_slices == 0) { c->err = "area+diameter path: one candidate's layer tables exceed the memory budget"; return ADK_ERR_NOMEM; }
-    uint32_t slices = (uint32_t) std::min<uint64_t>(want_slices, max_slices);
-    const bool same_layout = nV == c->ad_V && nQ == c->ad_Q && nL == c->ad_L && c->ad_slice_bytes == sb;
-    if (same_layout && slices <= c->ad_slices) { *got_slices = slices; return ADK_OK; }
-    if (same_layout) slices = std::max<uint32_t>(slices, c->ad_slices);
-    ADK_TRY(ensure(c, c->arena, sb * (size_t) slices));
-    const size_t words = (size_t) (nV / 32) + nL + 1;
-    dim3 grid((unsigned) std::min<size_t>((size_t) ((nV + 255) / 256), 1024), std::min<uint32_t>(slices, 65535));
-    k_ad_init_arena<<<grid, 256, 0, c->stream>>>(c->arena.as<unsigned char>(), sb, slices, nV, words);
+    const size_t smem = cells_smem_bytes(capL, capR);
+    if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
+    ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    ADK_CUDA(c, cudaMemsetAsync(&sm->counters.queue, 0, sizeof(unsigned int), c->stream));
+    ADK_CUDA(c, cudaMemsetAsync(d_ovf_count, 0, sizeof(unsigned int), c->stream));
+    Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
+    k_ad_cells<<<slices, kCellThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
+                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, capL, capR, kmax, nlayers_ref,
+                                                          amax, d_cta_best, d_ovf_list, d_ovf_count);
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());
-    c->ad_V = nV; c->ad_Q = nQ; c->ad_L = nL; c->ad_slice_bytes = sb; c->ad_slices = slices;
-    *got_slices = std::min<uint32_t>(want_slices, slices);
     return ADK_OK;
 }
 
-template <bool KEEP>
-int ad_launch_dp(Ctx* c, const PairRec* d_pairs, uint32_t npairs, uint32_t grid, uint32_t capL, uint32_t capR, uint32_t layers,
-                 uint64_t kmax, uint32_t nlayers_ref, double amax, AdCounters* d_counters, CtaBest* d_cta_best)
+// Resident CTAs of k_ad_cells per SM for the given lune capacity.
+int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, int* per_sm)
 {
-    const size_t smem = lune_smem_bytes(capL, capR, layers);
+    const size_t smem = cells_smem_bytes(capL, capR);
     if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
-    ADK_CUDA(c, cudaFuncSetAttribute(k_ad_dp<KEEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
-    k_ad_dp<KEEP><<<grid, kAdThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, npairs, d_counters,
-                                                         c->arena.as<unsigned char>(), c->ad_slice_bytes, c->ad_V, c->ad_Q, c->ad_L,
-                                                         capL, capR, kmax, nlayers_ref, amax, d_cta_best);
-    ++c->launches;
-    ADK_CUDA(c, cudaGetLastError());
+    ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    int occ = 0;
+    ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells, kCellThreads, smem));
+    *per_sm = occ > 0 ? occ : 1;
+    return ADK_OK;
+}
+
+// Runs every queued candidate; candidates whose record pool overflowed are re-run in fewer, larger slices.
+int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairStats& ps, uint64_t kmax, uint32_t nlayers_ref, double amax,
+                 AdSmall* sm, CellLayout* used_layout)
+{
+    const uint32_t max_src = ps.max_nl + ps.max_nr;
+    if (ps.max_dirs >= 0xffffffffull) { c->err = "area+diameter path: candidate too large for 32-bit directory offsets"; return ADK_ERR_NOMEM; }
+    const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, max_src, 0).off_v + 8192;
+    int occ = 1;
+    ADK_TRY(ad_cells_occupancy(c, ps.max_nl, ps.max_nr, &occ));
+    ADK_TRY(ensure(c, c->scratch2, sizeof(uint32_t) * 2 * (size_t) nqueued + 64));
+    uint32_t* d_ovf[2] = {c->scratch2.as<uint32_t>(), c->scratch2.as<uint32_t>() + nqueued};
+    const uint32_t* d_order = nullptr;
+    uint32_t count = nqueued;
+    uint64_t pool = kDefaultPoolRecords, prev_cap = 0;
+    int merge = 0;
+    for (int round = 0; count > 0; ++round)
+    {
+        const uint64_t budget = workspace_budget(c, c->arena);
+        const uint64_t min_bytes = fixed + 10 * kMinPoolRecords, want_bytes = fixed + 10 * pool;
+        if (budget < min_bytes) { c->err = "area+diameter path: one candidate's workspace exceeds the memory budget"; return ADK_ERR_NOMEM; }
+        uint64_t slices = std::min<uint64_t>(count, (uint64_t) c->sm_count * (uint64_t) occ);
+        if (round > 0) slices = std::min<uint64_t>(slices, std::max<uint64_t>(1, budget / want_bytes));   // fewer, larger slices
+        slices = std::max<uint64_t>(1, std::min<uint64_t>(slices, budget / min_bytes));
+        size_t slice_bytes = (size_t) std::min<uint64_t>(budget / slices, want_bytes) & ~(size_t) 255;
+        const CellLayout Lo = cell_layout(ps.max_cells, ps.max_dirs, max_src, slice_bytes);
+        if (round > 0 && Lo.cap <= prev_cap)
+        {   // the overflowing candidate already had everything the budget allows
+            c->err = "area+diameter path: one candidate's record pool exceeds the memory budget"; return ADK_ERR_NOMEM;
+        }
+        ADK_TRY(ensure(c, c->arena, slice_bytes * (size_t) slices));
+        ADK_TRY(ensure(c, c->scratch1, sizeof(CtaBest) * slices));
+        ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
+                                c->scratch1.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1]));
+        k_ad_reduce<<<1, 32, 0, c->stream>>>(c->scratch1.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+        merge = 1;
+        unsigned int novf = 0;
+        ADK_CUDA(c, cudaMemcpyAsync(&novf, &sm->ovf_count[round & 1], sizeof(novf), cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (used_layout) *used_layout = Lo;
+        if (novf == 0) break;
+        d_order = d_ovf[round & 1]; count = novf;
+        prev_cap = Lo.cap; pool = (uint64_t) Lo.cap * 8;
+    }
     return ADK_OK;
 }
 }  // namespace
@@ -635,16 +925,9 @@ int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, 
     AdCounters hc; std::memset(&hc, 0, sizeof(hc));
     if (ps.nqueued > 0)
     {
-        uint32_t grid = 0;
-        ADK_TRY(ad_prepare_arena(c, ps.max_cells, ps.max_lim + 1, ps.max_S, std::min<uint32_t>(ps.nqueued, (uint32_t) c->sm_count * 4), &grid));
-        ADK_TRY(ensure(c, c->scratch1, sizeof(CtaBest) * grid));
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
-        ADK_TRY(ad_launch_dp<false>(c, c->scratch0.as<PairRec>(), ps.nqueued, grid, ps.max_nl, ps.max_nr, ps.max_lim + 1, kmax,
-                                    nlayers_ref, amax, &sm->counters, c->scratch1.as<CtaBest>()));
+        ADK_TRY(ad_run_queue(c, c->scratch0.as<PairRec>(), ps.nqueued, ps, kmax, nlayers_ref, amax, sm, nullptr));
         ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
-        k_ad_reduce<<<1, 32, 0, c->stream>>>(c->scratch1.as<CtaBest>(), grid, &sm->best);
-        ++c->launches;
-        ADK_CUDA(c, cudaGetLastError());
         ADK_CUDA(c, cudaMemcpyAsync(&hb, &sm->best, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
         ADK_CUDA(c, cudaMemcpyAsync(&hc, &sm->counters, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
     }
@@ -679,7 +962,7 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
     ADK_TRY(run_count_tables(c));
     ADK_TRY(ensure(c, c->small, sizeof(AdSmall)));
     AdSmall* sm = c->small.as<AdSmall>();
-    // the winning candidate alone: size it, re-run it keeping the tables (:529-535), walk back, clean up
+    // the winning candidate alone: size it, re-run it in slice 0 (:529-535), walk back over its records
     ADK_TRY(ensure(c, c->scratch6, sizeof(int32_t) * 3 * ((size_t) n + 4) + sizeof(PairRec) + 64));
     int32_t* d_left = c->scratch6.as<int32_t>();
     int32_t* d_right = d_left + (n + 4);
@@ -699,23 +982,18 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
     const uint32_t lim = (uint32_t) std::min<uint64_t>(kmax - 2, inner);
     const uint32_t kopt = best->count - 2;
     if (kopt > lim) { c->err = "ad_finish: witness count exceeds the candidate's capacity"; return ADK_ERR_ARG; }
-    const unsigned long long S = (unsigned long long) pr.nl * pr.nr * pr.nr + (unsigned long long) pr.nr * pr.nl * pr.nl;
-    uint32_t grid = 0;
-    ADK_TRY(ad_prepare_arena(c, S * (lim + 1), lim + 1, S, 1, &grid));
+    PairStats ps; std::memset(&ps, 0, sizeof(ps));
+    ps.nqueued = 1; ps.max_nl = pr.nl; ps.max_nr = pr.nr; ps.max_lim = lim;
+    ps.max_cells = (unsigned long long) pr.nl * pr.nr; ps.max_dirs = ps.max_cells * (pr.nl + pr.nr - 2) / 2;
     ADK_CUDA(c, cudaMemcpyAsync(d_pair, &pr, sizeof(pr), cudaMemcpyHostToDevice, c->stream));
     ADK_CUDA(c, cudaMemsetAsync(&sm->counters, 0, sizeof(AdCounters), c->stream));
-    ADK_TRY(ensure(c, c->scratch1, sizeof(CtaBest) * 4));
-    ADK_TRY(ad_launch_dp<true>(c, d_pair, 1, 1, pr.nl, pr.nr, lim + 1, kmax, nlayers_ref, amax, &sm->counters, c->scratch1.as<CtaBest>()));
+    CellLayout Lo;
+    ADK_TRY(ad_run_queue(c, d_pair, 1, ps, kmax, nlayers_ref, amax, sm, &Lo));
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), n};
     const size_t smem = lune_smem_bytes(pr.nl, pr.nr, 1);
     ADK_CUDA(c, cudaFuncSetAttribute(k_ad_backtrack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    k_ad_backtrack<<<1, kAdThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, T, pr, c->arena.as<unsigned char>(),
-                                                       c->ad_slice_bytes, c->ad_V, c->ad_Q, c->ad_L, kopt, nlayers_ref,
-                                                       d_left, d_right, d_hull, &sm->hull);
-    ++c->launches;
-    ADK_CUDA(c, cudaGetLastError());
-    k_ad_clean<<<(unsigned) std::min<size_t>(((size_t) ((S + 31) / 32) * (lim + 1) + 255) / 256, 2048), 256, 0, c->stream>>>(
-        c->arena.as<unsigned char>(), c->ad_slice_bytes, c->ad_V, c->ad_Q, c->ad_L, (uint32_t) S, lim);
+    k_ad_backtrack<<<1, kCellThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, T, pr, c->arena.as<unsigned char>(), Lo, kopt,
+                                                         d_left, d_right, d_hull, &sm->hull);
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());
     AdHull hh;
@@ -729,7 +1007,6 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
     for (uint32_t t = 0; t < hh.len && t < n; ++t) hull[t] = (uint32_t) hp[t];
     return ADK_OK;
 }
-
 int ad_lune_lists(Ctx* c, uint32_t s, uint32_t t, int32_t* h_left, uint32_t* nl, int32_t* h_right, uint32_t* nr)
 {
     const uint32_t n = c->n;
