@@ -203,24 +203,25 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 constexpr int kCellWarps = 4;                    // warps per CTA (one candidate per CTA)
 constexpr int kCellThreads = kCellWarps * 32;
 constexpr int kBT = 32;                          // layers per accumulator tile
-constexpr int kSrcCap = 64;                      // source edges of a cell kept in shared memory (more spill to global)
+constexpr int kSrcCap = 64;                      // source edges of a cell kept in shared memory (larger cells use the global spill)
 
-struct DirEnt { uint32_t off, len, kmin, kmax; };                 // records [off, off+len) of one (cell, destination), k ascending
-struct SrcRec { double tri, refd; uint32_t off; uint16_t len, sidx; uint16_t c, cx; uint32_t pad; };   // sidx bit 15: LEFT
-static_assert(sizeof(SrcRec) == 32, "SrcRec layout");
+// Layer vector of one (cell, destination): areas of layers kmin .. kmin+len-1 at vpool[off ..], +inf where unreached.
+struct DirEnt { uint32_t off; uint16_t kmin, len; };
+struct SrcRec { double tri, refd; uint32_t off; uint16_t len, sidx; uint16_t c, cx; uint16_t kmin, pad; };   // sidx bit 15: LEFT
+static_assert(sizeof(SrcRec) == 32 && sizeof(DirEnt) == 8, "record layouts");
 
 // Per-CTA slice of the arena.
 struct CellSlice
 {
     unsigned char* alive;     // nl*nr flags: cell wrote its directory
     DirEnt* dir;              // directory entries at fixed positions (dir_base)
-    double* vpool;            // record areas
-    uint16_t* kpool;          // record layers
+    uint16_t* nfin;           // per directory entry: number of finite layers (for the cell-update counter)
+    double* vpool;            // layer vectors
     SrcRec* spill;            // kCellWarps * spill_cap source records
     uint32_t* spill_pred;     // kCellWarps * spill_cap predicate words
 };
 
-struct CellLayout { size_t off_dir, off_v, off_k, off_spill, off_pred, bytes; uint32_t cap, spill_cap; };
+struct CellLayout { size_t off_dir, off_nfin, off_v, off_spill, off_pred, bytes; uint32_t cap, spill_cap; };
 
 __host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, uint32_t max_src, size_t slice_bytes)
 {
@@ -229,13 +230,13 @@ __host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, 
     Lo.spill_cap = max_src;
     size_t o = up((size_t) max_cells);
     Lo.off_dir = o; o = up(o + sizeof(DirEnt) * (size_t) max_dirs);
+    Lo.off_nfin = o; o = up(o + sizeof(uint16_t) * (size_t) max_dirs);
     Lo.off_spill = o; o = up(o + sizeof(SrcRec) * (size_t) kCellWarps * max_src);
     Lo.off_pred = o; o = up(o + sizeof(uint32_t) * (size_t) kCellWarps * max_src);
     Lo.off_v = o;
     const size_t rest = slice_bytes > o + 4096 ? slice_bytes - o - 4096 : 0;
-    const size_t cap = rest / 10;                                   // 8 B area + 2 B layer per record
+    const size_t cap = rest / sizeof(double);
     Lo.cap = (uint32_t) (cap > 0xfffffff0ull ? 0xfffffff0ull : cap) & ~31u;
-    Lo.off_k = up(o + sizeof(double) * (size_t) Lo.cap);
     Lo.bytes = slice_bytes;
     return Lo;
 }
@@ -246,8 +247,8 @@ __device__ __forceinline__ CellSlice carve_cells(unsigned char* arena, const Cel
     CellSlice s;
     s.alive = base;
     s.dir = reinterpret_cast<DirEnt*>(base + Lo.off_dir);
+    s.nfin = reinterpret_cast<uint16_t*>(base + Lo.off_nfin);
     s.vpool = reinterpret_cast<double*>(base + Lo.off_v);
-    s.kpool = reinterpret_cast<uint16_t*>(base + Lo.off_k);
     s.spill = reinterpret_cast<SrcRec*>(base + Lo.off_spill);
     s.spill_pred = reinterpret_cast<uint32_t*>(base + Lo.off_pred);
     return s;
@@ -273,51 +274,60 @@ struct CellCtx
     double* acc;            // kBT * 32
     SrcRec* src;            // kSrcCap
     uint32_t* pred;         // kSrcCap
-    SrcRec* spill;          // this warp's spill region
+    SrcRec* spill;          // this warp's spill region (global)
     uint32_t* spill_pred;
     // CTA-shared
-    unsigned int* bump;     // records allocated so far
+    volatile uint32_t* rowdone;   // rowdone[a] = cells of row a finished (they finish in b order)
+    volatile uint32_t* coldone;   // coldone[b] = cells of column b finished (in a order)
+    unsigned int* next;     // next cell of the diagonal-major order to hand out
+    unsigned int* bump;     // pool entries allocated so far
     unsigned int* overflow;
 };
-
-__device__ __forceinline__ SrcRec& src_at(const CellCtx& C, uint32_t i) { return i < (uint32_t) kSrcCap ? C.src[i] : C.spill[i - kSrcCap]; }
-__device__ __forceinline__ uint32_t& pred_at(const CellCtx& C, uint32_t i) { return i < (uint32_t) kSrcCap ? C.pred[i] : C.spill_pred[i - kSrcCap]; }
 
 constexpr unsigned kFull = 0xffffffffu;
 
 // Accumulates, for the 32 destinations of one tile, the layer rows [k0, k0 + rows) of acc (all +inf on entry):
 // acc[row][lane] = min over sources with a set predicate bit of (area + triangle), at layer k + c (:188-195, :207-217).
-__device__ __forceinline__ void cell_accumulate(const CellCtx& C, uint32_t P, uint32_t lane, uint32_t k0, uint32_t rows)
+__device__ __forceinline__ void cell_accumulate(const CellCtx& C, const SrcRec* __restrict__ srcs, const uint32_t* __restrict__ preds,
+                                                uint32_t P, uint32_t lane, uint32_t k0, uint32_t rows)
 {
+    const uint32_t dmax = min(C.lim, C.nlayers - 1);          // :192-195; layers beyond lim are never read
+    const uint32_t khi = min(k0 + rows - 1, dmax);
+    double* col = C.acc + lane;
     for (uint32_t p = 0; p < P; ++p)
     {
-        const uint32_t m = pred_at(C, p);
+        const uint32_t m = preds[p];
         if (!m) continue;
         const bool mine = (m >> lane) & 1u;
-        const SrcRec& r = src_at(C, p);
-        const uint32_t off = r.off, len = r.len, c = r.c, cx = r.cx;
+        const SrcRec r = srcs[p];
         const double tri = r.tri;
-        bool done = false;
-        for (uint32_t e0 = 0; e0 < len && !done; e0 += 32)
+        if (r.kmin == 0)
+        {   // a layer-0 seed (:149-160): one record, and the count carries the extra collinear term
+            const uint32_t dst = (uint32_t) r.c + r.cx;
+            if (dst < k0 || dst > khi) continue;
+            const double v2 = __dadd_rn(C.sl.vpool[r.off], tri);
+            if (mine && v2 <= C.amax) { double* q = col + (dst - k0) * 32; if (v2 < *q) *q = v2; }
+            continue;
+        }
+        // entries e (layer kmin + e) land on row kmin + e + c - k0
+        const int shift = (int) r.kmin + (int) r.c - (int) k0;
+        const int elo = max(0, -shift), ehi = min((int) r.len, (int) khi - (int) k0 + 1 - shift);
+        for (int e0 = elo; e0 < ehi; e0 += 32)
         {
-            const uint32_t e = e0 + lane;
-            uint32_t kk = 0; double vv = 0.0;
-            if (e < len) { kk = C.sl.kpool[off + e]; vv = C.sl.vpool[off + e]; }
-            const uint32_t ne = min(32u, len - e0);
-            for (uint32_t t = 0; t < ne; ++t)
+            const int e = e0 + (int) lane;
+            double v2 = INFINITY;
+            if (e < ehi)
             {
-                const uint32_t k = __shfl_sync(kFull, kk, t);
-                const double v = __shfl_sync(kFull, vv, t);
-                const uint32_t dst = k + c + (k == 0 ? cx : 0u);          // layer 0 carries the extra collinear term (:25-28 of the count)
-                if (dst >= C.nlayers || dst > C.lim || dst < k0) continue; // :192-195; layers beyond lim are never read
-                if (dst >= k0 + rows) { if (k > 0) { done = true; break; } continue; }   // records are k-ascending
-                const double v2 = __dadd_rn(v, tri);
-                if (!(v2 <= C.amax)) continue;                             // :203, :229, :276, :302
-                if (mine)
-                {
-                    double* q = C.acc + (dst - k0) * 32 + lane;
-                    if (v2 < *q) *q = v2;
-                }
+                v2 = __dadd_rn(C.sl.vpool[r.off + e], tri);
+                if (!(v2 <= C.amax)) v2 = INFINITY;                // :203, :229, :276, :302
+            }
+            const int ne = min(32, ehi - e0);
+            double* q = col + (e0 + shift) * 32;
+#pragma unroll 4
+            for (int t = 0; t < ne; ++t)
+            {
+                const double xv = __shfl_sync(kFull, v2, t);
+                if (mine && xv < q[t * 32]) q[t * 32] = xv;
             }
         }
     }
@@ -335,6 +345,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     const bool dead = dist2(Lax, Lay, Rbx, Rby) > C.seg2;                // :183-186 / :256-259
     const uint32_t nDR = nr - 1 - b, nDL = nl - 1 - a, D = nDR + nDL;
     const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t dmax = min(C.lim, C.nlayers - 1);
 
     // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b)
     uint32_t P = 0, klo = 0xffffffffu, khi = 0;
@@ -343,30 +354,31 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     {
         const uint32_t u = u0 + lane;
         bool live = false, left = false;
-        uint32_t s = 0;
-        DirEnt de; de.off = 0; de.len = 0; de.kmin = 0; de.kmax = 0;
+        uint32_t s = 0, dix = 0;
+        DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
         if (u < npot)
         {
             left = u >= b; s = left ? u - b : u;
             const uint32_t pa = left ? s : a, pb = left ? b : s;
             if (C.sl.alive[pa * nr + pb])
             {
-                const uint32_t d = left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1);
-                de = C.sl.dir[dir_base(pa, pb, nl, nr) + d];
+                dix = dir_base(pa, pb, nl, nr) + (left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1));
+                de = C.sl.dir[dix];
                 live = de.len > 0;
             }
         }
+        const uint32_t kmax = (uint32_t) de.kmin + de.len - 1;
         if (live && (left ? term_l : term_r))
         {   // terminal states only report (:167-175): the deepest layer of this edge is its best
-            if (de.kmax > 0)
+            if (kmax > 0)
             {
                 const double v = C.sl.vpool[de.off + de.len - 1];
-                if (de.kmax > bk || (de.kmax == bk && v < bv)) { bk = de.kmax; bv = v; }
+                if (kmax > bk || (kmax == bk && v < bv)) { bk = kmax; bv = v; }
             }
             live = false;
         }
         if (dead) live = false;
-        SrcRec r; r.tri = 0.0; r.refd = 0.0; r.off = de.off; r.len = (uint16_t) de.len; r.sidx = 0; r.c = 0; r.cx = 0; r.pad = 0;
+        SrcRec r; r.tri = 0.0; r.refd = 0.0; r.off = de.off; r.len = de.len; r.kmin = de.kmin; r.sidx = 0; r.c = 0; r.cx = 0; r.pad = 0;
         if (live)
         {
             const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
@@ -383,24 +395,34 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
             r.refd = pseudo_dist(psx, psy, hx, hy, ox, oy);                      // :222 / :295
             r.sidx = (uint16_t) (s | (left ? 0x8000u : 0u));
             // cell updates the reference performs for these states (:198,225,271,298), and the output layer range
-            uint32_t nvalid = de.len;
-            if (de.kmax + c + cx >= C.nlayers)
+            const uint32_t ceff = c + (de.kmin == 0 ? cx : 0u);                  // only the seeds sit on layer 0
+            uint32_t nvalid = C.sl.nfin[dix];
+            if (kmax + ceff >= C.nlayers)
             {
                 nvalid = 0;
-                for (uint32_t e = 0; e < de.len; ++e) { const uint32_t k = C.sl.kpool[de.off + e]; nvalid += (k + c + (k == 0 ? cx : 0u) < C.nlayers) ? 1u : 0u; }
+                for (uint32_t e = 0; e < de.len; ++e)
+                    nvalid += (C.sl.vpool[de.off + e] < INFINITY && de.kmin + e + ceff < C.nlayers) ? 1u : 0u;
             }
             my_cells += (unsigned long long) nvalid * D;
-            const uint32_t lo = de.kmin + c, hi = min(min(de.kmax + c + cx, C.lim), C.nlayers - 1);
+            const uint32_t lo = de.kmin + ceff, hi = min(kmax + ceff, dmax);
             if (nvalid == 0 || lo > hi || !(r.tri <= C.amax)) live = false;
             else { klo = min(klo, lo); khi = max(khi, hi); }
         }
         const uint32_t lm = __ballot_sync(kFull, live);
-        if (live) src_at(C, P + __popc(lm & lt)) = r;
+        if (live)
+        {
+            const uint32_t at = P + __popc(lm & lt);
+            if (at < (uint32_t) kSrcCap) C.src[at] = r; else C.spill[at] = r;
+        }
         P += __popc(lm);
     }
     if (P == 0 || D == 0) return;
     klo = __reduce_min_sync(kFull, klo); khi = __reduce_max_sync(kFull, khi);
     __syncwarp();
+    const bool spilled = P > (uint32_t) kSrcCap;       // rare: the whole source list then lives in the global spill
+    if (spilled) { for (uint32_t t = lane; t < (uint32_t) kSrcCap; t += 32) C.spill[t] = C.src[t]; __syncwarp(); }
+    const SrcRec* srcs = spilled ? C.spill : C.src;
+    uint32_t* preds = spilled ? C.spill_pred : C.pred;
     const uint32_t ntiles = (khi - klo + kBT) / kBT;
     const uint32_t dirb = dir_base(a, b, nl, nr);
 
@@ -429,8 +451,8 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
         uint32_t anyp = 0;
         for (uint32_t p = 0; p < P; ++p)
         {
-            const SrcRec& r = src_at(C, p);
-            const uint32_t sx = r.sidx;
+            const uint32_t sx = srcs[p].sidx;
+            const double refd = srcs[p].refd;
             const bool left = (sx & 0x8000u) != 0;
             const uint32_t s = sx & 0x7fffu;
             const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
@@ -439,14 +461,15 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
             if (have && (left ? okL : okR))
             {
                 if (left != dR) ok = orientation(qx, qy, hx, hy, psx, psy) >= 0;     // stay on the edge's chain (:201, :274)
-                else ok = pseudo_dist(psx, psy, hx, hy, qx, qy) <= r.refd;           // switch chains (:226-227, :299-300)
+                else ok = pseudo_dist(psx, psy, hx, hy, qx, qy) <= refd;             // switch chains (:226-227, :299-300)
             }
             const uint32_t m = __ballot_sync(kFull, ok);
-            if (lane == 0) pred_at(C, p) = m;
+            if (lane == 0) preds[p] = m;
             anyp |= m;
         }
         __syncwarp();
-        uint32_t cnt = 0, run = 0, kfirst = 0, klast = 0, lane_off = 0, base = 0;
+        // the destination's layer vector: first .. last finite layer, holes stay +inf
+        uint32_t first = 0xffffffffu, last = 0, nfin = 0, lane_off = 0, base = 0;
         bool fits = true;
         if (anyp)
         {
@@ -456,12 +479,14 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                 for (uint32_t t = 0; t < ntiles; ++t)
                 {
                     const uint32_t k0 = klo + t * kBT, rows = min((uint32_t) kBT, khi + 1 - k0);
-                    cell_accumulate(C, P, lane, k0, rows);
+                    cell_accumulate(C, srcs, preds, P, lane, k0, rows);
                     if (counting)
                     {
-                        for (uint32_t rr = 0; rr < rows; ++rr) cnt += C.acc[rr * 32 + lane] < INFINITY ? 1u : 0u;
+                        for (uint32_t rr = 0; rr < rows; ++rr)
+                            if (C.acc[rr * 32 + lane] < INFINITY) { first = min(first, k0 + rr); last = k0 + rr; ++nfin; }
                         if (t == ntiles - 1)
-                        {   // allocate this tile's records: exclusive scan over the lanes, one bump of the CTA's pool
+                        {   // allocate this tile's vectors: exclusive scan over the lanes, one bump of the CTA's pool
+                            const uint32_t cnt = nfin ? last - first + 1 : 0u;
                             uint32_t incl = cnt;
                             for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, o); if ((int) lane >= o) incl += v; }
                             lane_off = incl - cnt;
@@ -470,21 +495,13 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                             base = __shfl_sync(kFull, base, 0);
                             fits = (unsigned long long) base + total <= C.cap;
                             if (!fits && lane == 0) *C.overflow = 1u;
-                            if (fits && lane == 0) my_states += total;
+                            my_states += fits ? nfin : 0u;
                         }
                     }
-                    if (emitting)
+                    if (emitting && fits && nfin)
                     {
-                        for (uint32_t rr = 0; rr < rows; ++rr)
-                        {
-                            const double v = C.acc[rr * 32 + lane];
-                            if (v < INFINITY)
-                            {
-                                if (fits) { const uint32_t at = base + lane_off + run; C.sl.vpool[at] = v; C.sl.kpool[at] = (uint16_t) (k0 + rr); }
-                                if (run == 0) kfirst = k0 + rr;
-                                klast = k0 + rr; ++run;
-                            }
-                        }
+                        const uint32_t r0 = max(first, k0), r1 = min(last, k0 + rows - 1);
+                        for (uint32_t k = r0; k <= r1 && r0 <= r1; ++k) C.sl.vpool[base + lane_off + (k - first)] = C.acc[(k - k0) * 32 + lane];
                     }
                     for (uint32_t rr = 0; rr < rows; ++rr) C.acc[rr * 32 + lane] = INFINITY;
                 }
@@ -492,8 +509,9 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
         }
         if (have)
         {
-            DirEnt de; de.off = base + lane_off; de.len = fits ? run : 0u; de.kmin = kfirst; de.kmax = klast;
+            DirEnt de; de.off = base + lane_off; de.kmin = (uint16_t) (nfin ? first : 0u); de.len = (uint16_t) ((fits && nfin) ? last - first + 1 : 0u);
             C.sl.dir[dirb + d] = de;
+            C.sl.nfin[dirb + d] = (uint16_t) nfin;
         }
     }
     __syncwarp();
@@ -503,12 +521,15 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
 struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best terminal layer (0 = none) of one candidate
 
 __host__ __device__ inline size_t cells_warp_smem() { return sizeof(double) * kBT * 32 + sizeof(SrcRec) * kSrcCap + sizeof(uint32_t) * kSrcCap; }
+__host__ __device__ inline size_t cells_lune_smem(uint32_t capL, uint32_t capR) { return (lune_smem_bytes(capL, capR, 0) + 15) & ~(size_t) 15; }
 __host__ __device__ inline size_t cells_smem_bytes(uint32_t capL, uint32_t capR)
 {
-    return ((lune_smem_bytes(capL, capR, 0) + 15) & ~(size_t) 15) + kCellWarps * cells_warp_smem();
+    return cells_lune_smem(capL, capR) + kCellWarps * cells_warp_smem() + sizeof(uint32_t) * ((size_t) capL + capR);
 }
 
 // Runs the whole layered DP of ONE candidate (already described by pr) inside the calling CTA's slice.
+// Cells are handed out in diagonal-major order; a warp starts cell (a,b) as soon as row a is finished up to b and
+// column b up to a (its only inputs), so no CTA-wide barrier separates the anti-diagonals.
 __device__ void run_candidate(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, const Tables& T, const PairRec& pr,
                               CellCtx& C, uint32_t* s_cnt, uint32_t* s_wk, double* s_wv, uint64_t kmax, uint32_t nlayers_ref,
                               unsigned long long& my_cells, unsigned int& my_states, CandResult& out)
@@ -525,22 +546,39 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
     C.seg2 = dist2(C.Sx, C.Sy, C.Ex, C.Ey);
     // reset the slice: no cell has produced anything; cell (0,0) "produces" the layer-0 seeds (:149-160):
     // RIGHT(0; 0->i) and LEFT(0; 0->i) all share one record (layer 0, area 0)
-    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) C.sl.alive[t] = 0;
+    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) C.sl.alive[t] = t == 0 ? 1 : 0;
     const uint32_t D0 = (nr - 1) + (nl - 1);
-    for (uint32_t t = threadIdx.x; t < D0; t += blockDim.x) { DirEnt de; de.off = 0; de.len = 1; de.kmin = 0; de.kmax = 0; C.sl.dir[t] = de; }
-    if (threadIdx.x == 0) { C.sl.vpool[0] = 0.0; C.sl.kpool[0] = 0; *C.bump = 1u; *C.overflow = 0u; }
-    __syncthreads();
-    if (threadIdx.x == 0) C.sl.alive[0] = 1;
+    for (uint32_t t = threadIdx.x; t < D0; t += blockDim.x) { DirEnt de; de.off = 0; de.kmin = 0; de.len = 1; C.sl.dir[t] = de; C.sl.nfin[t] = 1; }
+    for (uint32_t t = threadIdx.x; t < nl; t += blockDim.x) C.rowdone[t] = t == 0 ? 1u : 0u;
+    for (uint32_t t = threadIdx.x; t < nr; t += blockDim.x) C.coldone[t] = t == 0 ? 1u : 0u;
+    if (threadIdx.x == 0) { C.sl.vpool[0] = 0.0; *C.bump = 1u; *C.overflow = 0u; *C.next = 0u; }
     my_states += (threadIdx.x == 0) ? D0 : 0u;
     uint32_t bk = 0; double bv = INFINITY;
     __syncthreads();
-    // anti-diagonals of the head grid: every cell of diagonal a+b = d only reads cells of earlier diagonals
-    const uint32_t ndiag = nl + nr - 1;
-    for (uint32_t d = 1; d < ndiag; ++d)
+    const uint32_t total = nl * nr - 1;                 // every cell but (0,0)
+    uint32_t d = 1, dstart = 0;                         // current diagonal and the order index of its first cell
+    for (;;)
     {
-        const uint32_t alo = d > nr - 1 ? d - (nr - 1) : 0u, ahi = min(d, nl - 1);
-        for (uint32_t a = alo + warp; a <= ahi; a += kCellWarps) process_cell(C, T, a, d - a, lane, bk, bv, my_cells, my_states);
-        __syncthreads();
+        uint32_t t = 0;
+        if (lane == 0) t = atomicAdd(C.next, 1u);
+        t = __shfl_sync(kFull, t, 0);
+        if (t >= total) break;
+        uint32_t alo, cnt;
+        for (;;)
+        {
+            alo = d > nr - 1 ? d - (nr - 1) : 0u;
+            cnt = min(d, nl - 1) - alo + 1;
+            if (t < dstart + cnt) break;
+            dstart += cnt; ++d;
+        }
+        const uint32_t a = alo + (t - dstart), b = d - a;
+        if (lane == 0) while (C.rowdone[a] < b || C.coldone[b] < a) __nanosleep(32);
+        __syncwarp();
+        __threadfence_block();
+        process_cell(C, T, a, b, lane, bk, bv, my_cells, my_states);
+        __threadfence_block();
+        __syncwarp();
+        if (lane == 0) { C.rowdone[a] = b + 1; C.coldone[b] = a + 1; }
     }
     // best terminal state of the candidate: deepest layer, then smallest area (:169-173)
     for (int o = 16; o; o >>= 1)
@@ -557,18 +595,21 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
 }
 
 __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, uint32_t capL, uint32_t capR, unsigned char* arena,
-                                          const CellLayout& Lo, uint32_t slice, double amax, unsigned int* bump, unsigned int* overflow)
+                                          const CellLayout& Lo, uint32_t slice, double amax, unsigned int* next, unsigned int* bump,
+                                          unsigned int* overflow)
 {
     const uint32_t warp = threadIdx.x >> 5;
     C.S = carve_smem(smem_raw, capL, capR);
-    unsigned char* wbase = smem_raw + ((lune_smem_bytes(capL, capR, 0) + 15) & ~(size_t) 15) + warp * cells_warp_smem();
+    unsigned char* wbase = smem_raw + cells_lune_smem(capL, capR) + warp * cells_warp_smem();
     C.acc = reinterpret_cast<double*>(wbase);
     C.src = reinterpret_cast<SrcRec*>(wbase + sizeof(double) * kBT * 32);
     C.pred = reinterpret_cast<uint32_t*>(wbase + sizeof(double) * kBT * 32 + sizeof(SrcRec) * kSrcCap);
+    uint32_t* done = reinterpret_cast<uint32_t*>(smem_raw + cells_lune_smem(capL, capR) + kCellWarps * cells_warp_smem());
+    C.rowdone = done; C.coldone = done + capL;
     C.sl = carve_cells(arena, Lo, slice);
     C.spill = C.sl.spill + (size_t) warp * Lo.spill_cap;
     C.spill_pred = C.sl.spill_pred + (size_t) warp * Lo.spill_cap;
-    C.cap = Lo.cap; C.amax = amax; C.bump = bump; C.overflow = overflow;
+    C.cap = Lo.cap; C.amax = amax; C.next = next; C.bump = bump; C.overflow = overflow;
     for (uint32_t t = threadIdx.x & 31; t < (uint32_t) kBT * 32; t += 32) C.acc[t] = INFINITY;
 }
 
@@ -582,12 +623,12 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
-    __shared__ unsigned int s_pair, s_bump, s_overflow;
+    __shared__ unsigned int s_pair, s_bump, s_overflow, s_next;
     __shared__ uint32_t s_wk[kCellWarps];
     __shared__ double s_wv[kCellWarps];
     __shared__ CtaBest s_best;
     CellCtx C;
-    setup_ctx(C, smem_raw, capL, capR, arena, Lo, blockIdx.x, amax, &s_bump, &s_overflow);
+    setup_ctx(C, smem_raw, capL, capR, arena, Lo, blockIdx.x, amax, &s_next, &s_bump, &s_overflow);
     const uint32_t lane = threadIdx.x & 31;
     unsigned long long my_cells = 0; unsigned int my_states = 0;
     if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0; }
@@ -653,11 +694,8 @@ __device__ unsigned long long state_value(const CellSlice& sl, uint32_t nl, uint
     else { pa = s; pb = o; d = (nr - 1 - o) + (ss - s - 1); }             // LEFT (o; s->ss): produced by cell (s, o)
     if (!sl.alive[pa * nr + pb]) return kInfBits;
     const DirEnt de = sl.dir[dir_base(pa, pb, nl, nr) + d];
-    if (de.len == 0 || k < de.kmin || k > de.kmax) return kInfBits;
-    uint32_t lo = 0, hi = de.len;
-    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (sl.kpool[de.off + mid] < k) lo = mid + 1; else hi = mid; }
-    if (lo >= de.len || sl.kpool[de.off + lo] != k) return kInfBits;
-    return area_bits(sl.vpool[de.off + lo]);
+    if (de.len == 0 || k < de.kmin || k >= (uint32_t) de.kmin + de.len) return kInfBits;
+    return area_bits(sl.vpool[de.off + (k - de.kmin)]);      // holes hold +inf = kInfBits
 }
 
 // Re-derives the chain of states behind the best terminal state of layer kopt and emits the hull in the
@@ -816,7 +854,7 @@ namespace
 struct AdSmall { PairStats stats; AdCounters counters; CtaBest best; AdHull hull; uint32_t lune_cnt[2]; unsigned int ovf_count[2]; };
 
 constexpr uint64_t kMinPoolRecords = 1u << 16;        // smallest record pool a slice may have
-constexpr uint64_t kDefaultPoolRecords = 24u << 20;   // first-try pool per slice (overflowing candidates are re-run larger)
+constexpr uint64_t kDefaultPoolRecords = 4u << 20;    // first-try pool per slice (overflowing candidates are re-run larger)
 
 // Launches the cell kernel over `count` queue entries (order == nullptr: pairs[0..count)) with `slices` CTAs.
 int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uint32_t count, uint32_t slices, const CellLayout& Lo,
