@@ -37,7 +37,8 @@ struct PairStats
     unsigned long long max_dirs;    // max over queued candidates of nl * nr * (nl + nr - 2) / 2   (directory entries)
 };
 
-struct CtaBest { uint32_t found; uint32_t count; double area; unsigned long long key; uint32_t s, t; };
+struct CtaBest { uint32_t found; uint32_t count; double area; unsigned long long key; uint32_t s, t;
+                 uint32_t nl, nr, slice, round; };   // slice/round: where the winner's records still live (see ad_finish)
 
 struct AdCounters { unsigned long long cells, states; unsigned int queue; unsigned int pad; };
 
@@ -619,7 +620,7 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
            const PairRec* __restrict__ pairs, const uint32_t* __restrict__ order, uint32_t npairs, AdCounters* __restrict__ counters,
            unsigned char* arena, CellLayout Lo, uint32_t capL, uint32_t capR,
            uint64_t kmax, uint32_t nlayers_ref, double amax, CtaBest* __restrict__ cta_best,
-           uint32_t* __restrict__ ovf_list, unsigned int* __restrict__ ovf_count)
+           uint32_t* __restrict__ ovf_list, unsigned int* __restrict__ ovf_count, uint32_t round)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
@@ -628,10 +629,13 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
     __shared__ double s_wv[kCellWarps];
     __shared__ CtaBest s_best;
     CellCtx C;
-    setup_ctx(C, smem_raw, capL, capR, arena, Lo, blockIdx.x, amax, &s_next, &s_bump, &s_overflow);
+    uint32_t cur = 0;                      // each CTA owns slices 2*blockIdx and 2*blockIdx+1: the one being written and the
+                                           // one that holds the CTA's best candidate so far (kept for the witness walk)
+    setup_ctx(C, smem_raw, capL, capR, arena, Lo, 2 * blockIdx.x + cur, amax, &s_next, &s_bump, &s_overflow);
     const uint32_t lane = threadIdx.x & 31;
     unsigned long long my_cells = 0; unsigned int my_states = 0;
-    if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0; }
+    if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0;
+                            s_best.nl = s_best.nr = 0; s_best.slice = 0; s_best.round = round; }
     for (;;)
     {
         __syncthreads();
@@ -651,13 +655,26 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
             continue;
         }
         // candidate result (AntipodalOptimized.cpp:328-331, 512-517): count desc, area asc, first pair in (i<j) order
-        if (threadIdx.x == 0 && res.kbest > 0)
+        bool better = false;
+        if (res.kbest > 0)
         {
             const uint32_t cnt = res.kbest + 2;
             const unsigned long long key = (unsigned long long) pr.s * n + pr.t;
-            const bool better = !s_best.found || cnt > s_best.count ||
-                                (cnt == s_best.count && (res.area < s_best.area || (res.area == s_best.area && key < s_best.key)));
-            if (better) { s_best.found = 1; s_best.count = cnt; s_best.area = res.area; s_best.key = key; s_best.s = pr.s; s_best.t = pr.t; }
+            better = !s_best.found || cnt > s_best.count ||
+                     (cnt == s_best.count && (res.area < s_best.area || (res.area == s_best.area && key < s_best.key)));
+            __syncthreads();                   // every thread has read s_best
+            if (better && threadIdx.x == 0)
+            {
+                s_best.found = 1; s_best.count = cnt; s_best.area = res.area; s_best.key = key; s_best.s = pr.s; s_best.t = pr.t;
+                s_best.nl = pr.nl; s_best.nr = pr.nr; s_best.slice = 2 * blockIdx.x + cur; s_best.round = round;
+            }
+        }
+        if (better)
+        {   // keep this candidate's records: continue in the other slice
+            cur ^= 1u;
+            C.sl = carve_cells(arena, Lo, 2 * blockIdx.x + cur);
+            C.spill = C.sl.spill + (size_t) (threadIdx.x >> 5) * Lo.spill_cap;
+            C.spill_pred = C.sl.spill_pred + (size_t) (threadIdx.x >> 5) * Lo.spill_cap;
         }
     }
     for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(kFull, my_cells, o); my_states += __shfl_xor_sync(kFull, my_states, o); }
@@ -703,14 +720,14 @@ __device__ unsigned long long state_value(const CellSlice& sl, uint32_t nl, uint
 // Runs after k_ad_cells processed the winning candidate alone in slice 0.
 __global__ void __launch_bounds__(kCellThreads)
 k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T, PairRec pr,
-               unsigned char* arena, CellLayout Lo, uint32_t kopt,
+               unsigned char* arena, CellLayout Lo, uint32_t slice, uint32_t kopt,
                int32_t* __restrict__ left, int32_t* __restrict__ right, int32_t* __restrict__ hull, AdHull* __restrict__ out)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
     LuneSmem S = carve_smem(smem_raw, pr.nl, pr.nr);
     build_lune(x, y, n, pr, S, s_cnt);
-    const CellSlice sl = carve_cells(arena, Lo, 0);
+    const CellSlice sl = carve_cells(arena, Lo, slice);
     const uint32_t nl = pr.nl, nr = pr.nr;
     // best terminal state of layer kopt (:348-355): smallest area, first in (side, o, s) order; all threads scan
     __shared__ unsigned long long s_v[kCellThreads];
@@ -859,7 +876,7 @@ constexpr uint64_t kDefaultPoolRecords = 4u << 20;    // first-try pool per slic
 // Launches the cell kernel over `count` queue entries (order == nullptr: pairs[0..count)) with `slices` CTAs.
 int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uint32_t count, uint32_t slices, const CellLayout& Lo,
                     uint32_t capL, uint32_t capR, uint64_t kmax, uint32_t nlayers_ref, double amax, AdSmall* sm,
-                    CtaBest* d_cta_best, uint32_t* d_ovf_list, unsigned int* d_ovf_count)
+                    CtaBest* d_cta_best, uint32_t* d_ovf_list, unsigned int* d_ovf_count, uint32_t round)
 {
     const size_t smem = cells_smem_bytes(capL, capR);
     if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
@@ -869,7 +886,7 @@ int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uin
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
     k_ad_cells<<<slices, kCellThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
                                                           &sm->counters, c->arena.as<unsigned char>(), Lo, capL, capR, kmax, nlayers_ref,
-                                                          amax, d_cta_best, d_ovf_list, d_ovf_count);
+                                                          amax, d_cta_best, d_ovf_list, d_ovf_count, round);
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());
     return ADK_OK;
@@ -889,7 +906,7 @@ int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, int* per_sm)
 
 // Runs every queued candidate; candidates whose record pool overflowed are re-run in fewer, larger slices.
 int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairStats& ps, uint64_t kmax, uint32_t nlayers_ref, double amax,
-                 AdSmall* sm, CellLayout* used_layout)
+                 AdSmall* sm, CellLayout* used_layout, uint32_t* last_round)
 {
     const uint32_t max_src = ps.max_nl + ps.max_nr;
     if (ps.max_dirs >= 0xffffffffull) { c->err = "area+diameter path: candidate too large for 32-bit directory offsets"; return ADK_ERR_NOMEM; }
@@ -906,20 +923,21 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairSta
     {
         const uint64_t budget = workspace_budget(c, c->arena);
         const uint64_t min_bytes = fixed + 10 * kMinPoolRecords, want_bytes = fixed + 10 * pool;
-        if (budget < min_bytes) { c->err = "area+diameter path: one candidate's workspace exceeds the memory budget"; return ADK_ERR_NOMEM; }
+        if (budget < 2 * min_bytes) { c->err = "area+diameter path: one candidate's workspace exceeds the memory budget"; return ADK_ERR_NOMEM; }
+        // every CTA owns two slices (the one it writes and the one holding its best candidate so far)
         uint64_t slices = std::min<uint64_t>(count, (uint64_t) c->sm_count * (uint64_t) occ);
-        if (round > 0) slices = std::min<uint64_t>(slices, std::max<uint64_t>(1, budget / want_bytes));   // fewer, larger slices
-        slices = std::max<uint64_t>(1, std::min<uint64_t>(slices, budget / min_bytes));
-        size_t slice_bytes = (size_t) std::min<uint64_t>(budget / slices, want_bytes) & ~(size_t) 255;
+        if (round > 0) slices = std::min<uint64_t>(slices, std::max<uint64_t>(1, budget / (2 * want_bytes)));   // fewer, larger slices
+        slices = std::max<uint64_t>(1, std::min<uint64_t>(slices, budget / (2 * min_bytes)));
+        size_t slice_bytes = (size_t) std::min<uint64_t>(budget / (2 * slices), want_bytes) & ~(size_t) 255;
         const CellLayout Lo = cell_layout(ps.max_cells, ps.max_dirs, max_src, slice_bytes);
         if (round > 0 && Lo.cap <= prev_cap)
         {   // the overflowing candidate already had everything the budget allows
             c->err = "area+diameter path: one candidate's record pool exceeds the memory budget"; return ADK_ERR_NOMEM;
         }
-        ADK_TRY(ensure(c, c->arena, slice_bytes * (size_t) slices));
+        ADK_TRY(ensure(c, c->arena, slice_bytes * 2 * (size_t) slices));
         ADK_TRY(ensure(c, c->scratch1, sizeof(CtaBest) * slices));
         ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
-                                c->scratch1.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1]));
+                                c->scratch1.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round));
         k_ad_reduce<<<1, 32, 0, c->stream>>>(c->scratch1.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
@@ -928,6 +946,7 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairSta
         ADK_CUDA(c, cudaMemcpyAsync(&novf, &sm->ovf_count[round & 1], sizeof(novf), cudaMemcpyDeviceToHost, c->stream));
         ADK_CUDA(c, cudaStreamSynchronize(c->stream));
         if (used_layout) *used_layout = Lo;
+        if (last_round) *last_round = (uint32_t) round;
         if (novf == 0) break;
         d_order = d_ovf[round & 1]; count = novf;
         prev_cap = Lo.cap; pool = (uint64_t) Lo.cap * 8;
@@ -961,10 +980,13 @@ int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, 
     float dp_ms = 0.f;
     CtaBest hb; std::memset(&hb, 0, sizeof(hb));
     AdCounters hc; std::memset(&hc, 0, sizeof(hc));
+    CellLayout keep_layout; std::memset(&keep_layout, 0, sizeof(keep_layout));
+    uint32_t keep_round = 0;
+    c->ad_keep_valid = false;
     if (ps.nqueued > 0)
     {
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
-        ADK_TRY(ad_run_queue(c, c->scratch0.as<PairRec>(), ps.nqueued, ps, kmax, nlayers_ref, amax, sm, nullptr));
+        ADK_TRY(ad_run_queue(c, c->scratch0.as<PairRec>(), ps.nqueued, ps, kmax, nlayers_ref, amax, sm, &keep_layout, &keep_round));
         ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
         ADK_CUDA(c, cudaMemcpyAsync(&hb, &sm->best, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
         ADK_CUDA(c, cudaMemcpyAsync(&hc, &sm->counters, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
@@ -977,6 +999,13 @@ int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, 
     if (hb.found)
     {
         out->found = 1; out->count = hb.count; out->area = hb.area; out->tie_key = hb.key; out->w0 = hb.s; out->w1 = hb.t;
+        if (hb.round == keep_round)
+        {   // the winner's records are still in its slice: ad_finish can walk them without re-running the candidate
+            static_assert(sizeof(CellLayout) <= sizeof(c->ad_keep_layout), "ad_keep_layout too small");
+            std::memcpy(c->ad_keep_layout, &keep_layout, sizeof(CellLayout));
+            c->ad_keep_valid = true; c->ad_keep_slice = hb.slice; c->ad_keep_s = hb.s; c->ad_keep_t = hb.t;
+            c->ad_keep_nl = hb.nl; c->ad_keep_nr = hb.nr; c->ad_keep_count = hb.count; c->ad_keep_kmax = kmax; c->ad_keep_amax = amax;
+        }
     }
     if (st)
     {
@@ -1000,37 +1029,50 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
     ADK_TRY(run_count_tables(c));
     ADK_TRY(ensure(c, c->small, sizeof(AdSmall)));
     AdSmall* sm = c->small.as<AdSmall>();
-    // the winning candidate alone: size it, re-run it in slice 0 (:529-535), walk back over its records
     ADK_TRY(ensure(c, c->scratch6, sizeof(int32_t) * 3 * ((size_t) n + 4) + sizeof(PairRec) + 64));
     int32_t* d_left = c->scratch6.as<int32_t>();
     int32_t* d_right = d_left + (n + 4);
     int32_t* d_hull = d_right + (n + 4);
     PairRec* d_pair = reinterpret_cast<PairRec*>(d_hull + (n + 4));
-    const size_t smem_ll = lune_smem_bytes(n + 2, n + 2, 1);
-    if (smem_ll > 200 * 1024) { c->err = "ad_finish: point set too large for the lune kernel"; return ADK_ERR_NOMEM; }
-    ADK_CUDA(c, cudaFuncSetAttribute(k_ad_lune_lists, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_ll));
-    k_ad_lune_lists<<<1, kAdThreads, smem_ll, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, best->w0, best->w1, d_left, d_right, sm->lune_cnt);
-    ++c->launches;
-    ADK_CUDA(c, cudaGetLastError());
-    uint32_t cnt[2];
-    ADK_CUDA(c, cudaMemcpyAsync(cnt, sm->lune_cnt, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
-    ADK_CUDA(c, cudaStreamSynchronize(c->stream));
-    PairRec pr{best->w0, best->w1, cnt[0], cnt[1]};
-    const uint64_t inner = (uint64_t) pr.nl + pr.nr - 4;
-    const uint32_t lim = (uint32_t) std::min<uint64_t>(kmax - 2, inner);
-    const uint32_t kopt = best->count - 2;
-    if (kopt > lim) { c->err = "ad_finish: witness count exceeds the candidate's capacity"; return ADK_ERR_ARG; }
-    PairStats ps; std::memset(&ps, 0, sizeof(ps));
-    ps.nqueued = 1; ps.max_nl = pr.nl; ps.max_nr = pr.nr; ps.max_lim = lim;
-    ps.max_cells = (unsigned long long) pr.nl * pr.nr; ps.max_dirs = ps.max_cells * (pr.nl + pr.nr - 2) / 2;
-    ADK_CUDA(c, cudaMemcpyAsync(d_pair, &pr, sizeof(pr), cudaMemcpyHostToDevice, c->stream));
-    ADK_CUDA(c, cudaMemsetAsync(&sm->counters, 0, sizeof(AdCounters), c->stream));
+    PairRec pr;
     CellLayout Lo;
-    ADK_TRY(ad_run_queue(c, d_pair, 1, ps, kmax, nlayers_ref, amax, sm, &Lo));
+    uint32_t slice = 0;
+    const uint32_t kopt = best->count - 2;
+    if (c->ad_keep_valid && c->ad_keep_s == best->w0 && c->ad_keep_t == best->w1 && c->ad_keep_count == best->count &&
+        c->ad_keep_kmax == kmax && c->ad_keep_amax == amax)
+    {   // the partial solve on this context left the winner's records in place
+        pr = PairRec{best->w0, best->w1, c->ad_keep_nl, c->ad_keep_nr};
+        std::memcpy(&Lo, c->ad_keep_layout, sizeof(CellLayout));
+        slice = c->ad_keep_slice;
+    }
+    else
+    {   // the winning candidate alone (it was found on another GPU, or evicted): size it, re-run it (:529-535)
+        const size_t smem_ll = lune_smem_bytes(n + 2, n + 2, 1);
+        if (smem_ll > 200 * 1024) { c->err = "ad_finish: point set too large for the lune kernel"; return ADK_ERR_NOMEM; }
+        ADK_CUDA(c, cudaFuncSetAttribute(k_ad_lune_lists, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem_ll));
+        k_ad_lune_lists<<<1, kAdThreads, smem_ll, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, best->w0, best->w1, d_left, d_right, sm->lune_cnt);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+        uint32_t cnt[2];
+        ADK_CUDA(c, cudaMemcpyAsync(cnt, sm->lune_cnt, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+        pr = PairRec{best->w0, best->w1, cnt[0], cnt[1]};
+        const uint64_t inner = (uint64_t) pr.nl + pr.nr - 4;
+        const uint32_t lim = (uint32_t) std::min<uint64_t>(kmax - 2, inner);
+        if (kopt > lim) { c->err = "ad_finish: witness count exceeds the candidate's capacity"; return ADK_ERR_ARG; }
+        PairStats ps; std::memset(&ps, 0, sizeof(ps));
+        ps.nqueued = 1; ps.max_nl = pr.nl; ps.max_nr = pr.nr; ps.max_lim = lim;
+        ps.max_cells = (unsigned long long) pr.nl * pr.nr; ps.max_dirs = ps.max_cells * (pr.nl + pr.nr - 2) / 2;
+        ADK_CUDA(c, cudaMemcpyAsync(d_pair, &pr, sizeof(pr), cudaMemcpyHostToDevice, c->stream));
+        ADK_CUDA(c, cudaMemsetAsync(&sm->counters, 0, sizeof(AdCounters), c->stream));
+        c->ad_keep_valid = false;
+        ADK_TRY(ad_run_queue(c, d_pair, 1, ps, kmax, nlayers_ref, amax, sm, &Lo, nullptr));
+        slice = 0;                               // the only candidate of the only CTA: its first slice
+    }
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), n};
     const size_t smem = lune_smem_bytes(pr.nl, pr.nr, 1);
     ADK_CUDA(c, cudaFuncSetAttribute(k_ad_backtrack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    k_ad_backtrack<<<1, kCellThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, T, pr, c->arena.as<unsigned char>(), Lo, kopt,
+    k_ad_backtrack<<<1, kCellThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, T, pr, c->arena.as<unsigned char>(), Lo, slice, kopt,
                                                          d_left, d_right, d_hull, &sm->hull);
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());

@@ -27,6 +27,7 @@ void release_idle(Ctx* c, const DevBuf* keep)
     else if (c->arena.p)
     {
         drop(c->arena);
+        c->ad_keep_valid = false;
         c->ad_V = c->ad_Q = 0; c->ad_L = 0; c->ad_slices = 0; c->ad_slice_bytes = 0;
     }
 }

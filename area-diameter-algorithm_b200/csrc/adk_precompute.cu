@@ -154,16 +154,43 @@ __global__ void k_pit_query(const double* __restrict__ x, const double* __restri
 
 // ------------------------------------------------------------------------------------------------ host side
 
+static uint64_t hash_points(const double* x, const double* y, uint32_t n)
+{   // FNV-1a over the raw coordinate bytes
+    uint64_t h = 1469598103934665603ull ^ n;
+    const unsigned char* px = reinterpret_cast<const unsigned char*>(x);
+    const unsigned char* py = reinterpret_cast<const unsigned char*>(y);
+    for (size_t i = 0; i < sizeof(double) * (size_t) n; ++i) { h ^= px[i]; h *= 1099511628211ull; }
+    for (size_t i = 0; i < sizeof(double) * (size_t) n; ++i) { h ^= py[i]; h *= 1099511628211ull; }
+    return h;
+}
+
 int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool device_ptrs)
 {
     if (!x || !y || n == 0 || n > ADK_MAX_POINTS) { c->err = "bad point arrays / n out of range"; return ADK_ERR_ARG; }
+    // The same point set as the resident one (a diameter sweep, a partial followed by its finish) keeps the count
+    // tables, the orders and the retained winning candidate: compare a content hash before invalidating anything.
+    const double* hx = x; const double* hy = y;
+    if (device_ptrs)
+    {
+        ADK_TRY(ensure_pinned(c, sizeof(double) * 2 * (size_t) n));
+        double* h = static_cast<double*>(c->h_pinned);
+        ADK_CUDA(c, cudaMemcpyAsync(h, x, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaMemcpyAsync(h + n, y, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+        hx = h; hy = h + n;
+    }
+    const uint64_t hash = hash_points(hx, hy, n);
+    const bool same = c->points_valid && c->n == n && c->points_hash == hash;
     ADK_TRY(ensure(c, c->x, sizeof(double) * n));
     ADK_TRY(ensure(c, c->y, sizeof(double) * n));
     const cudaMemcpyKind kind = device_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     ADK_CUDA(c, cudaMemcpyAsync(c->x.p, x, sizeof(double) * n, kind, c->stream));
     ADK_CUDA(c, cudaMemcpyAsync(c->y.p, y, sizeof(double) * n, kind, c->stream));
+    if (same) return ADK_OK;       // the copy is still made (the caller's buffer is the input of this call); products stay valid
     c->n = n;
+    c->points_hash = hash; c->points_valid = true;
     c->have_cw = c->have_modpi = c->have_tables = c->have_yorder = false;
+    c->ad_keep_valid = false;
     return ADK_OK;
 }
 
