@@ -26,6 +26,7 @@ namespace adk
 {
 
 struct PairRec { uint32_t s, t; uint32_t nl, nr; };   // nl, nr include s and t themselves
+constexpr int kCostBuckets = 96;
 
 struct PairStats
 {
@@ -35,7 +36,18 @@ struct PairStats
     unsigned int pad;
     unsigned long long max_cells;   // max over queued candidates of nl * nr                      (cells of the head grid)
     unsigned long long max_dirs;    // max over queued candidates of nl * nr * (nl + nr - 2) / 2   (directory entries)
+    unsigned int hist[kCostBuckets];    // queued candidates per cost bucket (heaviest candidates are started first)
+    unsigned int cursor[kCostBuckets];
 };
+
+// Cost class of a candidate: 2 * log2(nl * nr * (nl + nr)), in half-octave steps.
+__device__ __forceinline__ uint32_t cost_bucket(uint32_t nl, uint32_t nr)
+{
+    const unsigned long long cost = (unsigned long long) nl * nr * (nl + nr);
+    const int l = 63 - __clzll((long long) cost);
+    const uint32_t b = 2u * (uint32_t) l + (uint32_t) ((cost >> (l - 1)) & 1ull);     // cost >= 16: l >= 4
+    return b < (uint32_t) kCostBuckets ? b : (uint32_t) kCostBuckets - 1;
+}
 
 struct CtaBest { uint32_t found; uint32_t count; double area; unsigned long long key; uint32_t s, t;
                  uint32_t nl, nr, slice, round; };   // slice/round: where the winner's records still live (see ad_finish)
@@ -101,8 +113,27 @@ __global__ void k_ad_pairs(const double* __restrict__ x, const double* __restric
                 const unsigned long long cells = (unsigned long long) nl * nr;
                 atomicMax(&stats->max_nl, nl); atomicMax(&stats->max_nr, nr); atomicMax(&stats->max_lim, (unsigned int) lim);
                 atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2) / 2);
+                atomicAdd(&stats->hist[cost_bucket(nl, nr)], 1u);
             }
         }
+    }
+}
+
+// Processing order of the queue: heaviest cost class first (a counting sort over kCostBuckets classes), so that the
+// long candidates do not end up alone at the tail of the persistent grid.
+__global__ void k_ad_order(const PairRec* __restrict__ pairs, uint32_t npairs, PairStats* __restrict__ stats, uint32_t* __restrict__ order)
+{
+    __shared__ uint32_t s_base[kCostBuckets];
+    if (threadIdx.x == 0)
+    {
+        uint32_t run = 0;
+        for (int b = kCostBuckets - 1; b >= 0; --b) { s_base[b] = run; run += stats->hist[b]; }
+    }
+    __syncthreads();
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < npairs; t += gridDim.x * blockDim.x)
+    {
+        const uint32_t b = cost_bucket(pairs[t].nl, pairs[t].nr);
+        order[s_base[b] + atomicAdd(&stats->cursor[b], 1u)] = t;
     }
 }
 
@@ -289,17 +320,19 @@ constexpr unsigned kFull = 0xffffffffu;
 
 // Accumulates, for the 32 destinations of one tile, the layer rows [k0, k0 + rows) of acc (all +inf on entry):
 // acc[row][lane] = min over sources with a set predicate bit of (area + triangle), at layer k + c (:188-195, :207-217).
+// REG: the lane's predicate bits over the (at most 64) sources are in `mask`; otherwise preds[p] holds one word per source.
+template <bool REG>
 __device__ __forceinline__ void cell_accumulate(const CellCtx& C, const SrcRec* __restrict__ srcs, const uint32_t* __restrict__ preds,
-                                                uint32_t P, uint32_t lane, uint32_t k0, uint32_t rows)
+                                                unsigned long long mask, uint32_t P, uint32_t lane, uint32_t k0, uint32_t rows)
 {
     const uint32_t dmax = min(C.lim, C.nlayers - 1);          // :192-195; layers beyond lim are never read
     const uint32_t khi = min(k0 + rows - 1, dmax);
     double* col = C.acc + lane;
     for (uint32_t p = 0; p < P; ++p)
     {
-        const uint32_t m = preds[p];
-        if (!m) continue;
-        const bool mine = (m >> lane) & 1u;
+        bool mine;
+        if (REG) { mine = (mask >> p) & 1ull; if (!__any_sync(kFull, mine)) continue; }
+        else { const uint32_t m = preds[p]; if (!m) continue; mine = (m >> lane) & 1u; }
         const SrcRec r = srcs[p];
         const double tri = r.tri;
         if (r.kmin == 0)
@@ -355,17 +388,23 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     {
         const uint32_t u = u0 + lane;
         bool live = false, left = false;
-        uint32_t s = 0, dix = 0;
+        uint32_t s = 0, dix = 0, nfin_src = 0;
         DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
         if (u < npot)
         {
             left = u >= b; s = left ? u - b : u;
             const uint32_t pa = left ? s : a, pb = left ? b : s;
-            if (C.sl.alive[pa * nr + pb])
-            {
-                dix = dir_base(pa, pb, nl, nr) + (left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1));
-                de = C.sl.dir[dix];
-                live = de.len > 0;
+            dix = dir_base(pa, pb, nl, nr) + (left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1));
+            const unsigned char al = C.sl.alive[pa * nr + pb];      // the flag and the entry are loaded together: the entry
+            const DirEnt dd = C.sl.dir[dix];                        // of a cell that produced nothing is stale and ignored
+            nfin_src = C.sl.nfin[dix];
+            if (al) { de = dd; live = de.len > 0; }
+            if (live)
+            {   // pull the layer vector towards L1 while the geometry below is computed
+                const char* v0 = reinterpret_cast<const char*>(C.sl.vpool + de.off);
+                const char* v1 = reinterpret_cast<const char*>(C.sl.vpool + de.off + de.len - 1);
+                for (const char* q = v0; q <= v1; q += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(v1));
             }
         }
         const uint32_t kmax = (uint32_t) de.kmin + de.len - 1;
@@ -397,7 +436,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
             r.sidx = (uint16_t) (s | (left ? 0x8000u : 0u));
             // cell updates the reference performs for these states (:198,225,271,298), and the output layer range
             const uint32_t ceff = c + (de.kmin == 0 ? cx : 0u);                  // only the seeds sit on layer 0
-            uint32_t nvalid = C.sl.nfin[dix];
+            uint32_t nvalid = nfin_src;
             if (kmax + ceff >= C.nlayers)
             {
                 nvalid = 0;
@@ -450,6 +489,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
         }
         // per (source edge, destination) geometry, once for all layers
         uint32_t anyp = 0;
+        unsigned long long mask = 0ull;
         for (uint32_t p = 0; p < P; ++p)
         {
             const uint32_t sx = srcs[p].sidx;
@@ -464,10 +504,15 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                 if (left != dR) ok = orientation(qx, qy, hx, hy, psx, psy) >= 0;     // stay on the edge's chain (:201, :274)
                 else ok = pseudo_dist(psx, psy, hx, hy, qx, qy) <= refd;             // switch chains (:226-227, :299-300)
             }
-            const uint32_t m = __ballot_sync(kFull, ok);
-            if (lane == 0) preds[p] = m;
-            anyp |= m;
+            if (!spilled) mask |= (unsigned long long) ok << p;
+            else
+            {
+                const uint32_t m = __ballot_sync(kFull, ok);
+                if (lane == 0) preds[p] = m;
+                anyp |= m;
+            }
         }
+        if (!spilled) anyp = __any_sync(kFull, mask != 0ull) ? 1u : 0u;
         __syncwarp();
         // the destination's layer vector: first .. last finite layer, holes stay +inf
         uint32_t first = 0xffffffffu, last = 0, nfin = 0, lane_off = 0, base = 0;
@@ -480,7 +525,8 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                 for (uint32_t t = 0; t < ntiles; ++t)
                 {
                     const uint32_t k0 = klo + t * kBT, rows = min((uint32_t) kBT, khi + 1 - k0);
-                    cell_accumulate(C, srcs, preds, P, lane, k0, rows);
+                    if (!spilled) cell_accumulate<true>(C, srcs, preds, mask, P, lane, k0, rows);
+                    else cell_accumulate<false>(C, srcs, preds, 0ull, P, lane, k0, rows);
                     if (counting)
                     {
                         for (uint32_t rr = 0; rr < rows; ++rr)
@@ -905,7 +951,7 @@ int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, int* per_sm)
 }
 
 // Runs every queued candidate; candidates whose record pool overflowed are re-run in fewer, larger slices.
-int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairStats& ps, uint64_t kmax, uint32_t nlayers_ref, double amax,
+int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint32_t nqueued, const PairStats& ps, uint64_t kmax, uint32_t nlayers_ref, double amax,
                  AdSmall* sm, CellLayout* used_layout, uint32_t* last_round)
 {
     const uint32_t max_src = ps.max_nl + ps.max_nr;
@@ -913,9 +959,9 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairSta
     const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, max_src, 0).off_v + 8192;
     int occ = 1;
     ADK_TRY(ad_cells_occupancy(c, ps.max_nl, ps.max_nr, &occ));
-    ADK_TRY(ensure(c, c->scratch2, sizeof(uint32_t) * 2 * (size_t) nqueued + 64));
-    uint32_t* d_ovf[2] = {c->scratch2.as<uint32_t>(), c->scratch2.as<uint32_t>() + nqueued};
-    const uint32_t* d_order = nullptr;
+    ADK_TRY(ensure(c, c->ad_ovf, sizeof(uint32_t) * 2 * (size_t) nqueued + 64));
+    uint32_t* d_ovf[2] = {c->ad_ovf.as<uint32_t>(), c->ad_ovf.as<uint32_t>() + nqueued};
+    const uint32_t* d_order = d_order0;
     uint32_t count = nqueued;
     uint64_t pool = kDefaultPoolRecords, prev_cap = 0;
     int merge = 0;
@@ -935,10 +981,10 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, uint32_t nqueued, const PairSta
             c->err = "area+diameter path: one candidate's record pool exceeds the memory budget"; return ADK_ERR_NOMEM;
         }
         ADK_TRY(ensure(c, c->arena, slice_bytes * 2 * (size_t) slices));
-        ADK_TRY(ensure(c, c->scratch1, sizeof(CtaBest) * slices));
+        ADK_TRY(ensure(c, c->ad_cta, sizeof(CtaBest) * slices));
         ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
-                                c->scratch1.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round));
-        k_ad_reduce<<<1, 32, 0, c->stream>>>(c->scratch1.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
+                                c->ad_cta.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round));
+        k_ad_reduce<<<1, 32, 0, c->stream>>>(c->ad_cta.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
         merge = 1;
@@ -986,7 +1032,13 @@ int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, 
     if (ps.nqueued > 0)
     {
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
-        ADK_TRY(ad_run_queue(c, c->scratch0.as<PairRec>(), ps.nqueued, ps, kmax, nlayers_ref, amax, sm, &keep_layout, &keep_round));
+        ADK_TRY(ensure(c, c->ad_order, sizeof(uint32_t) * (size_t) ps.nqueued));
+        k_ad_order<<<std::min<uint32_t>((ps.nqueued + 255) / 256, 64), 256, 0, c->stream>>>(c->scratch0.as<PairRec>(), ps.nqueued, &sm->stats,
+                                                                                          c->ad_order.as<uint32_t>());
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+        ADK_TRY(ad_run_queue(c, c->scratch0.as<PairRec>(), c->ad_order.as<uint32_t>(), ps.nqueued, ps, kmax, nlayers_ref, amax, sm,
+                             &keep_layout, &keep_round));
         ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
         ADK_CUDA(c, cudaMemcpyAsync(&hb, &sm->best, sizeof(hb), cudaMemcpyDeviceToHost, c->stream));
         ADK_CUDA(c, cudaMemcpyAsync(&hc, &sm->counters, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
@@ -1066,7 +1118,7 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
         ADK_CUDA(c, cudaMemcpyAsync(d_pair, &pr, sizeof(pr), cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(&sm->counters, 0, sizeof(AdCounters), c->stream));
         c->ad_keep_valid = false;
-        ADK_TRY(ad_run_queue(c, d_pair, 1, ps, kmax, nlayers_ref, amax, sm, &Lo, nullptr));
+        ADK_TRY(ad_run_queue(c, d_pair, nullptr, 1, ps, kmax, nlayers_ref, amax, sm, &Lo, nullptr));
         slice = 0;                               // the only candidate of the only CTA: its first slice
     }
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), n};

@@ -44,7 +44,8 @@ struct Ctx
 
     // scratch / arenas
     DevBuf scratch0, scratch1, scratch2, scratch3, scratch4, scratch5, scratch6;
-    DevBuf arena;                  // AD dense layer tables (kept clean between calls)
+    DevBuf arena;                  // AD per-CTA slices (directories + layer vectors)
+    DevBuf ad_order, ad_ovf, ad_cta;   // AD: processing order, overflow lists, per-CTA bests
     uint64_t ad_V = 0, ad_Q = 0;   // per-slice capacities the arena was initialised for (grow-only)
     uint32_t ad_L = 0, ad_slices = 0;
     size_t ad_slice_bytes = 0;

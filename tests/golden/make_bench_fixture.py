@@ -26,7 +26,7 @@ out = {"generated_by": "tests/golden/make_bench_fixture.py", "n": N, "seed": SEE
        "sets": {}}
 O = Oracle()
 R = RefLib("x87") if ref_available() else None
-for sigma, sample_d in ((3.0, [2.0, 3.0]), (2.0, [2.0, 3.0]), (1.0, []), (0.5, [])):
+for sigma, sample_d in ((3.0, [2.0, 3.0]), (2.0, [2.0, 3.0]), (1.5, [2.0]), (1.0, []), (0.5, [])):
     pts = synth.gaussian_points(N, sigma, SEED)
     x = [p[0] for p in pts]
     y = [p[1] for p in pts]
