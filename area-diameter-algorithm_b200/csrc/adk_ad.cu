@@ -462,7 +462,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     const bool spilled = P > (uint32_t) kSrcCap;       // rare: the whole source list then lives in the global spill
     if (spilled) { for (uint32_t t = lane; t < (uint32_t) kSrcCap; t += 32) C.spill[t] = C.src[t]; __syncwarp(); }
     const SrcRec* srcs = spilled ? C.spill : C.src;
-    uint32_t* preds = spilled ? C.spill_pred : C.pred;
+    uint32_t* preds = C.spill_pred;                    // only used when spilled
     const uint32_t ntiles = (khi - klo + kBT) / kBT;
     const uint32_t dirb = dir_base(a, b, nl, nr);
 
@@ -530,7 +530,11 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                     if (counting)
                     {
                         for (uint32_t rr = 0; rr < rows; ++rr)
-                            if (C.acc[rr * 32 + lane] < INFINITY) { first = min(first, k0 + rr); last = k0 + rr; ++nfin; }
+                            if (C.acc[rr * 32 + lane] < INFINITY)
+                            {
+                                first = min(first, k0 + rr); last = k0 + rr; ++nfin;
+                                if (!emitting) C.acc[rr * 32 + lane] = INFINITY;       // counting-only pass of a wide cell
+                            }
                         if (t == ntiles - 1)
                         {   // allocate this tile's vectors: exclusive scan over the lanes, one bump of the CTA's pool
                             const uint32_t cnt = nfin ? last - first + 1 : 0u;
@@ -545,12 +549,16 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                             my_states += fits ? nfin : 0u;
                         }
                     }
-                    if (emitting && fits && nfin)
-                    {
+                    if (emitting && nfin)
+                    {   // copy this lane's rows first..last out (holes stay +inf) and leave the column clean
                         const uint32_t r0 = max(first, k0), r1 = min(last, k0 + rows - 1);
-                        for (uint32_t k = r0; k <= r1 && r0 <= r1; ++k) C.sl.vpool[base + lane_off + (k - first)] = C.acc[(k - k0) * 32 + lane];
+                        for (uint32_t k = r0; k <= r1 && r0 <= r1; ++k)
+                        {
+                            double* q = C.acc + (k - k0) * 32 + lane;
+                            if (fits) C.sl.vpool[base + lane_off + (k - first)] = *q;
+                            *q = INFINITY;
+                        }
                     }
-                    for (uint32_t rr = 0; rr < rows; ++rr) C.acc[rr * 32 + lane] = INFINITY;
                 }
             }
         }
@@ -567,11 +575,34 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
 
 struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best terminal layer (0 = none) of one candidate
 
-__host__ __device__ inline size_t cells_warp_smem() { return sizeof(double) * kBT * 32 + sizeof(SrcRec) * kSrcCap + sizeof(uint32_t) * kSrcCap; }
-__host__ __device__ inline size_t cells_lune_smem(uint32_t capL, uint32_t capR) { return (lune_smem_bytes(capL, capR, 0) + 15) & ~(size_t) 15; }
+// Shared memory of k_ad_cells: [per-warp accumulators | per-warp source lists | lune coordinates + indices | done counters].
+// The staging arrays of build_lune (projection keys, unsorted indices) are only live while the lists are built, so they
+// alias the accumulators, which are re-initialised afterwards.
+__host__ __device__ inline size_t cells_acc_bytes() { return sizeof(double) * kBT * 32 * kCellWarps; }
+__host__ __device__ inline size_t cells_stage_bytes(uint32_t capL, uint32_t capR) { return (size_t) (capL + capR) * (sizeof(double) + sizeof(int32_t)); }
+__host__ __device__ inline size_t cells_front_bytes(uint32_t capL, uint32_t capR)
+{
+    const size_t a = cells_acc_bytes(), b = (cells_stage_bytes(capL, capR) + 15) & ~(size_t) 15;
+    return a > b ? a : b;
+}
 __host__ __device__ inline size_t cells_smem_bytes(uint32_t capL, uint32_t capR)
 {
-    return cells_lune_smem(capL, capR) + kCellWarps * cells_warp_smem() + sizeof(uint32_t) * ((size_t) capL + capR);
+    return cells_front_bytes(capL, capR) + sizeof(SrcRec) * kSrcCap * kCellWarps
+           + (size_t) (capL + capR) * (2 * sizeof(double) + sizeof(int32_t) + sizeof(uint32_t)) + 16;
+}
+
+__device__ __forceinline__ LuneSmem carve_cells_smem(unsigned char* smem_raw, uint32_t capL, uint32_t capR, uint32_t** done)
+{
+    LuneSmem S;
+    S.tproj = reinterpret_cast<double*>(smem_raw);                                  // aliases the accumulators
+    S.tidx = reinterpret_cast<int32_t*>(smem_raw + sizeof(double) * (capL + capR));
+    double* d = reinterpret_cast<double*>(smem_raw + cells_front_bytes(capL, capR) + sizeof(SrcRec) * kSrcCap * kCellWarps);
+    S.Lx = d; d += capL; S.Ly = d; d += capL; S.Rx = d; d += capR; S.Ry = d; d += capR;
+    int32_t* q = reinterpret_cast<int32_t*>(d);
+    S.Lidx = q; q += capL; S.Ridx = q; q += capR;
+    *done = reinterpret_cast<uint32_t*>(q);
+    S.lflag = nullptr;
+    return S;
 }
 
 // Runs the whole layered DP of ONE candidate (already described by pr) inside the calling CTA's slice.
@@ -583,6 +614,7 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
 {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     build_lune(x, y, n, pr, C.S, s_cnt);
+    for (uint32_t t = lane; t < (uint32_t) kBT * 32; t += 32) C.acc[t] = INFINITY;     // build_lune staged its keys here
     const uint32_t nl = pr.nl, nr = pr.nr;
     const uint64_t inner = (uint64_t) nl + nr - 4;
     C.nl = nl; C.nr = nr;
@@ -646,18 +678,16 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
                                           unsigned int* overflow)
 {
     const uint32_t warp = threadIdx.x >> 5;
-    C.S = carve_smem(smem_raw, capL, capR);
-    unsigned char* wbase = smem_raw + cells_lune_smem(capL, capR) + warp * cells_warp_smem();
-    C.acc = reinterpret_cast<double*>(wbase);
-    C.src = reinterpret_cast<SrcRec*>(wbase + sizeof(double) * kBT * 32);
-    C.pred = reinterpret_cast<uint32_t*>(wbase + sizeof(double) * kBT * 32 + sizeof(SrcRec) * kSrcCap);
-    uint32_t* done = reinterpret_cast<uint32_t*>(smem_raw + cells_lune_smem(capL, capR) + kCellWarps * cells_warp_smem());
+    uint32_t* done = nullptr;
+    C.S = carve_cells_smem(smem_raw, capL, capR, &done);
+    C.acc = reinterpret_cast<double*>(smem_raw) + (size_t) warp * kBT * 32;
+    C.src = reinterpret_cast<SrcRec*>(smem_raw + cells_front_bytes(capL, capR)) + (size_t) warp * kSrcCap;
+    C.pred = nullptr;                          // predicate words only exist on the (global) spill path
     C.rowdone = done; C.coldone = done + capL;
     C.sl = carve_cells(arena, Lo, slice);
     C.spill = C.sl.spill + (size_t) warp * Lo.spill_cap;
     C.spill_pred = C.sl.spill_pred + (size_t) warp * Lo.spill_cap;
     C.cap = Lo.cap; C.amax = amax; C.next = next; C.bump = bump; C.overflow = overflow;
-    for (uint32_t t = threadIdx.x & 31; t < (uint32_t) kBT * 32; t += 32) C.acc[t] = INFINITY;
 }
 
 // One candidate pair per CTA, pulled from a device queue.  `order` (optional) lists the queue in processing order.

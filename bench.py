@@ -282,7 +282,7 @@ def run_b200_arm(args):
         secs = res["dev_ms"] / 1e3
         value = res["cells"] / secs
         peak, peak_src = measured_peaks()
-        # dominant kernel: k_ad_dp, timed by the library's own CUDA events on the launching stream, live in this run
+        # dominant kernel: k_ad_cells, timed by the library's own CUDA events on the launching stream, live in this run
         dp_s = res["my_dp_ms"] / 1e3
         launches_dp = args.steps * len(diams)
         achieved = res["my_cells"] * BYTES_PER_CELL / dp_s / 1e9 if dp_s > 0 else 0.0
@@ -290,11 +290,11 @@ def run_b200_arm(args):
         tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
         if os.path.exists(tpath):
             try:
-                traffic = json.load(open(tpath)).get("k_ad_dp_dram_bytes_per_launch")
+                traffic = json.load(open(tpath)).get("k_ad_cells_dram_bytes_per_launch")
             except Exception:
                 traffic = None
         fp64_tflops = res["my_cells"] * FLOPS_PER_CELL / dp_s / 1e12 if dp_s > 0 else 0.0
-        roof = {"bound": "hbm", "kernel": "k_ad_dp", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        roof = {"bound": "hbm", "kernel": "k_ad_cells", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": res["my_cells"] * BYTES_PER_CELL / max(launches_dp, 1),
                 "avg_launch_ms": res["my_dp_ms"] / max(launches_dp, 1), "share_of_step": res["my_dp_ms"] / res["dev_ms"],
@@ -304,7 +304,7 @@ def run_b200_arm(args):
                 "ms_per_step": res["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
                 "config": workload_config(w, {"parallelism": f"candidate pairs sharded over {world} rank(s)",
-                                              "l2": "256 MiB memset on the timed stream before every step; the layer-table arena also exceeds L2",
+                                              "l2": "256 MiB memset on the timed stream before every step (L2 flush)",
                                               "states_per_step": res["states"] // args.steps, "cells_per_step": res["cells"] // args.steps}),
                 "solve_ms_per_instance": res["dev_ms"] / args.steps / len(diams),
                 "states_per_sec": res["states"] / secs,
@@ -333,7 +333,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--sigma", type=float, default=2.0, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.0, 0.5)")
+    ap.add_argument("--sigma", type=float, default=1.5, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.5, 1.0, 0.5)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
