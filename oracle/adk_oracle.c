@@ -689,8 +689,15 @@ static void layer_insert_new(layer_t* Ly, const entry_t* ne)
 }
 
 /* "insert if absent, else overwrite area/prev/side only if strictly smaller" (:207-217 and its three clones) */
+#ifdef ADK_ORACLE_DEVSTATS
+static uint64_t adk_dev_relax;   /* development statistic (tools/ad_cell_stats.c): transitions that pass every test */
+#define DEVSTAT_RELAX() (++adk_dev_relax)
+#else
+#define DEVSTAT_RELAX() ((void) 0)
+#endif
 static void layer_relax(layer_t* Ly, uint64_t key, uint32_t o, uint32_t s, uint32_t ss, uint32_t prev, double area, int side)
 {
+    DEVSTAT_RELAX();
     entry_t* e = layer_find(Ly, key);
     if (!e)
     {

@@ -1,6 +1,7 @@
 /* Development tool (not product, not test): per-cell statistics of the AD layered DP, to size the cell-wavefront kernel.
  * Includes the oracle restatement and walks the layer tables of every stride-th candidate pair.
  * Build: gcc -O2 -o /tmp/ad_cell_stats tools/ad_cell_stats.c -lm ; run: /tmp/ad_cell_stats points.txt amax dmax stride */
+#define ADK_ORACLE_DEVSTATS 1
 #include "../oracle/adk_oracle.c"
 #include <stdio.h>
 
@@ -65,6 +66,7 @@ int main(int argc, char** argv)
     printf("n %u pairs %lu sampled %lu states %lu (avg %.0f max %lu) cells(ref) %lu\n", n, pairs, used, tot_states, (double) tot_states / used, max_states, cells);
     printf("cells alive %lu of %lu (%.1f%%), entries/alive cell %.1f, edges/alive cell %.1f, band*dests per alive cell %.0f\n", tot_cells_alive, tot_cells,
            100.0 * tot_cells_alive / tot_cells, (double) tot_states / tot_cells_alive, (double) tot_edges / tot_cells_alive, (double) sum_band_x_dests / tot_cells_alive);
+    printf("transitions passing every test %lu = %.1f%% of the cell updates\n", adk_dev_relax, 100.0 * adk_dev_relax / cells);
     const char* names[] = { "entries/cell", "edges/cell", "band/cell", "len/(cell,edge)", "dests/cell" };
     uint64_t* hs[] = { hist_ent, hist_edges, hist_band, hist_len, hist_dests };
     for (int h = 0; h < 5; ++h) { printf("%-16s", names[h]); for (int b = 0; b < 12; ++b) printf(" [%d]%lu", 1 << b, hs[h][b]); printf("\n"); }
