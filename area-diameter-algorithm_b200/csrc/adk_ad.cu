@@ -515,56 +515,50 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
         if (!spilled) anyp = __any_sync(kFull, mask != 0ull) ? 1u : 0u;
         __syncwarp();
         // the destination's layer vector: first .. last finite layer, holes stay +inf
-        uint32_t first = 0xffffffffu, last = 0, nfin = 0, lane_off = 0, base = 0;
-        bool fits = true;
+        // A cell deeper than one accumulator tile is still swept once: the vector is given room up to the cell's last
+        // layer when its first finite layer shows up, later tiles append to it (the unused tail is never read).
+        uint32_t first = 0, last = 0, nfin = 0, off = 0;
+        bool fits = true, started = false;
         if (anyp)
         {
-            for (uint32_t pass = 0; pass < (ntiles > 1 ? 2u : 1u); ++pass)
+            for (uint32_t t = 0; t < ntiles; ++t)
             {
-                const bool counting = pass == 0, emitting = ntiles == 1 || pass == 1;
-                for (uint32_t t = 0; t < ntiles; ++t)
-                {
-                    const uint32_t k0 = klo + t * kBT, rows = min((uint32_t) kBT, khi + 1 - k0);
-                    if (!spilled) cell_accumulate<true>(C, srcs, preds, mask, P, lane, k0, rows);
-                    else cell_accumulate<false>(C, srcs, preds, 0ull, P, lane, k0, rows);
-                    if (counting)
+                const uint32_t k0 = klo + t * kBT, rows = min((uint32_t) kBT, khi + 1 - k0);
+                if (!spilled) cell_accumulate<true>(C, srcs, preds, mask, P, lane, k0, rows);
+                else cell_accumulate<false>(C, srcs, preds, 0ull, P, lane, k0, rows);
+                uint32_t tfirst = 0xffffffffu, tlast = 0, tn = 0;
+                for (uint32_t rr = 0; rr < rows; ++rr)
+                    if (C.acc[rr * 32 + lane] < INFINITY) { tfirst = min(tfirst, k0 + rr); tlast = k0 + rr; ++tn; }
+                const uint32_t need = (tn && !started) ? (ntiles == 1 ? tlast - tfirst + 1 : khi - tfirst + 1) : 0u;
+                if (__any_sync(kFull, need != 0u))
+                {   // allocate the vectors that start in this tile: exclusive scan over the lanes, one bump of the CTA's pool
+                    uint32_t incl = need;
+                    for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, o); if ((int) lane >= o) incl += v; }
+                    const uint32_t total = __shfl_sync(kFull, incl, 31);
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(C.bump, total);
+                    base = __shfl_sync(kFull, base, 0);
+                    const bool ok = (unsigned long long) base + total <= C.cap;
+                    if (!ok && lane == 0) *C.overflow = 1u;
+                    if (need) { started = true; first = tfirst; off = base + incl - need; fits = ok; }
+                }
+                if (started)
+                {   // copy this lane's rows out (holes stay +inf) and leave the column clean
+                    const uint32_t r0 = max(first, k0), r1 = ntiles == 1 ? tlast : k0 + rows - 1;
+                    for (uint32_t k = r0; k <= r1; ++k)
                     {
-                        for (uint32_t rr = 0; rr < rows; ++rr)
-                            if (C.acc[rr * 32 + lane] < INFINITY)
-                            {
-                                first = min(first, k0 + rr); last = k0 + rr; ++nfin;
-                                if (!emitting) C.acc[rr * 32 + lane] = INFINITY;       // counting-only pass of a wide cell
-                            }
-                        if (t == ntiles - 1)
-                        {   // allocate this tile's vectors: exclusive scan over the lanes, one bump of the CTA's pool
-                            const uint32_t cnt = nfin ? last - first + 1 : 0u;
-                            uint32_t incl = cnt;
-                            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, o); if ((int) lane >= o) incl += v; }
-                            lane_off = incl - cnt;
-                            const uint32_t total = __shfl_sync(kFull, incl, 31);
-                            if (lane == 0 && total) base = atomicAdd(C.bump, total);
-                            base = __shfl_sync(kFull, base, 0);
-                            fits = (unsigned long long) base + total <= C.cap;
-                            if (!fits && lane == 0) *C.overflow = 1u;
-                            my_states += fits ? nfin : 0u;
-                        }
+                        double* q = C.acc + (k - k0) * 32 + lane;
+                        if (fits) C.sl.vpool[off + (k - first)] = *q;
+                        *q = INFINITY;
                     }
-                    if (emitting && nfin)
-                    {   // copy this lane's rows first..last out (holes stay +inf) and leave the column clean
-                        const uint32_t r0 = max(first, k0), r1 = min(last, k0 + rows - 1);
-                        for (uint32_t k = r0; k <= r1 && r0 <= r1; ++k)
-                        {
-                            double* q = C.acc + (k - k0) * 32 + lane;
-                            if (fits) C.sl.vpool[base + lane_off + (k - first)] = *q;
-                            *q = INFINITY;
-                        }
-                    }
+                    if (tn) { last = tlast; nfin += tn; }
                 }
             }
         }
+        my_states += (started && fits) ? nfin : 0u;
         if (have)
         {
-            DirEnt de; de.off = base + lane_off; de.kmin = (uint16_t) (nfin ? first : 0u); de.len = (uint16_t) ((fits && nfin) ? last - first + 1 : 0u);
+            DirEnt de; de.off = off; de.kmin = (uint16_t) (started ? first : 0u); de.len = (uint16_t) ((fits && started) ? last - first + 1 : 0u);
             C.sl.dir[dirb + d] = de;
             C.sl.nfin[dirb + d] = (uint16_t) nfin;
         }

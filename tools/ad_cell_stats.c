@@ -6,6 +6,7 @@
 #include <stdio.h>
 
 static uint64_t hist_ent[16], hist_edges[16], hist_band[16], hist_len[16], hist_dests[16];
+static uint64_t w_ent[16], w_band[16], w_edges[16], w_tot;
 static int bucket(uint64_t v) { int b = 0; while (v > 1 && b < 15) { v >>= 1; ++b; } return b; }
 
 int main(int argc, char** argv)
@@ -59,6 +60,7 @@ int main(int argc, char** argv)
             const uint32_t a = c / nr, b = c % nr, D = (nr - 1 - b) + (nl - 1 - a);
             ++hist_ent[bucket(cent[c])]; ++hist_edges[bucket(edges)]; ++hist_band[bucket(kmax[c] - kmin[c] + 1)]; ++hist_dests[bucket(D ? D : 1)];
             sum_band_x_dests += (uint64_t) (kmax[c] - kmin[c] + 1) * D;
+            { const uint64_t w = (uint64_t) cent[c] * D; w_tot += w; w_ent[bucket(cent[c])] += w; w_band[bucket(kmax[c] - kmin[c] + 1)] += w; w_edges[bucket(edges)] += w; }
         }
         free(ecnt); free(kmin); free(kmax); free(cent);
         layers_clear(Ls, nlayers);
@@ -70,5 +72,8 @@ int main(int argc, char** argv)
     const char* names[] = { "entries/cell", "edges/cell", "band/cell", "len/(cell,edge)", "dests/cell" };
     uint64_t* hs[] = { hist_ent, hist_edges, hist_band, hist_len, hist_dests };
     for (int h = 0; h < 5; ++h) { printf("%-16s", names[h]); for (int b = 0; b < 12; ++b) printf(" [%d]%lu", 1 << b, hs[h][b]); printf("\n"); }
+    const char* wn[] = { "W entries/cell", "W band/cell", "W edges/cell" };
+    uint64_t* ws[] = { w_ent, w_band, w_edges };
+    for (int h = 0; h < 3; ++h) { printf("%-16s", wn[h]); for (int b = 0; b < 12; ++b) printf(" [%d]%.1f%%", 1 << b, 100.0 * ws[h][b] / w_tot); printf("\n"); }
     return 0;
 }
