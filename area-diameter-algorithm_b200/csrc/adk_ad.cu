@@ -235,6 +235,7 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 constexpr int kCellWarps = 4;                    // warps per CTA (one candidate per CTA)
 constexpr int kCellThreads = kCellWarps * 32;
 constexpr int kBT = 32;                          // layers per accumulator tile
+constexpr int kRS = kBT + 1;                     // accumulator row stride: acc[destination][layer], padded against bank conflicts
 constexpr int kSrcCap = 64;                      // source edges of a cell kept in shared memory (larger cells use the global spill)
 
 // Layer vector of one (cell, destination): areas of layers kmin .. kmin+len-1 at vpool[off ..], +inf where unreached.
@@ -303,7 +304,7 @@ struct CellCtx
     CellSlice sl;
     uint32_t cap;
     // warp-private shared memory
-    double* acc;            // kBT * 32
+    double* acc;            // 32 destinations x kRS layer rows
     SrcRec* src;            // kSrcCap
     uint32_t* pred;         // kSrcCap
     SrcRec* spill;          // this warp's spill region (global)
@@ -319,7 +320,9 @@ struct CellCtx
 constexpr unsigned kFull = 0xffffffffu;
 
 // Accumulates, for the 32 destinations of one tile, the layer rows [k0, k0 + rows) of acc (all +inf on entry):
-// acc[row][lane] = min over sources with a set predicate bit of (area + triangle), at layer k + c (:188-195, :207-217).
+// acc[destination][row] = min over sources with a set predicate bit of (area + triangle), at layer k + c (:188-195, :207-217).
+// Only ~1 in 8 (source, destination) pairs passes the tests, so the sweep is sparse in the destinations: every lane holds
+// one LAYER ENTRY of the source (area + triangle) and relaxes it into the column of each passing destination in turn.
 // REG: the lane's predicate bits over the (at most 64) sources are in `mask`; otherwise preds[p] holds one word per source.
 template <bool REG>
 __device__ __forceinline__ void cell_accumulate(const CellCtx& C, const SrcRec* __restrict__ srcs, const uint32_t* __restrict__ preds,
@@ -327,20 +330,20 @@ __device__ __forceinline__ void cell_accumulate(const CellCtx& C, const SrcRec* 
 {
     const uint32_t dmax = min(C.lim, C.nlayers - 1);          // :192-195; layers beyond lim are never read
     const uint32_t khi = min(k0 + rows - 1, dmax);
-    double* col = C.acc + lane;
     for (uint32_t p = 0; p < P; ++p)
     {
-        bool mine;
-        if (REG) { mine = (mask >> p) & 1ull; if (!__any_sync(kFull, mine)) continue; }
-        else { const uint32_t m = preds[p]; if (!m) continue; mine = (m >> lane) & 1u; }
-        const SrcRec r = srcs[p];
+        uint32_t dm;                                           // destinations of this tile that take source p
+        if (REG) dm = __ballot_sync(kFull, (mask >> p) & 1ull); else dm = preds[p];
+        if (!dm) continue;
+        __syncwarp();                                          // the previous source's relaxations (other lanes, same cells) are done
+        const SrcRec r = REG ? C.src[p] : srcs[p];
         const double tri = r.tri;
         if (r.kmin == 0)
         {   // a layer-0 seed (:149-160): one record, and the count carries the extra collinear term
             const uint32_t dst = (uint32_t) r.c + r.cx;
             if (dst < k0 || dst > khi) continue;
             const double v2 = __dadd_rn(C.sl.vpool[r.off], tri);
-            if (mine && v2 <= C.amax) { double* q = col + (dst - k0) * 32; if (v2 < *q) *q = v2; }
+            if (((dm >> lane) & 1u) && v2 <= C.amax) { double* q = C.acc + lane * kRS + (dst - k0); if (v2 < *q) *q = v2; }
             continue;
         }
         // entries e (layer kmin + e) land on row kmin + e + c - k0
@@ -350,18 +353,18 @@ __device__ __forceinline__ void cell_accumulate(const CellCtx& C, const SrcRec* 
         {
             const int e = e0 + (int) lane;
             double v2 = INFINITY;
+            int row = 0;
             if (e < ehi)
             {
+                row = e + shift;
                 v2 = __dadd_rn(C.sl.vpool[r.off + e], tri);
                 if (!(v2 <= C.amax)) v2 = INFINITY;                // :203, :229, :276, :302
             }
-            const int ne = min(32, ehi - e0);
-            double* q = col + (e0 + shift) * 32;
-#pragma unroll 4
-            for (int t = 0; t < ne; ++t)
+            double* q0 = C.acc + row;
+            for (uint32_t m = dm; m; m &= m - 1u)
             {
-                const double xv = __shfl_sync(kFull, v2, t);
-                if (mine && xv < q[t * 32]) q[t * 32] = xv;
+                double* q = q0 + (__ffs((int) m) - 1) * kRS;
+                if (v2 < *q) *q = v2;
             }
         }
     }
@@ -528,7 +531,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                 else cell_accumulate<false>(C, srcs, preds, 0ull, P, lane, k0, rows);
                 uint32_t tfirst = 0xffffffffu, tlast = 0, tn = 0;
                 for (uint32_t rr = 0; rr < rows; ++rr)
-                    if (C.acc[rr * 32 + lane] < INFINITY) { tfirst = min(tfirst, k0 + rr); tlast = k0 + rr; ++tn; }
+                    if (C.acc[lane * kRS + rr] < INFINITY) { tfirst = min(tfirst, k0 + rr); tlast = k0 + rr; ++tn; }
                 const uint32_t need = (tn && !started) ? (ntiles == 1 ? tlast - tfirst + 1 : khi - tfirst + 1) : 0u;
                 if (__any_sync(kFull, need != 0u))
                 {   // allocate the vectors that start in this tile: exclusive scan over the lanes, one bump of the CTA's pool
@@ -547,7 +550,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
                     const uint32_t r0 = max(first, k0), r1 = ntiles == 1 ? tlast : k0 + rows - 1;
                     for (uint32_t k = r0; k <= r1; ++k)
                     {
-                        double* q = C.acc + (k - k0) * 32 + lane;
+                        double* q = C.acc + lane * kRS + (k - k0);
                         if (fits) C.sl.vpool[off + (k - first)] = *q;
                         *q = INFINITY;
                     }
@@ -572,7 +575,7 @@ struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best te
 // Shared memory of k_ad_cells: [per-warp accumulators | per-warp source lists | lune coordinates + indices | done counters].
 // The staging arrays of build_lune (projection keys, unsorted indices) are only live while the lists are built, so they
 // alias the accumulators, which are re-initialised afterwards.
-__host__ __device__ inline size_t cells_acc_bytes() { return sizeof(double) * kBT * 32 * kCellWarps; }
+__host__ __device__ inline size_t cells_acc_bytes() { return sizeof(double) * kRS * 32 * kCellWarps; }
 __host__ __device__ inline size_t cells_stage_bytes(uint32_t capL, uint32_t capR) { return (size_t) (capL + capR) * (sizeof(double) + sizeof(int32_t)); }
 __host__ __device__ inline size_t cells_front_bytes(uint32_t capL, uint32_t capR)
 {
@@ -608,7 +611,7 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
 {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     build_lune(x, y, n, pr, C.S, s_cnt);
-    for (uint32_t t = lane; t < (uint32_t) kBT * 32; t += 32) C.acc[t] = INFINITY;     // build_lune staged its keys here
+    for (uint32_t t = lane; t < (uint32_t) kRS * 32; t += 32) C.acc[t] = INFINITY;     // build_lune staged its keys here
     const uint32_t nl = pr.nl, nr = pr.nr;
     const uint64_t inner = (uint64_t) nl + nr - 4;
     C.nl = nl; C.nr = nr;
@@ -674,7 +677,7 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
     const uint32_t warp = threadIdx.x >> 5;
     uint32_t* done = nullptr;
     C.S = carve_cells_smem(smem_raw, capL, capR, &done);
-    C.acc = reinterpret_cast<double*>(smem_raw) + (size_t) warp * kBT * 32;
+    C.acc = reinterpret_cast<double*>(smem_raw) + (size_t) warp * kRS * 32;
     C.src = reinterpret_cast<SrcRec*>(smem_raw + cells_front_bytes(capL, capR)) + (size_t) warp * kSrcCap;
     C.pred = nullptr;                          // predicate words only exist on the (global) spill path
     C.rowdone = done; C.coldone = done + capL;
