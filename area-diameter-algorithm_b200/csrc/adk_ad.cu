@@ -387,20 +387,35 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b)
     uint32_t P = 0, klo = 0xffffffffu, khi = 0;
     const uint32_t npot = a + b;
+    // The directory reads of the NEXT block of 32 potential sources are issued before this block is worked on: they
+    // are L2 / HBM round trips (the entries were written by other warps), the geometry below hides them.
+    auto fetch = [&](uint32_t u0, unsigned char& al, DirEnt& dd, uint32_t& nf)
+    {
+        const uint32_t u = u0 + lane;
+        al = 0; dd.off = 0; dd.kmin = 0; dd.len = 0; nf = 0;
+        if (u < npot)
+        {
+            const bool left = u >= b; const uint32_t s = left ? u - b : u;
+            const uint32_t pa = left ? s : a, pb = left ? b : s;
+            const uint32_t dix = dir_base(pa, pb, nl, nr) + (left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1));
+            al = C.sl.alive[pa * nr + pb];       // the flag and the entry are loaded together: the entry
+            dd = C.sl.dir[dix];                  // of a cell that produced nothing is stale and ignored
+            nf = C.sl.nfin[dix];
+        }
+    };
+    unsigned char al_n; DirEnt dd_n; uint32_t nf_n;
+    fetch(0, al_n, dd_n, nf_n);
     for (uint32_t u0 = 0; u0 < npot; u0 += 32)
     {
         const uint32_t u = u0 + lane;
         bool live = false, left = false;
-        uint32_t s = 0, dix = 0, nfin_src = 0;
+        uint32_t s = 0, nfin_src = 0;
         DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
+        const unsigned char al = al_n; const DirEnt dd = dd_n; nfin_src = nf_n;
+        if (u0 + 32 < npot) fetch(u0 + 32, al_n, dd_n, nf_n);
         if (u < npot)
         {
             left = u >= b; s = left ? u - b : u;
-            const uint32_t pa = left ? s : a, pb = left ? b : s;
-            dix = dir_base(pa, pb, nl, nr) + (left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1));
-            const unsigned char al = C.sl.alive[pa * nr + pb];      // the flag and the entry are loaded together: the entry
-            const DirEnt dd = C.sl.dir[dix];                        // of a cell that produced nothing is stale and ignored
-            nfin_src = C.sl.nfin[dix];
             if (al) { de = dd; live = de.len > 0; }
             if (live)
             {   // pull the layer vector towards L1 while the geometry below is computed
