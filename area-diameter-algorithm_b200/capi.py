@@ -42,12 +42,23 @@ class AdkStats(ctypes.Structure):
     ]
 
 
+class AdkInstance(ctypes.Structure):
+    _fields_ = [
+        ("x", ctypes.c_void_p), ("y", ctypes.c_void_p), ("n", ctypes.c_uint32), ("algo", ctypes.c_uint32),
+        ("kmax", ctypes.c_uint64), ("amax", ctypes.c_double), ("dmax", ctypes.c_double),
+        ("flags", ctypes.c_uint32), ("hull_cap", ctypes.c_uint32), ("hull", ctypes.c_void_p),
+    ]
+
+
+ALGO_AREA, ALGO_AREA_DIAMETER = 0, 1
+
 EXPORTS = [
     "adk_create", "adk_destroy", "adk_last_error", "adk_set_memory_budget", "adk_set_stream", "adk_launch_count",
     "adk_area_finish_dev", "adk_area_diameter_finish_dev",
     "adk_solve_area", "adk_solve_area_diameter",
     "adk_area_partial", "adk_area_finish", "adk_area_diameter_partial", "adk_area_diameter_finish",
     "adk_merge", "adk_area_partial_dev", "adk_area_diameter_partial_dev",
+    "adk_batch_assign", "adk_solve_batch",
     "adk_count_tables", "adk_points_in_triangle", "adk_cw_order", "adk_slope_order", "adk_lune_lists",
 ]
 
@@ -69,6 +80,37 @@ def _darr(v):
 
 def _k(kmax):
     return KMAX_INF if kmax is None or kmax >= KMAX_INF else int(kmax)
+
+
+def make_instances(point_sets, algo, kmax, amax, dmax, reconstruct, counters):
+    """point_sets: sequence of (n, 2) float64 arrays (NumPy; anything np.asarray takes).  The coordinates are split into
+    contiguous SoA columns once; the C side borrows those buffers (no per-point marshalling)."""
+    import numpy as np
+    m = len(point_sets)
+    inst = (AdkInstance * max(m, 1))()
+    keep = []
+    flags = (FLAG_RECONSTRUCT if reconstruct else 0) | (FLAG_COUNTERS if counters else 0)
+    for i, pts in enumerate(point_sets):
+        a = np.asarray(pts, dtype=np.float64).reshape(-1, 2)
+        x = np.ascontiguousarray(a[:, 0]); y = np.ascontiguousarray(a[:, 1])
+        hull = np.zeros(max(len(x) + 4, 4), dtype=np.uint32)
+        keep.append((x, y, hull))
+        inst[i].x = x.ctypes.data; inst[i].y = y.ctypes.data; inst[i].n = len(x); inst[i].algo = algo
+        inst[i].kmax = _k(kmax); inst[i].amax = float(amax); inst[i].dmax = float(dmax)
+        inst[i].flags = flags; inst[i].hull_cap = len(hull); inst[i].hull = hull.ctypes.data
+    return inst, keep
+
+
+def batch_assign(point_sets, nshards, algo=ALGO_AREA_DIAMETER):
+    """adk_batch_assign: which rank solves which instance (host side, needs no device)."""
+    lib = load_library()
+    inst, _keep = make_instances(point_sets, algo, None, 0.0, 0.0, False, False)
+    owner = (ctypes.c_uint32 * max(len(point_sets), 1))()
+    lib.adk_batch_assign.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]
+    rc = lib.adk_batch_assign(ctypes.cast(inst, ctypes.c_void_p), len(point_sets), nshards, ctypes.cast(owner, ctypes.c_void_p))
+    if rc != ADK_OK:
+        raise AdkError(f"adk_batch_assign failed (status {rc})")
+    return [int(owner[i]) for i in range(len(point_sets))]
 
 
 class Solver:
@@ -163,6 +205,21 @@ class Solver:
                                               ctypes.byref(res), hull)
         self._check(rc, "adk_solve_area_diameter")
         return self._pack(res, hull)
+
+    # ---- batches of independent instances (BASELINE config 5) -----------------------------------------
+    _instances = staticmethod(lambda *a: make_instances(*a))
+
+    def solve_batch(self, point_sets, algo=ALGO_AREA_DIAMETER, kmax=None, amax=float("inf"), dmax=float("inf"),
+                    reconstruct=True, counters=False, shard=0, nshards=1):
+        """One call for a list of independent point sets.  Returns one dict per instance (None for instances owned by
+        another shard)."""
+        m = len(point_sets)
+        inst, keep = self._instances(point_sets, algo, kmax, amax, dmax, reconstruct, counters)
+        res = (AdkResult * max(m, 1))()
+        self.lib.adk_solve_batch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]
+        rc = self.lib.adk_solve_batch(self.ctx, ctypes.cast(inst, ctypes.c_void_p), m, shard, nshards, ctypes.cast(res, ctypes.c_void_p))
+        self._check(rc, "adk_solve_batch")
+        return [None if res[i].found < 0 else self._pack(res[i], keep[i][2]) for i in range(m)]
 
     # ---- sharded solves ------------------------------------------------------------------------------------------
     def area_partial(self, x, y, kmax, amax, shard, nshards):

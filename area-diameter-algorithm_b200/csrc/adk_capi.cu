@@ -300,6 +300,54 @@ int adk_solve_area_diameter(adk_ctx* h, const double* x, const double* y, uint32
     return ADK_OK;
 }
 
+static double batch_cost(const adk_instance& in)
+{
+    const double n = (double) in.n;
+    return in.algo == ADK_ALGO_AREA_DIAMETER ? n * n * n * n : n * n * n;
+}
+
+int adk_batch_assign(const adk_instance* inst, uint32_t ninst, uint32_t nshards, uint32_t* owner)
+{
+    if (((!inst || !owner) && ninst) || nshards == 0) return ADK_ERR_ARG;
+    std::vector<uint32_t> order(ninst);
+    for (uint32_t i = 0; i < ninst; ++i) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return batch_cost(inst[a]) > batch_cost(inst[b]); });
+    std::vector<double> load(nshards, 0.0);
+    for (uint32_t i : order)
+    {   // heaviest instance first, onto the least loaded rank (lowest rank on ties)
+        uint32_t best = 0;
+        for (uint32_t r = 1; r < nshards; ++r) if (load[r] < load[best]) best = r;
+        owner[i] = best; load[best] += batch_cost(inst[i]);
+    }
+    return ADK_OK;
+}
+
+int adk_solve_batch(adk_ctx* h, const adk_instance* inst, uint32_t ninst, uint32_t shard, uint32_t nshards, adk_result* out)
+{
+    if (!h) return ADK_ERR_ARG;
+    if ((!inst && ninst) || !out || nshards == 0 || shard >= nshards) { h->c.err = "adk_solve_batch: bad argument"; return ADK_ERR_ARG; }
+    std::vector<uint32_t> owner(ninst);
+    int rc = adk_batch_assign(inst, ninst, nshards, owner.data());
+    if (rc != ADK_OK) return rc;
+    std::vector<uint32_t> mine;
+    for (uint32_t i = 0; i < ninst; ++i)
+    {
+        std::memset(&out[i], 0, sizeof(adk_result));
+        if (owner[i] == shard) mine.push_back(i); else out[i].found = -1;
+    }
+    std::stable_sort(mine.begin(), mine.end(), [&](uint32_t a, uint32_t b) { return batch_cost(inst[a]) > batch_cost(inst[b]); });
+    for (uint32_t i : mine)
+    {
+        const adk_instance& in = inst[i];
+        if ((in.flags & ADK_FLAG_RECONSTRUCT) && (!in.hull || in.hull_cap < in.n)) { h->c.err = "adk_solve_batch: hull buffer too small"; return ADK_ERR_ARG; }
+        if (in.algo == ADK_ALGO_AREA) rc = adk_solve_area(h, in.x, in.y, in.n, in.kmax, in.amax, in.flags, &out[i], in.hull);
+        else if (in.algo == ADK_ALGO_AREA_DIAMETER) rc = adk_solve_area_diameter(h, in.x, in.y, in.n, in.kmax, in.amax, in.dmax, in.flags, &out[i], in.hull);
+        else { h->c.err = "adk_solve_batch: unknown algo"; rc = ADK_ERR_ARG; }
+        if (rc != ADK_OK) return rc;
+    }
+    return ADK_OK;
+}
+
 int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out)
 {
     if (!parts || !out) return ADK_ERR_ARG;

@@ -55,3 +55,19 @@ def gather_stats_sum(values, device=None, group=None):
     t = torch.tensor(list(values), dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
     return t.cpu().tolist()
+
+
+def gather_batch_results(results, group=None):
+    """Instance-level sharding (adk_solve_batch with shard = rank): every rank holds the results of the instances it owns
+    (None elsewhere); returns the complete list on every rank.  A host gather of small records: no data-path collective."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return list(results)
+    world = dist.get_world_size(group)
+    parts = [None] * world
+    dist.all_gather_object(parts, list(results), group=group)
+    out = [None] * len(results)
+    for part in parts:
+        for i, r in enumerate(part):
+            if r is not None:
+                out[i] = r
+    return out

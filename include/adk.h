@@ -11,6 +11,7 @@
  *                                MT::AntipodalAlgorithmWithBenchmarkInfo           src/common/Antipodal.h:18-25 (served by the same kernels)
  *   adk_*_partial / adk_merge / adk_*_finish : the same two solves split into "my shard of anchors / candidate pairs",
  *                                a host-side lexicographic merge and the witness reconstruction, for one-process-per-GPU sharding.
+ *   adk_solve_batch           <- the per-slide loop over thesis.AreaDiameterAlgorithmOptimized (Area-Selector, quality_of_results_comparison.py:48-55)
  *   adk_count_tables          <- MT::CountPointsBelowAllSegments                  src/common/Utils.h:41-43,   Utils.cpp:74-143
  *   adk_points_in_triangle    <- MT::PointsInTriangle                             src/common/Utils.h:45-49,   Utils.cpp:251-293
  *   adk_cw_order              <- MT::SortPointsClockWiseAroundPoint               src/common/Utils.h:53,      Utils.cpp:311-316
@@ -106,6 +107,36 @@ int adk_area_diameter_partial(adk_ctx* ctx, const double* x, const double* y, ui
                               double dmax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats);
 int adk_area_diameter_finish(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
                              double dmax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
+
+/* ---- batches of independent instances (BASELINE config 5: the cell samples of one study, one instance per slide;
+ *      replaces the Python loop over thesis.AreaDiameterAlgorithmOptimized in
+ *      external/Area-Selector/run/quality_of_results_comparison.py:48-55,194-197 and the per-call marshalling of
+ *      src/py-binding/main.cpp:10-18) -------------------------------------------------------------------------------- */
+#define ADK_ALGO_AREA 0u              /* MT::EppsteinAlgorithm */
+#define ADK_ALGO_AREA_DIAMETER 1u     /* MT::AntipodalOptimizedAlgorithm (also serves MT::AntipodalAlgorithm) */
+
+typedef struct adk_instance
+{
+    const double* x;            /* host SoA coordinates, borrowed for the call */
+    const double* y;
+    uint32_t n;
+    uint32_t algo;              /* ADK_ALGO_* */
+    uint64_t kmax;              /* aMaxPointsCount (ADK_KMAX_INF = no bound) */
+    double amax, dmax;          /* aMaxArea, aMaxDiameter (dmax ignored by ADK_ALGO_AREA) */
+    uint32_t flags;             /* ADK_FLAG_* */
+    uint32_t hull_cap;          /* capacity of hull[] (>= n when ADK_FLAG_RECONSTRUCT) */
+    uint32_t* hull;             /* caller buffer or NULL */
+} adk_instance;
+
+/* Instance-level sharding ("C5 batching"): longest-processing-time-first assignment of `ninst` instances to
+ * `nshards` ranks by estimated cost (n^3 for the area path, n^4 for the area+diameter path).  owner[i] = rank of instance i.
+ * Deterministic and identical on every rank; host side, no device work. */
+int adk_batch_assign(const adk_instance* inst, uint32_t ninst, uint32_t nshards, uint32_t* owner /* ninst */);
+
+/* Solves the instances owned by `shard` (all of them when nshards == 1), heaviest first, on this context's device.
+ * out[i].found = -1 marks an instance owned by another shard (its adk_result is otherwise zero).  There is no data-path
+ * exchange between ranks: the caller gathers the results it needs (a host gather of adk_result records). */
+int adk_solve_batch(adk_ctx* ctx, const adk_instance* inst, uint32_t ninst, uint32_t shard, uint32_t nshards, adk_result* out);
 
 /* Lexicographic best of `count` partials: count desc, area asc, tie_key asc (host side, no device work). */
 int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out);

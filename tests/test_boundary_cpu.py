@@ -109,3 +109,53 @@ def test_two_rank_gather_and_merge_over_gloo(built):
         assert nparts == 2
         assert best == dict(found=1, count=9, area=2.5, tie_key=17, w0=1, w1=7)
         assert tot == [30.0, 2.0]
+
+
+def test_batch_assignment_is_lpt_and_deterministic(pkg):
+    """adk_batch_assign (SURVEY 8e, C5 batching): heaviest instance first onto the least loaded rank; no device needed."""
+    import numpy as np
+    sizes = [699, 623, 594, 526, 492, 474, 412, 382, 377, 362]            # the real cell samples (SURVEY 8d, C5)
+    sets = [np.zeros((n, 2)) for n in sizes]
+    own = pkg.batch_assign(sets, 8)
+    assert own == pkg.batch_assign(sets, 8)
+    assert own[:8] == list(range(8))                                      # the eight largest start one rank each
+    load = [0.0] * 8
+    for n, o in zip(sizes, own):
+        load[o] += float(n) ** 4
+    assert max(load) == 699.0 ** 4                                        # nothing is stacked on the densest slide
+    assert pkg.batch_assign(sets, 1) == [0] * 10
+    assert pkg.batch_assign([], 4) == []
+    # order of the input does not matter for who gets the big ones
+    own_r = pkg.batch_assign(sets[::-1], 2)
+    tot = [sum(float(n) ** 4 for n, o in zip(sizes[::-1], own_r) if o == r) for r in range(2)]
+    assert abs(tot[0] - tot[1]) <= 699.0 ** 4
+
+
+def _gloo_batch_worker(rank, world, port, q):
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    ge.load_package()
+    from importlib import import_module
+    d = import_module("area_diameter_algorithm_b200.dist")
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    mine = [({"count": 10 + i, "owner": rank} if i % world == rank else None) for i in range(5)]
+    allr = d.gather_batch_results(mine)
+    dist.destroy_process_group()
+    q.put((rank, allr))
+
+
+def test_two_rank_batch_gather_over_gloo(built):
+    """Instance-level sharding: each rank holds the results it owns, the host gather completes the list on every rank."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_batch_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, allr in got:
+        assert allr == [{"count": 10 + i, "owner": i % 2} for i in range(5)]

@@ -166,6 +166,45 @@ def test_shards_merge_to_the_whole_solve(golden, solver, nshards):
         assert sum(p[1]["cells_executed"] for p in ps) == whole["cells_executed"]
 
 
+# ------------------------------------------------------------------------------------------------ batches (config 5)
+def test_batch_of_cell_samples_equals_the_reference_and_single_solves(golden, solver):
+    """adk_solve_batch on real cell samples, the call of Area-Selector's quality_of_results_comparison.py:48-55 (A = 4, D = 4,
+    K = inf, reconstruct) plus a tighter D; answers = the unmodified reference's frozen outputs = the one-by-one solves."""
+    import numpy as np
+    for tag in ("real.ADopt", "real.ADopt.d1"):
+        runs = [r for r in golden["runs"][tag] if len(golden["points"][r["name"]]) <= 500]
+        assert len(runs) >= 4
+        sets = [np.array(golden["points"][r["name"]], dtype=np.float64) for r in runs]
+        amax, dmax = runs[0]["amax"], runs[0]["dmax"]
+        assert all(r["amax"] == amax and r["dmax"] == dmax for r in runs)
+        got = solver.solve_batch(sets, pkg_algo(solver, "AD"), None, amax, dmax, True)
+        for r, g in zip(runs, got):
+            assert_same_solution(g, r, (tag, r["name"]))
+        # sharded by instance: every instance solved by exactly one rank, union == whole batch
+        parts = [solver.solve_batch(sets, pkg_algo(solver, "AD"), None, amax, dmax, True, shard=s, nshards=3) for s in range(3)]
+        for i, g in enumerate(got):
+            owners = [s for s in range(3) if parts[s][i] is not None]
+            assert len(owners) == 1
+            assert_same_solution(parts[owners[0]][i], g, (tag, "shard", i))
+
+
+def test_batch_area_path_and_edge_cases(golden, solver):
+    import numpy as np
+    names = ["tests/20/1", "tests/50/2", "tests/10/3", "uniform/0/2"]
+    sets = [np.array(golden["points"][n], dtype=np.float64) for n in names] + [np.zeros((0, 2)), np.array([[0.0, 0.0], [1.0, 1.0]])]
+    got = solver.solve_batch(sets, pkg_algo(solver, "A"), None, 30.0, float("inf"), True)
+    for n, g in zip(names, got):
+        x, y = xy(golden["points"][n])
+        assert_same_solution(g, solver.solve_area(x, y, None, 30.0, True), ("batch A", n))
+    assert got[-1]["found"] == 0 and got[-2]["found"] == 0          # n < 3 -> nullopt (Eppstein.cpp:137-140)
+    assert solver.solve_batch([], pkg_algo(solver, "A")) == []
+
+
+def pkg_algo(solver, which):
+    capi = sys.modules["area_diameter_algorithm_b200.capi"]
+    return capi.ALGO_AREA if which == "A" else capi.ALGO_AREA_DIAMETER
+
+
 # ------------------------------------------------------------------------------------------------ full-size properties
 def _synth():
     import __graft_entry__ as ge
