@@ -232,9 +232,15 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 //   d <  nr-1-b : RIGHT(a; b -> b+1+d)          d >= nr-1-b : LEFT(b; a -> a+1+(d-(nr-1-b)))
 // and the whole layer vector of a destination is produced inside this one cell.
 
-constexpr int kCellWarps = 4;                    // warps per CTA (one candidate per CTA)
+#ifndef ADK_CELL_WARPS
+#define ADK_CELL_WARPS 4
+#endif
+constexpr int kCellWarps = ADK_CELL_WARPS;       // warps per CTA (one candidate per CTA)
 constexpr int kCellThreads = kCellWarps * 32;
-constexpr int kBT = 32;                          // layers per accumulator tile
+#ifndef ADK_KBT
+#define ADK_KBT 32
+#endif
+constexpr int kBT = ADK_KBT;                     // layers per accumulator tile
 constexpr int kRS = kBT + 1;                     // accumulator row stride: acc[destination][layer], padded against bank conflicts
 constexpr int kSrcCap = 64;                      // source edges of a cell kept in shared memory (larger cells use the global spill)
 
@@ -421,8 +427,18 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
             {   // pull the layer vector towards L1 while the geometry below is computed
                 const char* v0 = reinterpret_cast<const char*>(C.sl.vpool + de.off);
                 const char* v1 = reinterpret_cast<const char*>(C.sl.vpool + de.off + de.len - 1);
+#ifndef ADK_PREFETCH
+#define ADK_PREFETCH 1
+#endif
+#if ADK_PREFETCH == 1
                 for (const char* q = v0; q <= v1; q += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
                 asm volatile("prefetch.global.L1 [%0];" ::"l"(v1));
+#elif ADK_PREFETCH == 2
+                for (const char* q = v0; q <= v1; q += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(v1));
+#else
+                (void) v0; (void) v1;
+#endif
             }
         }
         const uint32_t kmax = (uint32_t) de.kmin + de.len - 1;
@@ -703,7 +719,7 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
 }
 
 // One candidate pair per CTA, pulled from a device queue.  `order` (optional) lists the queue in processing order.
-__global__ void __launch_bounds__(kCellThreads)
+__global__ void __launch_bounds__(kCellThreads, 16 / kCellWarps)
 k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
            const PairRec* __restrict__ pairs, const uint32_t* __restrict__ order, uint32_t npairs, AdCounters* __restrict__ counters,
            unsigned char* arena, CellLayout Lo, uint32_t capL, uint32_t capR,

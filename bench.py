@@ -28,7 +28,19 @@ METRIC = "dp_cell_updates_per_sec"
 UNIT = "cells/s"
 BYTES_PER_CELL = 20      # read-modify-write of the 8-byte destination area + 4-byte packed back-pointer
 FLOPS_PER_CELL = 20      # two Orientation tests (2 x 9) + area add + compare
-FP64_NOMINAL_TFLOPS = 37.2   # 148 SM x 64 FP64 lanes x 2 x 1.965 GHz (no measured FP64 entry in MEASURED_PEAKS.json)
+FP64_NOMINAL_TFLOPS = 37.2   # 148 SM x 64 FP64 lanes x 2 x 1.965 GHz (no FP64 entry in MEASURED_PEAKS.json)
+
+
+def fp64_peak():
+    """FP64 issue peak measured on this pool's B200 by tools/issue_peaks.cu (dependency-free DFMA chains), else nominal."""
+    p = os.path.join(ROOT, "profiles", "issue_peaks.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["fp64_tflops_fma"]), ("measured DFMA issue peak (profiles/issue_peaks.json, tools/issue_peaks.cu: "
+                                              f"{d['dfma_per_sm_per_clk_at_max']:.1f} DFMA/SM/clk); 20 flop/cell (SURVEY 8d)")
+    except Exception:
+        return FP64_NOMINAL_TFLOPS, "nominal 148 SM x 64 lanes x 2 x 1.965 GHz; 20 flop/cell (SURVEY 8d)"
 
 
 def load_workload(sigma):
@@ -294,12 +306,13 @@ def run_b200_arm(args):
             except Exception:
                 traffic = None
         fp64_tflops = res["my_cells"] * FLOPS_PER_CELL / dp_s / 1e12 if dp_s > 0 else 0.0
+        fp64_pk, fp64_src = fp64_peak()
         roof = {"bound": "hbm", "kernel": "k_ad_cells", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": res["my_cells"] * BYTES_PER_CELL / max(launches_dp, 1),
                 "avg_launch_ms": res["my_dp_ms"] / max(launches_dp, 1), "share_of_step": res["my_dp_ms"] / res["dev_ms"],
-                "fp64_issue": {"achieved": fp64_tflops, "peak": FP64_NOMINAL_TFLOPS, "unit": "TFLOP/s", "frac": fp64_tflops / FP64_NOMINAL_TFLOPS,
-                               "peak_source": "nominal 148 SM x 64 lanes x 2 x 1.965 GHz; 20 flop/cell (SURVEY 8d)"}}
+                "fp64_issue": {"achieved": fp64_tflops, "peak": fp64_pk, "unit": "TFLOP/s", "frac": fp64_tflops / fp64_pk,
+                               "peak_source": fp64_src}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": res["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",

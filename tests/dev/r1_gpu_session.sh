@@ -11,4 +11,6 @@ $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu1.log 2>&1
 $CMD > gpurun_out/${TAG}_plain2.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_ad_cells -s $SKIP -c 1 -f -o gpurun_out/${TAG}_prof_cells $CMD > gpurun_out/${TAG}_ncu2.log 2>&1
+$CMD > gpurun_out/${TAG}_plain3.log 2>&1 &&
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:k_ad_cells -s 5 -c 5 --csv --log-file gpurun_out/${TAG}_traffic.csv $CMD > gpurun_out/${TAG}_ncu3.log 2>&1
 tail -3 gpurun_out/${TAG}_pytest.log; cut -c1-900 gpurun_out/${TAG}_bench.json; tail -n 2 gpurun_out/${TAG}_ncu1.log gpurun_out/${TAG}_ncu2.log
