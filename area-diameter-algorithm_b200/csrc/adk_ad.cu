@@ -252,15 +252,16 @@ static_assert(sizeof(SrcRec) == 32 && sizeof(DirEnt) == 8, "record layouts");
 // Per-CTA slice of the arena.
 struct CellSlice
 {
-    unsigned char* alive;     // nl*nr flags: cell wrote its directory
-    DirEnt* dir;              // directory entries at fixed positions (dir_base)
+    unsigned char* alive;     // nl*nr flags: cell wrote its directory ([a][b])
+    unsigned char* aliveT;    // the same flags transposed ([b][a]): a column's flags are contiguous for the gather
+    DirEnt* dir;              // directory entries at fixed positions (dir_right / dir_left)
     uint16_t* nfin;           // per directory entry: number of finite layers (for the cell-update counter)
     double* vpool;            // layer vectors
     SrcRec* spill;            // kCellWarps * spill_cap source records
     uint32_t* spill_pred;     // kCellWarps * spill_cap predicate words
 };
 
-struct CellLayout { size_t off_dir, off_nfin, off_v, off_spill, off_pred, bytes; uint32_t cap, spill_cap; };
+struct CellLayout { size_t off_aliveT, off_dir, off_nfin, off_v, off_spill, off_pred, bytes; uint32_t cap, spill_cap; };
 
 __host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, uint32_t max_src, size_t slice_bytes)
 {
@@ -268,6 +269,7 @@ __host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, 
     auto up = [](size_t v) { return (v + 255) & ~(size_t) 255; };
     Lo.spill_cap = max_src;
     size_t o = up((size_t) max_cells);
+    Lo.off_aliveT = o; o = up(o + (size_t) max_cells);
     Lo.off_dir = o; o = up(o + sizeof(DirEnt) * (size_t) max_dirs);
     Lo.off_nfin = o; o = up(o + sizeof(uint16_t) * (size_t) max_dirs);
     Lo.off_spill = o; o = up(o + sizeof(SrcRec) * (size_t) kCellWarps * max_src);
@@ -285,6 +287,7 @@ __device__ __forceinline__ CellSlice carve_cells(unsigned char* arena, const Cel
     unsigned char* base = arena + (size_t) cta * Lo.bytes;
     CellSlice s;
     s.alive = base;
+    s.aliveT = base + Lo.off_aliveT;
     s.dir = reinterpret_cast<DirEnt*>(base + Lo.off_dir);
     s.nfin = reinterpret_cast<uint16_t*>(base + Lo.off_nfin);
     s.vpool = reinterpret_cast<double*>(base + Lo.off_v);
@@ -293,11 +296,16 @@ __device__ __forceinline__ CellSlice carve_cells(unsigned char* arena, const Cel
     return s;
 }
 
-// First directory entry of cell (a,b); cells are laid out row-major, cell (a,b) has (nr-1-b) + (nl-1-a) destinations.
-__device__ __forceinline__ uint32_t dir_base(uint32_t a, uint32_t b, uint32_t nl, uint32_t nr)
+// Directory position of the state vector "pending edge s -> e on one chain, head h on the other chain".  Consumer-major:
+// cell (a,b) reads RIGHT(a; s->b), s = 0..b-1, and LEFT(b; s->a), s = 0..a-1, as two contiguous runs (the producing cells
+// scatter their entries instead; stores do not stall a warp, the gather's loads do).
+__device__ __forceinline__ uint32_t dir_right(uint32_t h, uint32_t e, uint32_t s, uint32_t nr)
 {
-    const uint32_t rows = a * (nr * (nr - 1) / 2) + nr * (a * (nl - 1) - a * (a - 1) / 2);
-    return rows + b * (nr - 1) - b * (b - 1) / 2 + b * (nl - 1 - a);
+    return h * (nr * (nr - 1) / 2) + e * (e - 1) / 2 + s;
+}
+__device__ __forceinline__ uint32_t dir_left(uint32_t h, uint32_t e, uint32_t s, uint32_t nl, uint32_t nr)
+{
+    return nl * (nr * (nr - 1) / 2) + h * (nl * (nl - 1) / 2) + e * (e - 1) / 2 + s;
 }
 
 struct CellCtx
@@ -402,9 +410,8 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
         if (u < npot)
         {
             const bool left = u >= b; const uint32_t s = left ? u - b : u;
-            const uint32_t pa = left ? s : a, pb = left ? b : s;
-            const uint32_t dix = dir_base(pa, pb, nl, nr) + (left ? (nr - 1 - b) + (a - s - 1) : (b - s - 1));
-            al = C.sl.alive[pa * nr + pb];       // the flag and the entry are loaded together: the entry
+            const uint32_t dix = left ? dir_left(b, a, s, nl, nr) : dir_right(a, b, s, nr);
+            al = left ? C.sl.aliveT[b * nl + s] : C.sl.alive[a * nr + s];       // the flag and the entry are loaded together: the entry
             dd = C.sl.dir[dix];                  // of a cell that produced nothing is stale and ignored
             nf = C.sl.nfin[dix];
         }
@@ -498,7 +505,6 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     const SrcRec* srcs = spilled ? C.spill : C.src;
     uint32_t* preds = C.spill_pred;                    // only used when spilled
     const uint32_t ntiles = (khi - klo + kBT) / kBT;
-    const uint32_t dirb = dir_base(a, b, nl, nr);
 
     for (uint32_t d0 = 0; d0 < D; d0 += 32)
     {
@@ -593,12 +599,13 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
         if (have)
         {
             DirEnt de; de.off = off; de.kmin = (uint16_t) (started ? first : 0u); de.len = (uint16_t) ((fits && started) ? last - first + 1 : 0u);
-            C.sl.dir[dirb + d] = de;
-            C.sl.nfin[dirb + d] = (uint16_t) nfin;
+            const uint32_t dix = dR ? dir_right(a, i, b, nr) : dir_left(b, i, a, nl, nr);
+            C.sl.dir[dix] = de;
+            C.sl.nfin[dix] = (uint16_t) nfin;
         }
     }
     __syncwarp();
-    if (lane == 0) C.sl.alive[a * nr + b] = 1;
+    if (lane == 0) { C.sl.alive[a * nr + b] = 1; C.sl.aliveT[b * nl + a] = 1; }
 }
 
 struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best terminal layer (0 = none) of one candidate
@@ -653,9 +660,13 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
     C.seg2 = dist2(C.Sx, C.Sy, C.Ex, C.Ey);
     // reset the slice: no cell has produced anything; cell (0,0) "produces" the layer-0 seeds (:149-160):
     // RIGHT(0; 0->i) and LEFT(0; 0->i) all share one record (layer 0, area 0)
-    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) C.sl.alive[t] = t == 0 ? 1 : 0;
+    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) { C.sl.alive[t] = t == 0 ? 1 : 0; C.sl.aliveT[t] = t == 0 ? 1 : 0; }
     const uint32_t D0 = (nr - 1) + (nl - 1);
-    for (uint32_t t = threadIdx.x; t < D0; t += blockDim.x) { DirEnt de; de.off = 0; de.kmin = 0; de.len = 1; C.sl.dir[t] = de; C.sl.nfin[t] = 1; }
+    for (uint32_t t = threadIdx.x; t < D0; t += blockDim.x)
+    {
+        const uint32_t dix = t < nr - 1 ? dir_right(0, t + 1, 0, nr) : dir_left(0, t - (nr - 1) + 1, 0, nl, nr);
+        DirEnt de; de.off = 0; de.kmin = 0; de.len = 1; C.sl.dir[dix] = de; C.sl.nfin[dix] = 1;
+    }
     for (uint32_t t = threadIdx.x; t < nl; t += blockDim.x) C.rowdone[t] = t == 0 ? 1u : 0u;
     for (uint32_t t = threadIdx.x; t < nr; t += blockDim.x) C.coldone[t] = t == 0 ? 1u : 0u;
     if (threadIdx.x == 0) { C.sl.vpool[0] = 0.0; *C.bump = 1u; *C.overflow = 0u; *C.next = 0u; }
@@ -719,7 +730,10 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
 }
 
 // One candidate pair per CTA, pulled from a device queue.  `order` (optional) lists the queue in processing order.
-__global__ void __launch_bounds__(kCellThreads, 16 / kCellWarps)
+#ifndef ADK_MIN_BLOCKS
+#define ADK_MIN_BLOCKS (16 / ADK_CELL_WARPS)
+#endif
+__global__ void __launch_bounds__(kCellThreads, ADK_MIN_BLOCKS)
 k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
            const PairRec* __restrict__ pairs, const uint32_t* __restrict__ order, uint32_t npairs, AdCounters* __restrict__ counters,
            unsigned char* arena, CellLayout Lo, uint32_t capL, uint32_t capR,
@@ -810,11 +824,11 @@ struct AdHull { uint32_t len; uint32_t ok; uint32_t nl, nr; };
 // Area pattern of the reference state Entry{o, s, ss} on the given side at layer k, or +inf if it was never reached.
 __device__ unsigned long long state_value(const CellSlice& sl, uint32_t nl, uint32_t nr, bool right, uint32_t o, uint32_t s, uint32_t ss, uint32_t k)
 {
-    uint32_t pa, pb, d;
-    if (right) { pa = o; pb = s; d = ss - s - 1; }                       // RIGHT(o; s->ss): produced by cell (o, s)
-    else { pa = s; pb = o; d = (nr - 1 - o) + (ss - s - 1); }             // LEFT (o; s->ss): produced by cell (s, o)
+    uint32_t pa, pb;
+    if (right) { pa = o; pb = s; }                                       // RIGHT(o; s->ss): produced by cell (o, s)
+    else { pa = s; pb = o; }                                             // LEFT (o; s->ss): produced by cell (s, o)
     if (!sl.alive[pa * nr + pb]) return kInfBits;
-    const DirEnt de = sl.dir[dir_base(pa, pb, nl, nr) + d];
+    const DirEnt de = sl.dir[right ? dir_right(o, ss, s, nr) : dir_left(o, ss, s, nl, nr)];
     if (de.len == 0 || k < de.kmin || k >= (uint32_t) de.kmin + de.len) return kInfBits;
     return area_bits(sl.vpool[de.off + (k - de.kmin)]);      // holes hold +inf = kInfBits
 }
