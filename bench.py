@@ -340,6 +340,165 @@ def run_b200_arm(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------------- other configs
+def _aux_ref_worker(args):
+    algo, x, y, kmax, amax, dmax = args
+    from oracle.refpy import RefLib
+    lib = RefLib("x87")
+    t0 = time.perf_counter()
+    r = lib.solve(algo, x, y, kmax, amax, dmax, True)
+    return time.perf_counter() - t0, r["count"]
+
+
+def run_aux_workload(args):
+    """BASELINE configs 3 and 5 as secondary bench lines (same JSON shape; the driver's headline stays config 4).
+      area_n1000  : area-bounded DP (Eppstein path), synthetic clustered n = 1000 (sigma 2, seed 1000), A = 4, K = inf; anchors
+                    sharded over the ranks.  value = NOMINAL cells/s, (K-2) n (n-1) (n-2) / 3, executed cells beside it.
+      cells_batch : the ten cell samples (n = 362..699), A = 4, D = 4, K = inf, reconstruct; instances sharded over the ranks
+                    (adk_solve_batch).  value = cells/s over the whole batch."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import importlib
+    import __graft_entry__ as ge
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    pkg = ge.load_package()
+    adist = importlib.import_module("area_diameter_algorithm_b200.dist")
+    capi = importlib.import_module("area_diameter_algorithm_b200.capi")
+    solver = pkg.Solver(local)
+    stream = torch.cuda.Stream(device=dev)
+    solver.set_stream(stream.cuda_stream)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    amax = 4.0
+    if args.workload == "area_n1000":
+        synth = importlib.import_module("area_diameter_algorithm_b200.synth")
+        pts = synth.gaussian_points(1000, 2.0, 1000)
+        n = len(pts)
+        x = [p[0] for p in pts]; y = [p[1] for p in pts]
+        d_x = torch.tensor(x, dtype=torch.float64, device=dev); d_y = torch.tensor(y, dtype=torch.float64, device=dev)
+        h_x = torch.tensor(x, dtype=torch.float64).pin_memory(); h_y = torch.tensor(y, dtype=torch.float64).pin_memory()
+        nominal = (n - 2) * n * (n - 1) * (n - 2) // 3
+        desc = f"area-bounded DP (Eppstein), synthetic Gaussian n={n} sigma=2.0 seed=1000 in [0,20]^2, A={amax}, K=inf, reconstruct (BASELINE config 3)"
+        kernel, bytes_per_cell = "k_area_dp", 16
+
+        def step(resident):
+            flush.zero_()
+            if resident or world > 1:
+                part, st = (solver.area_partial_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, rank, world) if resident else
+                            solver.area_partial(x, y, None, amax, rank, world))
+                best = adist.merge_partials(adist.gather_partials(part, device=dev))
+                r = solver.area_finish_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, best, True) if rank == 0 else None
+                return st["cells_executed"], st["dp_ms"], r
+            r = solver.solve_area_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, True)
+            return r["cells_executed"], r["dp_ms"], r
+        h2d, d2h = 2 * n * 8, 64 + 4 * (n + 4) + 112
+    else:
+        with open(os.path.join(ROOT, "tests", "golden", "points.json")) as f:
+            allp = json.load(f)
+        names = [f"real/{i}/0" for i in range(10)]
+        sets = [np.array(allp[k], dtype=np.float64) for k in names]
+        dmax = 4.0
+        desc = (f"area+diameter-bounded DP on the ten cell samples (n={[len(s_) for s_ in sets]}), A={amax}, D={dmax}, K=inf, reconstruct, "
+                "one adk_solve_batch call (BASELINE config 5)")
+        kernel, bytes_per_cell, nominal = "k_ad_cells", BYTES_PER_CELL, None
+
+        def step(resident):
+            flush.zero_()
+            mine = solver.solve_batch(sets, capi.ALGO_AREA_DIAMETER, None, amax, dmax, True, shard=rank, nshards=world)
+            cells = sum(r["cells_executed"] for r in mine if r is not None)
+            dp = sum(r["dp_ms"] for r in mine if r is not None)
+            return cells, dp, adist.gather_batch_results(mine)
+        h2d = sum(len(s_) * 16 for s_ in sets); d2h = sum(64 + 4 * (len(s_) + 4) + 112 for s_ in sets)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def timed(resident, steps, warmup):
+        with torch.cuda.stream(stream):
+            for _ in range(warmup):
+                step(resident)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); torch.cuda.synchronize()
+            l0 = solver.launch_count(); t0 = time.perf_counter(); ev0.record(stream)
+            cells = 0; dp = 0.0; last = None
+            for _ in range(steps):
+                c, d, last = step(resident)
+                cells += c; dp += d
+            ev1.record(stream); torch.cuda.synchronize(); barrier()
+            wall = 1e3 * (time.perf_counter() - t0); devms = ev0.elapsed_time(ev1)
+            launches = solver.launch_count() - l0 + steps
+        agg = torch.tensor([cells, launches], dtype=torch.float64, device=dev)
+        mx = torch.tensor([devms, wall], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(agg, op=dist.ReduceOp.SUM); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        return {"cells": int(agg[0].item()), "launches": int(agg[1].item()), "dev_ms": float(mx[0].item()), "wall_ms": float(mx[1].item()),
+                "my_cells": cells, "my_dp_ms": dp, "last": last}
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    res = timed(True, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    e2e = timed(False, args.steps, 1)
+    if rank == 0:
+        secs = res["dev_ms"] / 1e3
+        units = nominal * args.steps if nominal else res["cells"]
+        peak, peak_src = measured_peaks()
+        dp_s = res["my_dp_ms"] / 1e3
+        achieved = res["my_cells"] * bytes_per_cell / dp_s / 1e9 if dp_s > 0 else 0.0     # EXECUTED cells of this rank (levels that cannot be finite are skipped)
+        line = {"metric": METRIC, "value": units / secs, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": res["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic" if nominal else "the reference's cell samples (tests/golden/points.json)",
+                "config": {"workload": desc, "l2": "256 MiB memset on the timed stream before every step (L2 flush)",
+                           "cells": "nominal (K-2) n (n-1) (n-2) / 3" if nominal else "counted in-kernel",
+                           "cells_executed_per_step": res["cells"] // args.steps},
+                "executed_cells_per_sec": res["cells"] / secs,
+                "e2e": {"value": (nominal * args.steps if nominal else e2e["cells"]) / (e2e["wall_ms"] / 1e3), "unit": UNIT,
+                        "ms_per_step": e2e["wall_ms"] / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "timer": "host wall clock around the C-ABI calls, max over ranks"},
+                "gpu_launches": res["launches"],
+                "roofline": {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "peak_source": peak_src, "share_of_step": res["my_dp_ms"] / res["dev_ms"]},
+                "clocks": clocks}
+        last = res["last"]
+        if nominal:
+            line["answers"] = [{"count": last["count"], "area": last["area"], "hull": last["hull"]}]
+        else:
+            line["answers"] = [{"n": len(s_), "count": r["count"], "area": r["area"], "diam": r["diam"], "ms": r["kernel_ms"]} for s_, r in zip(sets, last)]
+            line["instances_per_sec"] = len(sets) * args.steps / secs
+        if world == 1 and not args.no_cpu:
+            from multiprocessing import get_context
+            from oracle.refpy import RefLib, ref_available
+            if ref_available("x87"):
+                ncores = max(1, min(os.cpu_count() or 1, 32))
+                if nominal:
+                    sub, kc = 200, 16
+                    job = (RefLib.ALGO_EPPSTEIN, x[:sub], y[:sub], kc, amax, float("inf"))
+                    cpu_cells = (kc - 2) * sub * (sub - 1) * (sub - 2) // 3
+                    what = f"first {sub} points, K={kc} (nominal {cpu_cells} cells; the un-capped n=1000 table is 32 GB for the reference)"
+                else:
+                    k9 = names.index("real/9/0")
+                    job = (RefLib.ALGO_ANTIPODAL_OPTIMIZED, sets[k9][:, 0].tolist(), sets[k9][:, 1].tolist(), None, amax, dmax)
+                    cpu_cells = last[k9]["cells_executed"]
+                    what = f"the lightest slide real/9 (n={len(sets[k9])}, {cpu_cells} cells)"
+                with get_context("spawn").Pool(ncores) as pool:
+                    t0 = time.perf_counter(); out = pool.map(_aux_ref_worker, [job] * ncores); dt = time.perf_counter() - t0
+                line["cpu_baseline"] = {"value": cpu_cells * ncores / dt, "unit": UNIT, "cores": ncores, "kind": "reference",
+                                        "sample": f"{what}, one replica per core, {dt:.2f} s"}
+        print(json.dumps(line), flush=True)
+    solver.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -348,9 +507,13 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sigma", type=float, default=1.5, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.5, 1.0, 0.5)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="ad_n200", choices=["ad_n200", "area_n1000", "cells_batch"],
+                    help="ad_n200 = the headline (BASELINE config 4); area_n1000 = config 3; cells_batch = config 5")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.workload != "ad_n200":
+        run_aux_workload(args)
     else:
         run_b200_arm(args)
 
