@@ -20,6 +20,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace adk
@@ -36,6 +38,7 @@ struct PairStats
     unsigned int pad;
     unsigned long long max_cells;   // max over queued candidates of nl * nr                      (cells of the head grid)
     unsigned long long max_dirs;    // max over queued candidates of nl * nr * (nl + nr - 2) / 2   (directory entries)
+    unsigned long long cost_sum, cost_max;   // sum / max over queued candidates of the cost proxy nl * nr * (nl + nr)
     unsigned int hist[kCostBuckets];    // queued candidates per cost bucket (heaviest candidates are started first)
     unsigned int cursor[kCostBuckets];
 };
@@ -114,6 +117,8 @@ __global__ void k_ad_pairs(const double* __restrict__ x, const double* __restric
                 atomicMax(&stats->max_nl, nl); atomicMax(&stats->max_nr, nr); atomicMax(&stats->max_lim, (unsigned int) lim);
                 atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2) / 2);
                 atomicAdd(&stats->hist[cost_bucket(nl, nr)], 1u);
+                const unsigned long long cost = cells * (nl + nr);
+                atomicAdd(&stats->cost_sum, cost); atomicMax(&stats->cost_max, cost);
             }
         }
     }
@@ -235,7 +240,8 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 #ifndef ADK_CELL_WARPS
 #define ADK_CELL_WARPS 4
 #endif
-constexpr int kCellWarps = ADK_CELL_WARPS;       // warps per CTA (one candidate per CTA)
+constexpr int kCellWarps = ADK_CELL_WARPS;       // warps per CTA (one candidate per CTA) when candidates are plentiful
+constexpr int kMaxCellWarps = 16;                // ... and when few, heavy candidates set the critical path (chosen per launch)
 constexpr int kCellThreads = kCellWarps * 32;
 #ifndef ADK_KBT
 #define ADK_KBT 32
@@ -272,8 +278,8 @@ __host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, 
     Lo.off_aliveT = o; o = up(o + (size_t) max_cells);
     Lo.off_dir = o; o = up(o + sizeof(DirEnt) * (size_t) max_dirs);
     Lo.off_nfin = o; o = up(o + sizeof(uint16_t) * (size_t) max_dirs);
-    Lo.off_spill = o; o = up(o + sizeof(SrcRec) * (size_t) kCellWarps * max_src);
-    Lo.off_pred = o; o = up(o + sizeof(uint32_t) * (size_t) kCellWarps * max_src);
+    Lo.off_spill = o; o = up(o + sizeof(SrcRec) * (size_t) kMaxCellWarps * max_src);
+    Lo.off_pred = o; o = up(o + sizeof(uint32_t) * (size_t) kMaxCellWarps * max_src);
     Lo.off_v = o;
     const size_t rest = slice_bytes > o + 4096 ? slice_bytes - o - 4096 : 0;
     const size_t cap = rest / sizeof(double);
@@ -613,25 +619,25 @@ struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best te
 // Shared memory of k_ad_cells: [per-warp accumulators | per-warp source lists | lune coordinates + indices | done counters].
 // The staging arrays of build_lune (projection keys, unsorted indices) are only live while the lists are built, so they
 // alias the accumulators, which are re-initialised afterwards.
-__host__ __device__ inline size_t cells_acc_bytes() { return sizeof(double) * kRS * 32 * kCellWarps; }
+__host__ __device__ inline size_t cells_acc_bytes(uint32_t nw) { return sizeof(double) * kRS * 32 * nw; }
 __host__ __device__ inline size_t cells_stage_bytes(uint32_t capL, uint32_t capR) { return (size_t) (capL + capR) * (sizeof(double) + sizeof(int32_t)); }
-__host__ __device__ inline size_t cells_front_bytes(uint32_t capL, uint32_t capR)
+__host__ __device__ inline size_t cells_front_bytes(uint32_t capL, uint32_t capR, uint32_t nw)
 {
-    const size_t a = cells_acc_bytes(), b = (cells_stage_bytes(capL, capR) + 15) & ~(size_t) 15;
+    const size_t a = cells_acc_bytes(nw), b = (cells_stage_bytes(capL, capR) + 15) & ~(size_t) 15;
     return a > b ? a : b;
 }
-__host__ __device__ inline size_t cells_smem_bytes(uint32_t capL, uint32_t capR)
+__host__ __device__ inline size_t cells_smem_bytes(uint32_t capL, uint32_t capR, uint32_t nw)
 {
-    return cells_front_bytes(capL, capR) + sizeof(SrcRec) * kSrcCap * kCellWarps
+    return cells_front_bytes(capL, capR, nw) + sizeof(SrcRec) * kSrcCap * nw
            + (size_t) (capL + capR) * (2 * sizeof(double) + sizeof(int32_t) + sizeof(uint32_t)) + 16;
 }
 
-__device__ __forceinline__ LuneSmem carve_cells_smem(unsigned char* smem_raw, uint32_t capL, uint32_t capR, uint32_t** done)
+__device__ __forceinline__ LuneSmem carve_cells_smem(unsigned char* smem_raw, uint32_t capL, uint32_t capR, uint32_t nw, uint32_t** done)
 {
     LuneSmem S;
     S.tproj = reinterpret_cast<double*>(smem_raw);                                  // aliases the accumulators
     S.tidx = reinterpret_cast<int32_t*>(smem_raw + sizeof(double) * (capL + capR));
-    double* d = reinterpret_cast<double*>(smem_raw + cells_front_bytes(capL, capR) + sizeof(SrcRec) * kSrcCap * kCellWarps);
+    double* d = reinterpret_cast<double*>(smem_raw + cells_front_bytes(capL, capR, nw) + sizeof(SrcRec) * kSrcCap * nw);
     S.Lx = d; d += capL; S.Ly = d; d += capL; S.Rx = d; d += capR; S.Ry = d; d += capR;
     int32_t* q = reinterpret_cast<int32_t*>(d);
     S.Lidx = q; q += capL; S.Ridx = q; q += capR;
@@ -707,7 +713,7 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
     if (lane == 0) { s_wk[warp] = bk; s_wv[warp] = bv; }
     __syncthreads();
     uint32_t k = 0; double v = INFINITY;
-    for (int w = 0; w < kCellWarps; ++w) if (s_wk[w] > k || (s_wk[w] == k && s_wv[w] < v)) { k = s_wk[w]; v = s_wv[w]; }
+    for (int w = 0; w < (int) (blockDim.x >> 5); ++w) if (s_wk[w] > k || (s_wk[w] == k && s_wv[w] < v)) { k = s_wk[w]; v = s_wv[w]; }
     out.kbest = k; out.area = v;
     __syncthreads();
 }
@@ -718,9 +724,10 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
 {
     const uint32_t warp = threadIdx.x >> 5;
     uint32_t* done = nullptr;
-    C.S = carve_cells_smem(smem_raw, capL, capR, &done);
+    const uint32_t nw = blockDim.x >> 5;
+    C.S = carve_cells_smem(smem_raw, capL, capR, nw, &done);
     C.acc = reinterpret_cast<double*>(smem_raw) + (size_t) warp * kRS * 32;
-    C.src = reinterpret_cast<SrcRec*>(smem_raw + cells_front_bytes(capL, capR)) + (size_t) warp * kSrcCap;
+    C.src = reinterpret_cast<SrcRec*>(smem_raw + cells_front_bytes(capL, capR, nw)) + (size_t) warp * kSrcCap;
     C.pred = nullptr;                          // predicate words only exist on the (global) spill path
     C.rowdone = done; C.coldone = done + capL;
     C.sl = carve_cells(arena, Lo, slice);
@@ -730,10 +737,9 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
 }
 
 // One candidate pair per CTA, pulled from a device queue.  `order` (optional) lists the queue in processing order.
-#ifndef ADK_MIN_BLOCKS
-#define ADK_MIN_BLOCKS (16 / ADK_CELL_WARPS)
-#endif
-__global__ void __launch_bounds__(kCellThreads, ADK_MIN_BLOCKS)
+// Two instantiations of the same body: the 4-warp CTA (4 per SM) and the wide CTA (8 or 16 warps); 128 registers either way.
+template <int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
 k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
            const PairRec* __restrict__ pairs, const uint32_t* __restrict__ order, uint32_t npairs, AdCounters* __restrict__ counters,
            unsigned char* arena, CellLayout Lo, uint32_t capL, uint32_t capR,
@@ -743,8 +749,8 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
     __shared__ unsigned int s_pair, s_bump, s_overflow, s_next;
-    __shared__ uint32_t s_wk[kCellWarps];
-    __shared__ double s_wv[kCellWarps];
+    __shared__ uint32_t s_wk[kMaxCellWarps];
+    __shared__ double s_wv[kMaxCellWarps];
     __shared__ CtaBest s_best;
     CellCtx C;
     uint32_t cur = 0;                      // each CTA owns slices 2*blockIdx and 2*blockIdx+1: the one being written and the
@@ -994,15 +1000,21 @@ constexpr uint64_t kDefaultPoolRecords = 4u << 20;    // first-try pool per slic
 // Launches the cell kernel over `count` queue entries (order == nullptr: pairs[0..count)) with `slices` CTAs.
 int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uint32_t count, uint32_t slices, const CellLayout& Lo,
                     uint32_t capL, uint32_t capR, uint64_t kmax, uint32_t nlayers_ref, double amax, AdSmall* sm,
-                    CtaBest* d_cta_best, uint32_t* d_ovf_list, unsigned int* d_ovf_count, uint32_t round)
+                    CtaBest* d_cta_best, uint32_t* d_ovf_list, unsigned int* d_ovf_count, uint32_t round, uint32_t nw)
 {
-    const size_t smem = cells_smem_bytes(capL, capR);
+    const size_t smem = cells_smem_bytes(capL, capR, nw);
     if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
-    ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, 16 / kCellWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    else ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kMaxCellWarps * 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     ADK_CUDA(c, cudaMemsetAsync(&sm->counters.queue, 0, sizeof(unsigned int), c->stream));
     ADK_CUDA(c, cudaMemsetAsync(d_ovf_count, 0, sizeof(unsigned int), c->stream));
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
-    k_ad_cells<<<slices, kCellThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
+    if (nw == (uint32_t) kCellWarps)
+        k_ad_cells<kCellThreads, 16 / kCellWarps><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
+                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, capL, capR, kmax, nlayers_ref,
+                                                          amax, d_cta_best, d_ovf_list, d_ovf_count, round);
+    else
+        k_ad_cells<kMaxCellWarps * 32, 1><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
                                                           &sm->counters, c->arena.as<unsigned char>(), Lo, capL, capR, kmax, nlayers_ref,
                                                           amax, d_cta_best, d_ovf_list, d_ovf_count, round);
     ++c->launches;
@@ -1011,14 +1023,20 @@ int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uin
 }
 
 // Resident CTAs of k_ad_cells per SM for the given lune capacity.
-int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, int* per_sm)
+int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, uint32_t nw, int* per_sm)
 {
-    const size_t smem = cells_smem_bytes(capL, capR);
-    if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
-    ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const size_t smem = cells_smem_bytes(capL, capR, nw);
+    if (smem > 200 * 1024)
+    {
+        if (nw > (uint32_t) kCellWarps) { *per_sm = 0; return ADK_OK; }        // this CTA width is not available for such lunes
+        c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM;
+    }
+    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, 16 / kCellWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    else ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kMaxCellWarps * 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int occ = 0;
-    ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells, kCellThreads, smem));
-    *per_sm = occ > 0 ? occ : 1;
+    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kCellThreads, 16 / kCellWarps>, (int) nw * 32, smem));
+    else ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kMaxCellWarps * 32, 1>, (int) nw * 32, smem));
+    *per_sm = occ > 0 ? occ : (nw > (uint32_t) kCellWarps ? 0 : 1);
     return ADK_OK;
 }
 
@@ -1029,8 +1047,29 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
     const uint32_t max_src = ps.max_nl + ps.max_nr;
     if (ps.max_dirs >= 0xffffffffull) { c->err = "area+diameter path: candidate too large for 32-bit directory offsets"; return ADK_ERR_NOMEM; }
     const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, max_src, 0).off_v + 8192;
+    // Warps per candidate.  Plenty of candidates per CTA: 4 warps each, 4 CTAs per SM (best throughput).  Few, heavy ones
+    // (a shard of a multi-GPU solve, the re-run of a winner): the longest candidate is the critical path, so wider CTAs
+    // take fewer candidates at a time and finish each one sooner.  Both sides are estimated in the same cost proxy.
     int occ = 1;
-    ADK_TRY(ad_cells_occupancy(c, ps.max_nl, ps.max_nr, &occ));
+    uint32_t nw = (uint32_t) kCellWarps;
+    {
+        const double eff[3] = {1.0, 0.92, 0.82};                       // measured throughput of 4 / 8 / 16 warps per candidate
+        double best_t = 0.0;
+        for (int v = 0; v < 3; ++v)
+        {
+            const uint32_t w = (uint32_t) kCellWarps << v;
+            if (w > (uint32_t) kMaxCellWarps) break;
+            int o = 0;
+            ADK_TRY(ad_cells_occupancy(c, ps.max_nl, ps.max_nr, w, &o));
+            if (o <= 0) break;
+            const double speed = (double) w / kCellWarps * eff[v];       // of one CTA, relative to a 4-warp CTA
+            const double ctas = (double) std::min<uint64_t>(nqueued, (uint64_t) c->sm_count * (uint64_t) o);
+            const double t = std::max((double) ps.cost_sum / (ctas * speed), (double) ps.cost_max / speed);
+            if (v == 0 || t < 0.9 * best_t) { best_t = v == 0 ? t : std::min(t, best_t); nw = w; occ = o; }
+            if (getenv("ADK_DEBUG")) fprintf(stderr, "[adk] queue %u  w=%u occ=%d  load=%.3g critical=%.3g -> t=%.3g  (chosen w=%u)\n", nqueued, w, o,
+                                             (double) ps.cost_sum / (ctas * speed), (double) ps.cost_max / speed, t, nw);
+        }
+    }
     ADK_TRY(ensure(c, c->ad_ovf, sizeof(uint32_t) * 2 * (size_t) nqueued + 64));
     uint32_t* d_ovf[2] = {c->ad_ovf.as<uint32_t>(), c->ad_ovf.as<uint32_t>() + nqueued};
     const uint32_t* d_order = d_order0;
@@ -1055,7 +1094,7 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
         ADK_TRY(ensure(c, c->arena, slice_bytes * 2 * (size_t) slices));
         ADK_TRY(ensure(c, c->ad_cta, sizeof(CtaBest) * slices));
         ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
-                                c->ad_cta.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round));
+                                c->ad_cta.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round, nw));
         k_ad_reduce<<<1, 32, 0, c->stream>>>(c->ad_cta.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
@@ -1187,6 +1226,7 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
         PairStats ps; std::memset(&ps, 0, sizeof(ps));
         ps.nqueued = 1; ps.max_nl = pr.nl; ps.max_nr = pr.nr; ps.max_lim = lim;
         ps.max_cells = (unsigned long long) pr.nl * pr.nr; ps.max_dirs = ps.max_cells * (pr.nl + pr.nr - 2) / 2;
+        ps.cost_sum = ps.cost_max = ps.max_cells * (pr.nl + pr.nr);
         ADK_CUDA(c, cudaMemcpyAsync(d_pair, &pr, sizeof(pr), cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(&sm->counters, 0, sizeof(AdCounters), c->stream));
         c->ad_keep_valid = false;
