@@ -1053,7 +1053,7 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
     int occ = 1;
     uint32_t nw = (uint32_t) kCellWarps;
     {
-        const double eff[3] = {1.0, 0.92, 0.82};                       // measured throughput of 4 / 8 / 16 warps per candidate
+        const double eff[3] = {1.0, 0.92, 0.72};                       // measured throughput of 4 / 8 / 16 warps per candidate
         double best_t = 0.0;
         for (int v = 0; v < 3; ++v)
         {
@@ -1065,7 +1065,8 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
             const double speed = (double) w / kCellWarps * eff[v];       // of one CTA, relative to a 4-warp CTA
             const double ctas = (double) std::min<uint64_t>(nqueued, (uint64_t) c->sm_count * (uint64_t) o);
             const double t = std::max((double) ps.cost_sum / (ctas * speed), (double) ps.cost_max / speed);
-            if (v == 0 || t < 0.9 * best_t) { best_t = v == 0 ? t : std::min(t, best_t); nw = w; occ = o; }
+            const char* force = getenv("ADK_FORCE_CELL_WARPS");            // experiments only
+            if (force ? (uint32_t) atoi(force) == w : (v == 0 || t < 0.9 * best_t)) { best_t = v == 0 ? t : std::min(t, best_t); nw = w; occ = o; }
             if (getenv("ADK_DEBUG")) fprintf(stderr, "[adk] queue %u  w=%u occ=%d  load=%.3g critical=%.3g -> t=%.3g  (chosen w=%u)\n", nqueued, w, o,
                                              (double) ps.cost_sum / (ctas * speed), (double) ps.cost_max / speed, t, nw);
         }

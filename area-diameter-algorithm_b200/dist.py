@@ -71,3 +71,24 @@ def gather_batch_results(results, group=None):
             if r is not None:
                 out[i] = r
     return out
+
+
+def solve_batch_pair_sharded(solver, point_sets, kmax, amax, dmax, reconstruct=True, device=None, group=None):
+    """A batch of area+diameter instances with EVERY instance's candidate pairs sharded over the ranks (instead of whole
+    instances): the right split when one instance dominates the batch (the densest cell sample is 60 % of config 5).
+    Per instance: adk_area_diameter_partial on every rank, one 32-byte all-gather, and the rank that owns the winning
+    pair (tie key mod world: its records are still resident) reconstructs.  Returns (complete result list, my cell count)."""
+    world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    results, my_cells, my_dp_ms = [None] * len(point_sets), 0, 0.0
+    for i, pts in enumerate(point_sets):
+        x = [float(p[0]) for p in pts]
+        y = [float(p[1]) for p in pts]
+        part, st = solver.area_diameter_partial(x, y, kmax, amax, dmax, rank, world)
+        my_cells += st["cells_executed"]
+        my_dp_ms += st["dp_ms"]
+        best = merge_partials(gather_partials(part, device=device, group=group))
+        owner = best["tie_key"] % world if best["found"] else 0
+        if rank == owner:
+            results[i] = solver.area_diameter_finish(x, y, kmax, amax, dmax, best, reconstruct)
+    return gather_batch_results(results, group=group), my_cells, my_dp_ms

@@ -411,6 +411,10 @@ def run_aux_workload(args):
 
         def step(resident):
             flush.zero_()
+            if world > 1 and not args.instance_sharding:
+                # one slide dominates the batch: shard every instance's candidate pairs instead of whole instances
+                allr, cells, dp = adist.solve_batch_pair_sharded(solver, sets, None, amax, dmax, True, device=dev)
+                return cells, dp, allr
             mine = solver.solve_batch(sets, capi.ALGO_AREA_DIAMETER, None, amax, dmax, True, shard=rank, nshards=world)
             cells = sum(r["cells_executed"] for r in mine if r is not None)
             dp = sum(r["dp_ms"] for r in mine if r is not None)
@@ -473,6 +477,8 @@ def run_aux_workload(args):
             line["answers"] = [{"count": last["count"], "area": last["area"], "hull": last["hull"]}]
         else:
             line["answers"] = [{"n": len(s_), "count": r["count"], "area": r["area"], "diam": r["diam"], "ms": r["kernel_ms"]} for s_, r in zip(sets, last)]
+            line["config"]["parallelism"] = ("one GPU" if world == 1 else "whole instances per rank (adk_solve_batch)" if args.instance_sharding
+                                             else "candidate pairs of every instance sharded over the ranks")
             line["instances_per_sec"] = len(sets) * args.steps / secs
         if world == 1 and not args.no_cpu:
             from multiprocessing import get_context
@@ -507,6 +513,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sigma", type=float, default=1.5, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.5, 1.0, 0.5)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--instance-sharding", action="store_true", help="cells_batch on N > 1 GPUs: whole instances per rank (adk_solve_batch) "
+                    "instead of every instance's candidate pairs")
     ap.add_argument("--workload", default="ad_n200", choices=["ad_n200", "area_n1000", "cells_batch"],
                     help="ad_n200 = the headline (BASELINE config 4); area_n1000 = config 3; cells_batch = config 5")
     args = ap.parse_args()
