@@ -53,7 +53,7 @@ __device__ __forceinline__ uint32_t cost_bucket(uint32_t nl, uint32_t nr)
 }
 
 struct CtaBest { uint32_t found; uint32_t count; double area; unsigned long long key; uint32_t s, t;
-                 uint32_t nl, nr, slice, round; };   // slice/round: where the winner's records still live (see ad_finish)
+                 uint32_t nl, nr, slice, round, states, pad; };   // slice/round: where the winner's records still live (see ad_finish)
 
 struct AdCounters { unsigned long long cells, states; unsigned int queue; unsigned int pad; };
 
@@ -614,7 +614,7 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     if (lane == 0) { C.sl.alive[a * nr + b] = 1; C.sl.aliveT[b * nl + a] = 1; }
 }
 
-struct CandResult { uint32_t kbest; uint32_t pad; double area; };     // best terminal layer (0 = none) of one candidate
+struct CandResult { uint32_t kbest; uint32_t states; double area; };     // best terminal layer (0 = none) of one candidate
 
 // Shared memory of k_ad_cells: [per-warp accumulators | per-warp source lists | lune coordinates + indices | done counters].
 // The staging arrays of build_lune (projection keys, unsorted indices) are only live while the lists are built, so they
@@ -651,9 +651,11 @@ __device__ __forceinline__ LuneSmem carve_cells_smem(unsigned char* smem_raw, ui
 // column b up to a (its only inputs), so no CTA-wide barrier separates the anti-diagonals.
 __device__ void run_candidate(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, const Tables& T, const PairRec& pr,
                               CellCtx& C, uint32_t* s_cnt, uint32_t* s_wk, double* s_wv, uint64_t kmax, uint32_t nlayers_ref,
-                              unsigned long long& my_cells, unsigned int& my_states, CandResult& out)
+                              unsigned long long& my_cells, unsigned int& my_states, CandResult& out, unsigned int* s_cstates)
 {
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned int states0 = my_states;
+    if (threadIdx.x == 0) *s_cstates = 0u;
     build_lune(x, y, n, pr, C.S, s_cnt);
     for (uint32_t t = lane; t < (uint32_t) kRS * 32; t += 32) C.acc[t] = INFINITY;     // build_lune staged its keys here
     const uint32_t nl = pr.nl, nr = pr.nr;
@@ -710,8 +712,11 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
         const uint32_t ok = __shfl_xor_sync(kFull, bk, o); const double ov = __shfl_xor_sync(kFull, bv, o);
         if (ok > bk || (ok == bk && ov < bv)) { bk = ok; bv = ov; }
     }
-    if (lane == 0) { s_wk[warp] = bk; s_wv[warp] = bv; }
+    unsigned int dst = my_states - states0;          // states this candidate created (the reference's hash entries, :519-524)
+    for (int o = 16; o; o >>= 1) dst += __shfl_xor_sync(kFull, dst, o);
+    if (lane == 0) { s_wk[warp] = bk; s_wv[warp] = bv; atomicAdd(s_cstates, dst); }
     __syncthreads();
+    out.states = *s_cstates;
     uint32_t k = 0; double v = INFINITY;
     for (int w = 0; w < (int) (blockDim.x >> 5); ++w) if (s_wk[w] > k || (s_wk[w] == k && s_wv[w] < v)) { k = s_wk[w]; v = s_wv[w]; }
     out.kbest = k; out.area = v;
@@ -748,7 +753,7 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_cnt[2];
-    __shared__ unsigned int s_pair, s_bump, s_overflow, s_next;
+    __shared__ unsigned int s_pair, s_bump, s_overflow, s_next, s_cstates;
     __shared__ uint32_t s_wk[kMaxCellWarps];
     __shared__ double s_wv[kMaxCellWarps];
     __shared__ CtaBest s_best;
@@ -759,7 +764,7 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
     const uint32_t lane = threadIdx.x & 31;
     unsigned long long my_cells = 0; unsigned int my_states = 0;
     if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0;
-                            s_best.nl = s_best.nr = 0; s_best.slice = 0; s_best.round = round; }
+                            s_best.nl = s_best.nr = 0; s_best.slice = 0; s_best.round = round; s_best.states = 0; s_best.pad = 0; }
     for (;;)
     {
         __syncthreads();
@@ -771,7 +776,7 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
         const PairRec pr = pairs[pi];
         CandResult res;
         unsigned long long cells0 = my_cells; unsigned int states0 = my_states;
-        run_candidate(x, y, n, T, pr, C, s_cnt, s_wk, s_wv, kmax, nlayers_ref, my_cells, my_states, res);
+        run_candidate(x, y, n, T, pr, C, s_cnt, s_wk, s_wv, kmax, nlayers_ref, my_cells, my_states, res, &s_cstates);
         if (s_overflow)
         {   // the record pool of this slice was too small: the host re-runs the candidate in a larger slice
             my_cells = cells0; my_states = states0;
@@ -790,7 +795,7 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
             if (better && threadIdx.x == 0)
             {
                 s_best.found = 1; s_best.count = cnt; s_best.area = res.area; s_best.key = key; s_best.s = pr.s; s_best.t = pr.t;
-                s_best.nl = pr.nl; s_best.nr = pr.nr; s_best.slice = 2 * blockIdx.x + cur; s_best.round = round;
+                s_best.nl = pr.nl; s_best.nr = pr.nr; s_best.slice = 2 * blockIdx.x + cur; s_best.round = round; s_best.states = res.states;
             }
         }
         if (better)
@@ -1168,7 +1173,7 @@ int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, 
             static_assert(sizeof(CellLayout) <= sizeof(c->ad_keep_layout), "ad_keep_layout too small");
             std::memcpy(c->ad_keep_layout, &keep_layout, sizeof(CellLayout));
             c->ad_keep_valid = true; c->ad_keep_slice = hb.slice; c->ad_keep_s = hb.s; c->ad_keep_t = hb.t;
-            c->ad_keep_nl = hb.nl; c->ad_keep_nr = hb.nr; c->ad_keep_count = hb.count; c->ad_keep_kmax = kmax; c->ad_keep_amax = amax;
+            c->ad_keep_nl = hb.nl; c->ad_keep_nr = hb.nr; c->ad_keep_count = hb.count; c->ad_keep_states = hb.states; c->ad_keep_kmax = kmax; c->ad_keep_amax = amax;
         }
     }
     if (st)
@@ -1208,6 +1213,7 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
         pr = PairRec{best->w0, best->w1, c->ad_keep_nl, c->ad_keep_nr};
         std::memcpy(&Lo, c->ad_keep_layout, sizeof(CellLayout));
         slice = c->ad_keep_slice;
+        out->entries_required = (int64_t) c->ad_keep_states;      // carried to the caller: the re-run the reference does (:529-535)
     }
     else
     {   // the winning candidate alone (it was found on another GPU, or evicted): size it, re-run it (:529-535)
@@ -1233,6 +1239,10 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
         c->ad_keep_valid = false;
         ADK_TRY(ad_run_queue(c, d_pair, nullptr, 1, ps, kmax, nlayers_ref, amax, sm, &Lo, nullptr));
         slice = 0;                               // the only candidate of the only CTA: its first slice
+        AdCounters rc;
+        ADK_CUDA(c, cudaMemcpyAsync(&rc, &sm->counters, sizeof(rc), cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+        out->entries_required = (int64_t) rc.states;
     }
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), n};
     const size_t smem = lune_smem_bytes(pr.nl, pr.nr, 1);

@@ -20,7 +20,8 @@
 namespace adk
 {
 
-struct SrcRec { double area; uint32_t gidx; uint16_t c; uint16_t c3; };   // 16 B, one per source cell
+struct SrcRec { double area; uint32_t gidx; uint16_t c; uint16_t c3; };   // 16 B, one per source cell; c3 bit 15: the source is the
+                                                                           // first element of its row's slope list (for the counter)
 constexpr uint32_t kNoPrev = 0xffffffffu;   // nothing before the read position: level 2 reads 0, deeper levels read +inf
 
 struct AnchorInfo
@@ -41,6 +42,7 @@ struct AnchorInfo
     uint32_t levels_run;
     uint64_t list_cells;   // sum of slope-list lengths = reference cells per level
     uint64_t nonempty_rows;
+    uint64_t required;     // prefix-minimum change points beyond the first list element (Eppstein.cpp:228-232)
 };
 
 // --------------------------------------------------------------------------------------------- PREP kernel
@@ -145,8 +147,9 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
                 if (src)
                 {
                     const uint32_t k = ns + __popc(sm & lt);
+                    const uint32_t head = (k == 0 && kept == 0 && (km & lt) == 0u) ? 0x8000u : 0u;
                     rsrc[k] = (uint16_t) sl;
-                    rrec[k] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) c3};
+                    rrec[k] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) (c3 | head)};
                 }
                 if (defer)
                 {
@@ -175,7 +178,7 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
                     if (area <= amax && (uint64_t) cfull <= K)
                     {
                         rsrc[ns] = (uint16_t) sl;
-                        rrec[ns] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) cfull};
+                        rrec[ns] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) (cfull | ((ns == 0 && kept == 0) ? 0x8000u : 0u))};
                         ++ns;
                     }
                     ++kept;
@@ -224,7 +227,7 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
         if (threadIdx.x == 0)
         {
             A.rows = rows; A.U = s_total; A.cmax = s_cmax; A.list_cells = s_cells; A.nonempty_rows = s_nonempty;
-            A.best_m = 0; A.best_area = 0.0; A.best_row = -1; A.levels_run = 0;
+            A.best_m = 0; A.best_area = 0.0; A.best_row = -1; A.levels_run = 0; A.required = 0;
         }
         __syncthreads();
     }
@@ -251,7 +254,7 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
           const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc, const uint32_t* __restrict__ rowbase,
           double* __restrict__ Tbuf, uint64_t K, double amax)
 {
-    __shared__ unsigned long long s_lvl[3];
+    __shared__ unsigned long long s_lvl[3], s_req;
     __shared__ unsigned int s_next;
     __shared__ int s_row;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -269,7 +272,8 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
         double* T = Tbuf + A.t_off;
         uint32_t top = 2, levels = 0;
         double best_area = 0.0;
-        if (threadIdx.x == 0) { s_lvl[0] = s_lvl[1] = s_lvl[2] = kInfBits; s_row = 0x7fffffff; }
+        if (threadIdx.x == 0) { s_lvl[0] = s_lvl[1] = s_lvl[2] = kInfBits; s_row = 0x7fffffff; s_req = 0ull; }
+        unsigned int req = 0;
         __syncthreads();
         if (U > 0)
         {
@@ -288,10 +292,12 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
                     {
                         const uint32_t k = k0 + lane;
                         double val = INFINITY;
+                        bool head = false;
                         if (k < ns)
                         {
                             const SrcRec r = rrec[k];
-                            const uint64_t c = m == 3 ? r.c3 : r.c;
+                            const uint64_t c = m == 3 ? (r.c3 & 0x7fffu) : r.c;
+                            head = (r.c3 & 0x8000u) != 0;
                             if (c + 2 <= m)
                             {   // Eppstein.cpp:210-216 with T[0], T[1] = +inf and T[2] = 0
                                 const uint64_t lvl = m - c;
@@ -302,7 +308,12 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
                                 if (cur <= amax) val = cur;
                             }
                         }
+                        const bool head_finite = k == 0 && head && val < INFINITY;       // counted once as "first element", not as a change
                         val = fmin(warp_prefix_min(val, lane), carry);
+                        double before = __shfl_up_sync(0xffffffffu, val, 1);
+                        if (lane == 0) before = carry;
+                        req += (unsigned int) __popc(__ballot_sync(0xffffffffu, k < ns && val < before))
+                               - (unsigned int) __popc(__ballot_sync(0xffffffffu, head_finite));      // Eppstein.cpp:228-232
                         if (k < ns) out[k] = val;                                   // Eppstein.cpp:234
                         carry = __shfl_sync(0xffffffffu, val, 31);
                     }
@@ -324,10 +335,11 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
                 }
             }
         }
+        if (lane == 0 && req) atomicAdd(&s_req, (unsigned long long) req);
         __syncthreads();
         if (threadIdx.x == 0)
         {
-            A.levels_run = levels;
+            A.levels_run = levels; A.required = s_req;
             if (top > 2) { A.best_m = top; A.best_area = best_area; A.best_row = s_row; }
         }
         __syncthreads();
@@ -335,24 +347,25 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
 }
 
 struct AreaBest { int32_t found; uint32_t m; double area; uint32_t order; int32_t row; int32_t pt; int32_t jpt;
-                  uint64_t cells_nominal, cells_executed; };
+                  uint64_t cells_nominal, cells_executed, required; };
 
 // Lexicographic best over anchors: m desc, area asc, reference anchor order asc (Eppstein.cpp:219-224).
 __global__ void k_area_reduce(const AnchorInfo* __restrict__ info, uint32_t count, const int32_t* __restrict__ rowpt,
                               uint64_t K, AreaBest* __restrict__ out)
 {
-    __shared__ unsigned long long s_cn, s_ce;
+    __shared__ unsigned long long s_cn, s_ce, s_rq;
     __shared__ uint32_t s_m; __shared__ unsigned long long s_area; __shared__ uint32_t s_order;
-    if (threadIdx.x == 0) { s_cn = 0; s_ce = 0; s_m = 0; s_area = kInfBits; s_order = 0xffffffffu; }
+    if (threadIdx.x == 0) { s_cn = 0; s_ce = 0; s_rq = 0; s_m = 0; s_area = kInfBits; s_order = 0xffffffffu; }
     __syncthreads();
-    unsigned long long cn = 0, ce = 0; uint32_t bm = 0;
+    unsigned long long cn = 0, ce = 0, rq = 0; uint32_t bm = 0;
     for (uint32_t t = threadIdx.x; t < count; t += blockDim.x)
     {
         cn += info[t].list_cells * (K - 2);
         ce += (unsigned long long) info[t].levels_run * info[t].U;
+        rq += info[t].required + info[t].nonempty_rows * (K - 2);      // every non-empty list counts once per level (:228-232)
         bm = max(bm, info[t].best_m);
     }
-    atomicAdd(&s_cn, cn); atomicAdd(&s_ce, ce); atomicMax(&s_m, bm);
+    atomicAdd(&s_cn, cn); atomicAdd(&s_ce, ce); atomicAdd(&s_rq, rq); atomicMax(&s_m, bm);
     __syncthreads();
     const uint32_t m = s_m;
     if (m > 0)
@@ -373,7 +386,7 @@ __global__ void k_area_reduce(const AnchorInfo* __restrict__ info, uint32_t coun
     if (threadIdx.x == 0)
     {
         if (m == 0) { out->found = 0; out->m = 0; out->area = 0.0; out->order = 0; out->row = -1; out->pt = -1; out->jpt = -1; }
-        out->cells_nominal = s_cn; out->cells_executed = s_ce;
+        out->cells_nominal = s_cn; out->cells_executed = s_ce; out->required = s_rq;
     }
 }
 
@@ -452,7 +465,7 @@ __global__ void k_area_backtrack(const double* __restrict__ x, const double* __r
         }
         if (pick < 0) { ok = 0; break; }
         const SrcRec r = arec[(size_t) row * acap + pick];
-        m -= m == 3 ? r.c3 : r.c;
+        m -= m == 3 ? (r.c3 & 0x7fffu) : r.c;
         hull[h++] = j;
         row = (int) asrc[(size_t) row * acap + pick];
     }
@@ -669,7 +682,7 @@ int area_partial(Ctx* c, uint64_t kmax, double amax, uint32_t shard, uint32_t ns
     }
     if (st)
     {
-        st->cells_nominal = hb.cells_nominal; st->cells_executed = hb.cells_executed;
+        st->cells_nominal = hb.cells_nominal; st->cells_executed = hb.cells_executed; st->states = hb.required;
         st->kernel_ms = ms; st->dp_ms = dp_ms; st->launches = c->launches;
         st->arena_bytes = c->scratch1.cap + c->scratch2.cap + c->scratch3.cap + c->scratch4.cap + c->scratch5.cap;
     }

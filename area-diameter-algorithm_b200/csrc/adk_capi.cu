@@ -237,6 +237,7 @@ int adk_solve_area(adk_ctx* h, const double* x, const double* y, uint32_t n, uin
     {   // Eppstein.cpp:171-175: the reference's dense table size; "required" is reported by the DP kernels
         const uint64_t K = std::min<uint64_t>(kmax, n);
         out->entries_alloc = (int64_t) ((K + 1) * 2 * (uint64_t) n * n);
+        out->entries_required = (int64_t) st.states;      // area path: prefix-minimum change points (Eppstein.cpp:228-232)
     }
     return ADK_OK;
 }
@@ -268,7 +269,9 @@ int adk_area_diameter_finish(adk_ctx* h, const double* x, const double* y, uint3
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
     ADK_TRY(adk::upload_points(c, x, y, n, false));
-    return adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
+    const int rc = adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
+    out->entries_required = -1;      // ad_finish carries the winner's state count there for adk_solve_area_diameter only
+    return rc;
 }
 
 int adk_area_diameter_finish_dev(adk_ctx* h, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,
@@ -280,7 +283,9 @@ int adk_area_diameter_finish_dev(adk_ctx* h, const double* d_x, const double* d_
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
     ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
-    return adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
+    const int rc = adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
+    out->entries_required = -1;      // ad_finish carries the winner's state count there for adk_solve_area_diameter only
+    return rc;
 }
 
 int adk_solve_area_diameter(adk_ctx* h, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
@@ -295,8 +300,11 @@ int adk_solve_area_diameter(adk_ctx* h, const double* x, const double* y, uint32
     adk_partial part; adk_stats st;
     ADK_TRY(adk::ad_partial(c, kmax, amax, dmax, 0, 1, &part, &st));
     ADK_TRY(adk::ad_finish(c, kmax, amax, dmax, &part, flags, out, hull));
+    // AntipodalOptimized.cpp:519-524, 529-535: every pair's hash entries, plus the winner's once more when its DP is re-run
+    const int64_t again = (out->found && (flags & ADK_FLAG_RECONSTRUCT) && out->entries_required > 0) ? out->entries_required : 0;
+    out->entries_required = -1;
     fill_result_from(out, st, flags);
-    if (flags & ADK_FLAG_COUNTERS) { out->entries_alloc = (int64_t) st.states; out->entries_required = (int64_t) st.states; }
+    if (flags & ADK_FLAG_COUNTERS) { out->entries_alloc = (int64_t) st.states + again; out->entries_required = (int64_t) st.states + again; }
     return ADK_OK;
 }
 

@@ -52,7 +52,7 @@ struct Ctx
     // the winning candidate of the last area+diameter partial solve, still resident in its arena slice (see ad_finish)
     bool ad_keep_valid = false;
     uint32_t ad_keep_slice = 0, ad_keep_s = 0, ad_keep_t = 0, ad_keep_nl = 0, ad_keep_nr = 0, ad_keep_count = 0;
-    uint64_t ad_keep_kmax = 0;
+    uint64_t ad_keep_kmax = 0, ad_keep_states = 0;
     double ad_keep_amax = 0.0;
     unsigned char ad_keep_layout[96] = {0};   // the CellLayout the slice was written with
     uint64_t points_hash = 0;      // content hash of the resident point set (same points => precompute products stay valid)

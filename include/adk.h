@@ -57,7 +57,7 @@ typedef struct adk_result
     int64_t entries_required;   /* myRequiredEntriesCount  (-1 when not requested) */
     uint64_t cells_nominal;     /* DP cell updates the reference executes for this call */
     uint64_t cells_executed;    /* DP cell updates the kernels executed */
-    uint64_t states;            /* area+diameter path: DP states created (reference "entries") */
+    uint64_t states;            /* area+diameter path: DP states created (reference "entries"); area path: prefix-minimum change points */
     uint64_t pairs;             /* area+diameter path: candidate pairs within the diameter bound */
     double kernel_ms;           /* device time of the whole call (CUDA events on the solver's stream) */
     double dp_ms;               /* device time of the dominant DP kernel alone */

@@ -138,6 +138,29 @@ def test_device_counters_match_the_oracle(golden, solver, oracle):
         assert g["pairs"] == o["pairs"], name
 
 
+def test_benchmark_info_counters_match_the_reference(golden, solver):
+    """MT::BenchmarkInfo (Utils.h:35-39; SURVEY 8f N2): myAllocatedEntriesCount / myRequiredEntriesCount of both paths equal the
+    unmodified reference's on every frozen run (path A: table size and prefix-minimum change points, Eppstein.cpp:171-175,228-232;
+    path AD: hash entries of every pair plus the winner's re-run, AntipodalOptimized.cpp:519-524,529-535)."""
+    checked = 0
+    for tag in ("test.A", "bench.A", "test.ADopt", "bind.ADopt.75", "bench.ADopt"):
+        for r in golden["runs"][tag][::3]:
+            pts = golden["points"][r["name"]]
+            if len(pts) > 200:
+                continue
+            x, y = xy(pts)
+            k = None if r["kmax"] >= 2 ** 63 else r["kmax"]
+            if r["algo"] == 0:
+                g = solver.solve_area(x, y, k, r["amax"], True, True)
+            else:
+                g = solver.solve_area_diameter(x, y, k, r["amax"], r["dmax"], True, True)
+            assert (g["entries_alloc"], g["entries_required"]) == (r["entries_alloc"], r["entries_required"]), (tag, r["name"])
+            checked += 1
+    assert checked >= 100
+    x, y = xy(golden["points"]["tests/30/0"])
+    assert solver.solve_area(x, y, None, 30.0, True)["entries_required"] == -1          # only on request (ADK_FLAG_COUNTERS)
+
+
 def test_edge_cases(solver):
     assert solver.solve_area([0, 1], [0, 1])["found"] == 0                              # n < 3
     assert solver.solve_area([0, 1, 0], [0, 0, 1], 2)["found"] == 0                     # K < 3
