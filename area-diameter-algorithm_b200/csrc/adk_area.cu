@@ -13,6 +13,8 @@
 #include "adk_internal.h"
 #include "adk_device.cuh"
 
+#include <cooperative_groups.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -43,6 +45,8 @@ struct AnchorInfo
     uint64_t list_cells;   // sum of slope-list lengths = reference cells per level
     uint64_t nonempty_rows;
     uint64_t required;     // prefix-minimum change points beyond the first list element (Eppstein.cpp:228-232)
+    unsigned long long lvl[3];   // best area (order-preserving bits) of the level in flight and its two neighbours
+    int32_t best_row_any, pad_;
 };
 
 // --------------------------------------------------------------------------------------------- PREP kernel
@@ -228,6 +232,7 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
         {
             A.rows = rows; A.U = s_total; A.cmax = s_cmax; A.list_cells = s_cells; A.nonempty_rows = s_nonempty;
             A.best_m = 0; A.best_area = 0.0; A.best_row = -1; A.levels_run = 0; A.required = 0;
+            A.lvl[0] = A.lvl[1] = A.lvl[2] = kInfBits; A.best_row_any = 0x7fffffff;
         }
         __syncthreads();
     }
@@ -249,20 +254,29 @@ __device__ __forceinline__ double warp_prefix_min(double v, uint32_t lane)
 }
 
 // One CTA per anchor (dynamic queue, heaviest anchor first), one warp per row, wavefront over levels.
+// One anchor per thread-block CLUSTER: the rows of the anchor are dealt over the warps of all CTAs of the cluster and
+// the levels are separated by a cluster barrier.  Anchor costs grow like a_i^3, so the heaviest anchor alone outweighs the
+// average CTA's share of a whole solve: one CTA per anchor left half of the SM time idle behind the last heavy anchors
+// (profiles/r1c_ncu_k_area_dp_n1000.txt); spreading an anchor over 8 SMs shortens that critical path 8 times.
 __global__ void __launch_bounds__(kDpThreads)
 k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
           const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc, const uint32_t* __restrict__ rowbase,
-          double* __restrict__ Tbuf, uint64_t K, double amax)
+          double* __restrict__ Tbuf, uint64_t K, double amax, unsigned int* __restrict__ cluster_next)
 {
-    __shared__ unsigned long long s_lvl[3], s_req;
-    __shared__ unsigned int s_next;
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const uint32_t crank = cluster.block_rank(), csize = cluster.num_blocks();
+    const uint32_t cid = blockIdx.x / csize;
+    __shared__ unsigned long long s_lvl, s_req;
     __shared__ int s_row;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const uint32_t gwarp = crank * nwarps + warp, gnwarps = csize * nwarps;
     for (;;)
     {
-        if (threadIdx.x == 0) s_next = atomicAdd(queue, 1u);
-        __syncthreads();
-        const uint32_t q = s_next;
+        if (crank == 0 && threadIdx.x == 0) cluster_next[cid] = atomicAdd(queue, 1u);
+        __threadfence();
+        cluster.sync();
+        const uint32_t q = *reinterpret_cast<volatile unsigned int*>(cluster_next + cid);
         if (q >= count) break;
         AnchorInfo& A = info[first + q];
         const uint32_t rows = A.rows, U = A.U, W = A.W, acap = (uint32_t) A.a, cmax = A.cmax;
@@ -270,18 +284,19 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
         const uint32_t* ansrc = nsrc + A.row_off;
         const uint32_t* abase = rowbase + A.row_off;
         double* T = Tbuf + A.t_off;
+        volatile unsigned long long* g_lvl = A.lvl;          // best area of levels m, m+1, m+2 (mod 3), shared by the cluster
         uint32_t top = 2, levels = 0;
         double best_area = 0.0;
-        if (threadIdx.x == 0) { s_lvl[0] = s_lvl[1] = s_lvl[2] = kInfBits; s_row = 0x7fffffff; s_req = 0ull; }
+        if (threadIdx.x == 0) { s_lvl = kInfBits; s_row = 0x7fffffff; s_req = 0ull; }
         unsigned int req = 0;
         __syncthreads();
         if (U > 0)
         {
             for (uint64_t m = 3; m <= K; ++m)
             {
-                if (threadIdx.x == 0) s_lvl[(m + 1) % 3] = kInfBits;
+                if (crank == 0 && threadIdx.x == 0) A.lvl[(m + 1) % 3] = kInfBits;
                 double* Tm = T + (size_t) (m % W) * U;
-                for (uint32_t jj = warp; jj < rows; jj += nwarps)
+                for (uint32_t jj = gwarp; jj < rows; jj += gnwarps)
                 {
                     const uint32_t ns = ansrc[jj];
                     if (ns == 0) continue;
@@ -303,7 +318,7 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
                                 const uint64_t lvl = m - c;
                                 double prev;
                                 if (lvl == 2) prev = 0.0;
-                                else prev = r.gidx == kNoPrev ? INFINITY : T[(size_t) (lvl % W) * U + r.gidx];
+                                else prev = r.gidx == kNoPrev ? INFINITY : __ldcg(&T[(size_t) (lvl % W) * U + r.gidx]);
                                 const double cur = __dadd_rn(prev, r.area);
                                 if (cur <= amax) val = cur;
                             }
@@ -314,24 +329,31 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
                         if (lane == 0) before = carry;
                         req += (unsigned int) __popc(__ballot_sync(0xffffffffu, k < ns && val < before))
                                - (unsigned int) __popc(__ballot_sync(0xffffffffu, head_finite));      // Eppstein.cpp:228-232
-                        if (k < ns) out[k] = val;                                   // Eppstein.cpp:234
+                        if (k < ns) __stcg(&out[k], val);                           // Eppstein.cpp:234
                         carry = __shfl_sync(0xffffffffu, val, 31);
                     }
-                    if (lane == 0 && carry < INFINITY) atomicMin(&s_lvl[m % 3], area_bits(carry));
+                    if (lane == 0 && carry < INFINITY) atomicMin(&s_lvl, area_bits(carry));
                 }
                 __syncthreads();
+                if (threadIdx.x == 0)
+                {
+                    if (s_lvl != kInfBits) atomicMin(const_cast<unsigned long long*>(&g_lvl[m % 3]), s_lvl);
+                    s_lvl = kInfBits;
+                    __threadfence();
+                }
+                cluster.sync();                          // level m is complete in every CTA of the cluster
                 ++levels;
-                const unsigned long long lb = s_lvl[m % 3];
+                const unsigned long long lb = g_lvl[m % 3];
                 if (lb != kInfBits) { top = (uint32_t) m; best_area = bits_area(lb); }
                 if (m >= (uint64_t) top + cmax) break;      // no deeper level can be finite
             }
             if (top > 2)
             {   // first row (in j order) that attains the best area at the best level (Eppstein.cpp:219-224)
                 const double* Tt = T + (size_t) (top % W) * U;
-                for (uint32_t jj = threadIdx.x; jj < rows; jj += blockDim.x)
+                for (uint32_t jj = crank * blockDim.x + threadIdx.x; jj < rows; jj += csize * blockDim.x)
                 {
                     const uint32_t ns = ansrc[jj];
-                    if (ns && Tt[abase[jj] + ns - 1] == best_area) atomicMin(&s_row, (int) jj);
+                    if (ns && __ldcg(&Tt[abase[jj] + ns - 1]) == best_area) atomicMin(&s_row, (int) jj);
                 }
             }
         }
@@ -339,10 +361,16 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
         __syncthreads();
         if (threadIdx.x == 0)
         {
-            A.levels_run = levels; A.required = s_req;
-            if (top > 2) { A.best_m = top; A.best_area = best_area; A.best_row = s_row; }
+            if (s_row != 0x7fffffff) atomicMin(&A.best_row_any, s_row);
+            if (s_req) atomicAdd(reinterpret_cast<unsigned long long*>(&A.required), s_req);
+            __threadfence();
         }
-        __syncthreads();
+        cluster.sync();
+        if (crank == 0 && threadIdx.x == 0)
+        {
+            A.levels_run = levels;
+            if (top > 2) { A.best_m = top; A.best_area = best_area; A.best_row = *reinterpret_cast<volatile int*>(&A.best_row_any); }
+        }
     }
 }
 
@@ -530,7 +558,7 @@ struct AreaPlan
     uint32_t amax_rows = 0;
 };
 
-struct SmallOut { unsigned int queue; unsigned int pad; AreaBest best; AreaHull hull; };
+struct SmallOut { unsigned int queue; unsigned int pad; AreaBest best; AreaHull hull; unsigned int cluster_next[1024]; };
 
 int area_fetch_yorder(Ctx* c, std::vector<int32_t>& yorder, std::vector<int32_t>& above)
 {
@@ -617,10 +645,24 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
         ADK_TRY(ensure(c, c->scratch5, sizeof(double) * std::max<uint64_t>(total, 1)));
         ADK_CUDA(c, cudaMemcpyAsync(d_info + b0, P.info.data() + b0, sizeof(AnchorInfo) * (b1 - b0), cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(c->small.p, 0, sizeof(unsigned int) * 2, c->stream));
-        const uint32_t grid = std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 2);
+        // cluster size by the depth of the heaviest anchor of the batch (rows / 64 warps' worth), 1 .. 8 CTAs per anchor
+        uint32_t max_rows = 1;
+        for (uint32_t t = b0; t < b1; ++t) max_rows = std::max<uint32_t>(max_rows, (uint32_t) P.info[t].a);
+        uint32_t cs = 1;
+        while (cs < 8 && max_rows >= 128u * cs) cs *= 2;
+        const uint32_t nclusters = std::max<uint32_t>(1, std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 2 / cs));
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
-        k_area_dp<<<grid, kDpThreads, 0, c->stream>>>(d_info, b0, b1 - b0, &c->small.as<SmallOut>()->queue, d_recs, d_nsrc, d_rowbase,
-                                                      c->scratch5.as<double>(), K, amax);
+        {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(nclusters * cs); cfg.blockDim = dim3(kDpThreads); cfg.dynamicSmemBytes = 0; cfg.stream = c->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            SmallOut* so_ = c->small.as<SmallOut>();
+            ADK_CUDA(c, cudaLaunchKernelEx(&cfg, k_area_dp, d_info, b0, b1 - b0, &so_->queue, (const SrcRec*) d_recs, (const uint32_t*) d_nsrc,
+                                           (const uint32_t*) d_rowbase, c->scratch5.as<double>(), K, amax, so_->cluster_next));
+        }
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
         ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
