@@ -1,5 +1,6 @@
 #!/usr/bin/env bash
-# Builds the reference's UNMODIFIED gtest (src/test/main.cpp) and pybind module (src/py-binding/main.cpp) against this
+# Builds the reference's UNMODIFIED gtest (src/test/main.cpp), pybind module (src/py-binding/main.cpp) and google-benchmark
+# driver (src/bench/main.cpp) against this
 # repo's GPU-backed libadk_host.so instead of the reference's src/common solver sources.  Proves the drop-in boundary:
 # same headers (the reference's own declarations), our definitions at link time.  Only Parser.cpp (JSON I/O, not on the
 # solver path) is taken from the reference.  Needs /root/reference; outputs go to tests/dropin/_build (git-ignored).
@@ -36,4 +37,20 @@ pbinc="$(python -c 'import pybind11; print(pybind11.get_include())')"
 ext="$(python -c 'import sysconfig; print(sysconfig.get_config_var("EXT_SUFFIX"))')"
 g++ "${common[@]}" -fPIC -shared -I"$pyinc" -I"$pbinc" "$ref/src/py-binding/main.cpp" -o "$out/thesis$ext" \
     -L"$pkg" -ladk_host -ladk -Wl,-rpath,"$pkg" -Wl,-rpath,'$ORIGIN/../../../area-diameter-algorithm_b200'
-echo "built $out/ref_test_dropin $out/thesis$ext"
+# the reference's google-benchmark driver (src/bench/main.cpp), same treatment; google/benchmark itself is compiled from
+# the sources vendored by the reference (external/benchmark/src/*.cc, plain g++, no cmake)
+gb="$ref/external/benchmark"
+if [ -d "$gb/src" ]; then
+  mkdir -p "$out/gbench"
+  if [ ! -f "$out/gbench/benchmark.o" ]; then
+    for f in "$gb"/src/*.cc; do
+      b="$(basename "$f" .cc)"; [ "$b" = benchmark_main ] && continue
+      g++ -std=c++17 -O1 -w -I"$gb/include" -I"$gb/src" -DHAVE_STD_REGEX -DHAVE_STEADY_CLOCK -DNDEBUG -DBENCHMARK_STATIC_DEFINE -c "$f" -o "$out/gbench/$b.o" &
+    done
+    wait
+  fi
+  g++ "${common[@]}" -I"$gb/include" -DBENCHMARK_STATIC_DEFINE -c "$ref/src/bench/main.cpp" -o "$out/ref_bench_main.o"
+  g++ "$out/ref_bench_main.o" "$out/Parser.o" "$out"/gbench/*.o -o "$out/ref_bench_dropin" \
+      -L"$pkg" -ladk_host -ladk -Wl,-rpath,"$pkg" -Wl,-rpath,'$ORIGIN/../../../area-diameter-algorithm_b200' -lpthread
+fi
+echo "built $out/ref_test_dropin $out/thesis$ext $out/ref_bench_dropin"

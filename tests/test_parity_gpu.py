@@ -10,7 +10,7 @@ import sys
 import pytest
 
 from util import (ROOT, xy, assert_same_solution, float32_equal, same_cycle, check_witness, write_reference_layout,
-                  polygon_area)
+                  write_experiments_layout, polygon_area)
 
 pytestmark = pytest.mark.gpu
 
@@ -275,6 +275,45 @@ def test_reference_gtest_binary_runs_against_the_gpu_library(golden, built):
     p = subprocess.run([exe], capture_output=True, text=True, timeout=1500, cwd=ROOT)
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
     assert "[  PASSED  ] 1 test" in p.stdout
+
+
+def test_reference_bench_driver_runs_against_the_gpu_library(golden, built):
+    """The reference's own google-benchmark driver (src/bench/main.cpp, compiled unmodified against libadk_host.so) on the GPU:
+    it prints its counter columns and appends to benchmark_results.json in the reference's schema (bench/main.cpp:113-155,
+    Parser.cpp:5-33); the solutions it records equal the unmodified reference's frozen outputs."""
+    import json
+    exe = os.path.join(ROOT, "tests", "dropin", "_build", "ref_bench_dropin")
+    if not os.path.exists(exe):
+        pytest.skip("tests/dropin/_build/ref_bench_dropin not present (built only where /root/reference exists)")
+    data = os.path.join(ROOT, "tests", "dropin", "_data")
+    write_experiments_layout(golden, data, [("uniform", 10), ("uniform", 0)])
+    res = os.path.join(data, "benchmark_results.json")
+    if os.path.exists(res):
+        os.unlink(res)
+    p = subprocess.run([exe, "--benchmark_filter=^(Antipodal/Uniform/10/2|Eppstein/Uniform/0)/"], capture_output=True, text=True,
+                       timeout=1500, cwd=ROOT)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-2000:]
+    assert "min_entries" in p.stdout and "Antipodal/Uniform/10/2" in p.stdout and "Eppstein/Uniform/0" in p.stdout, p.stdout[-2000:]
+    with open(res) as f:
+        out = json.load(f)
+    # (the reference appends every benchmark's solutions as ONE array element: results is a list of lists, bench/main.cpp:148)
+    flat = [r for grp in out["results"] for r in (grp if isinstance(grp, list) else [grp])]
+    assert out["count"] == 200 and len(flat) == 200
+    by_name = {r["name"]: r for r in flat}
+    checked = 0
+    for tag, prefix, kind, dmax in (("bench.ADopt", "Antipodal/Uniform/10/2/iterations:100", "uniform/10", 4.0),
+                                    ("bench.A", "Eppstein/Uniform/0/iterations:100", "uniform/0", float("inf"))):
+        for r in golden["runs"][tag]:
+            if not r["name"].startswith(kind + "/") or float(r["dmax"]) != dmax:
+                continue
+            i = int(r["name"].rsplit("/", 1)[1])
+            got = by_name[[k for k in by_name if k.startswith(prefix.rsplit(":", 1)[0]) and k.endswith(f"iterations:{i}")][0]]
+            ca = got["convex_area"]
+            assert ca["count"] == r["count"] and same_cycle(ca["hull_indices"], r["hull"]), (tag, r["name"])
+            assert abs(ca["area"] - r["area"]) <= 1e-9 * r["area"]
+            assert sorted(ca["diameter_indices"]) == sorted(r["diam"])
+            checked += 1
+    assert checked >= 8
 
 
 def test_reference_pybind_module_runs_against_the_gpu_library(golden, built):

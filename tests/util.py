@@ -103,3 +103,18 @@ def write_reference_layout(golden, dest):
             results.append(r)
         with open(os.path.join(d, "results.json"), "w") as f:
             json.dump({"count": len(results), "results": results}, f)
+
+
+def write_experiments_layout(golden, dest, folders):
+    """Re-creates data/samples/experiments/<kind>/<idx>/points_{0..99}.json for the reference's bench driver
+    (src/bench/main.cpp:28-33,78): the committed golden point sets of that folder, repeated cyclically to 100 files."""
+    for kind, idx in folders:
+        names = sorted((k for k in golden["points"] if k.startswith(f"{kind}/{idx}/")), key=lambda k: int(k.rsplit("/", 1)[1]))
+        assert names, (kind, idx)
+        d = os.path.join(dest, "experiments", kind, str(idx))
+        os.makedirs(d, exist_ok=True)
+        for i in range(100):
+            pts = golden["points"][names[i % len(names)]]
+            with open(os.path.join(d, f"points_{i}.json"), "w") as f:
+                json.dump({"points": [{"x": p[0], "y": p[1]} for p in pts], "count": len(pts)}, f)
+    return dest
