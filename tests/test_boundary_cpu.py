@@ -159,3 +159,22 @@ def test_two_rank_batch_gather_over_gloo(built):
         assert p.exitcode == 0
     for rank, allr in got:
         assert allr == [{"count": 10 + i, "owner": i % 2} for i in range(5)]
+
+
+def test_tiled_workflow_window_grid_equals_the_reference(built):
+    """tiling.make_patches against the reference's own create_patch_dict (frozen by tests/golden/make_tiled_golden.py):
+    same number of non-empty windows, visited by population, largest first (no device needed)."""
+    import json
+    from importlib import import_module
+    built.load_package()
+    tiling = import_module("area_diameter_algorithm_b200.tiling")
+    with open(os.path.join(ROOT, "tests", "golden", "tiled_area.json")) as f:
+        cases = json.load(f)["cases"]
+    with open(os.path.join(ROOT, "tests", "golden", "points.json")) as f:
+        pts = json.load(f)
+    for c in cases:
+        xy, keep, order, member = tiling.make_patches(pts[c["name"]], c["patch_size"], c["step_size"])
+        assert len(order) == c["patches"], c["name"]
+        pops = [len(member(w)) for w in order]
+        assert pops == sorted(pops, reverse=True) and pops[-1] >= 1
+        assert len(xy) == len(set(map(tuple, pts[c["name"]])))

@@ -228,6 +228,23 @@ def pkg_algo(solver, which):
     return capi.ALGO_AREA if which == "A" else capi.ALGO_AREA_DIAMETER
 
 
+def test_tiled_area_workflow_equals_the_reference(solver):
+    """run_area_only_tiled (Area-Selector, quality_of_results_comparison.py:77-103) on the GPU against outputs of the reference's
+    own create_patch_dict + unmodified solver, frozen in tests/golden/tiled_area.json: same polygon, same number of windows solved."""
+    import json
+    tiling = importlib.import_module("area_diameter_algorithm_b200.tiling")
+    with open(os.path.join(ROOT, "tests", "golden", "tiled_area.json")) as f:
+        cases = json.load(f)["cases"]
+    with open(os.path.join(ROOT, "tests", "golden", "points.json")) as f:
+        pts = json.load(f)
+    for c in cases:
+        got = tiling.solve_area_tiled(solver, pts[c["name"]], c["patch_size"], c["step_size"], None, c["max_area"])
+        assert got["found"] == int(c["found"]) and got["count"] == c["count"], (c["name"], c["step_size"], got)
+        assert abs(got["area"] - c["area"]) <= 1e-9 * c["area"]
+        assert same_cycle(got["hull"], c["hull"]), (c["name"], got["hull"], c["hull"])
+        assert (got["patches"], got["solved"]) == (c["patches"], c["solved"])
+
+
 # ------------------------------------------------------------------------------------------------ full-size properties
 def _synth():
     import __graft_entry__ as ge
