@@ -896,6 +896,7 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
     uint32_t k = kopt;
     while (ok && k > 0)
     {
+        if (a + b >= nl + nr) { ok = 0; break; }     // exactly degenerate input: a step that consumes no point must not run away
         const bool rt = e_right;
         const double* ownx = rt ? S.Rx : S.Lx; const double* owny = rt ? S.Ry : S.Ly;
         const double* othx = rt ? S.Lx : S.Rx; const double* othy = rt ? S.Ly : S.Ry;

@@ -427,21 +427,29 @@ __device__ void hull_diameter_dev(const double* x, const double* y, const int32_
 #define ADK_HA(p, q, r) signed_area(x[hull[p]], y[hull[p]], x[hull[q]], y[hull[q]], x[hull[r]], y[hull[r]])
 #define ADK_NX(v) (((v) + 1) % cnt)
 #define ADK_VISIT(p, q) { const double d = dist2(x[hull[p]], y[hull[p]], x[hull[q]], y[hull[q]]); if (d > best) { best = d; ba = (p); bb = (q); } }
+    // The walk below terminates on a strictly convex cycle; on a degenerate one (collinear vertices: exactly equal areas in
+    // binary64, where the reference's 80-bit arithmetic happens to break the ties) it can circle forever, so it is
+    // given a step budget and falls back to the plain farthest pair of the cycle.
+    uint32_t budget = 8 * cnt + 32;
+    bool gave_up = false;
     if (cnt > 2)
     {
         uint32_t pi = cnt - 1, qi = 0;
-        while (ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)) > ADK_HA(pi, ADK_NX(pi), qi)) qi = ADK_NX(qi);
+        while (ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)) > ADK_HA(pi, ADK_NX(pi), qi)) { qi = ADK_NX(qi); if (--budget == 0) { gave_up = true; break; } }
         const uint32_t q0 = qi;
-        while (qi != 0)
+        while (qi != 0 && !gave_up)
         {
+            if (--budget == 0) { gave_up = true; break; }
             pi = ADK_NX(pi);
             ADK_VISIT(pi, qi)
             while (ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)) > ADK_HA(pi, ADK_NX(pi), qi))
             {
+                if (--budget == 0) { gave_up = true; break; }
                 qi = ADK_NX(qi);
                 if (pi != q0 || qi != 0) ADK_VISIT(pi, qi)
                 else break;
             }
+            if (gave_up) break;
             const double diff = __dsub_rn(ADK_HA(pi, ADK_NX(pi), ADK_NX(qi)), ADK_HA(pi, ADK_NX(pi), qi));
             if (near_zero(diff))
             {
@@ -449,6 +457,11 @@ __device__ void hull_diameter_dev(const double* x, const double* y, const int32_
                 else break;
             }
         }
+    }
+    if (gave_up)
+    {
+        best = 0.0; ba = 0; bb = 0;
+        for (uint32_t a = 0; a < cnt; ++a) for (uint32_t b = a + 1; b < cnt; ++b) ADK_VISIT(a, b)
     }
     out[0] = (uint32_t) hull[ba]; out[1] = (uint32_t) hull[bb];
 #undef ADK_HA
@@ -478,8 +491,10 @@ __global__ void k_area_backtrack(const double* __restrict__ x, const double* __r
     uint32_t m = best_m, h = 0, ok = 1;
     int row = best_row;
     hull[h++] = A.pt;
-    while (m > 2)
+    const uint32_t hcap = A.rows + 2;        // a polygon has at most rows + 1 vertices; on exactly degenerate inputs a step can
+    while (m > 2)                            // consume no point (c = 0) and the walk must not run away
     {
+        if (h >= hcap) { ok = 0; break; }
         const int last = hull[h - 1], j = arowpt[row];
         const uint32_t ns = ansrc[row];
         const double* Tm = T + (size_t) (m % W) * U + abase[row];

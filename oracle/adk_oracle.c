@@ -316,21 +316,29 @@ static void hull_diameter(const pts_t* P, const int32_t* hull, uint32_t cnt, uin
 #define HA(p, q, r) sarea(P, hull[p], hull[q], hull[r])
 #define NX(v) (((v) + 1) % cnt)
     diam_acc acc = { 0.0, 0, 0, P, hull };
+    /* Step budget: on a degenerate cycle (collinear vertices, exactly equal areas in binary64 where the reference's 80-bit
+     * arithmetic happens to break the ties) the walk can circle forever; it then falls back to the plain farthest pair.
+     * Same rule as the CUDA path (adk_area.cu, hull_diameter_dev). */
+    uint32_t budget = 8 * cnt + 32;
+    int gave_up = 0;
     if (cnt > 2)
     {
         uint32_t pi = cnt - 1, qi = 0;
-        while (HA(pi, NX(pi), NX(qi)) > HA(pi, NX(pi), qi)) qi = NX(qi);
+        while (HA(pi, NX(pi), NX(qi)) > HA(pi, NX(pi), qi)) { qi = NX(qi); if (--budget == 0) { gave_up = 1; break; } }
         const uint32_t q0 = qi;
-        while (qi != 0)
+        while (qi != 0 && !gave_up)
         {
+            if (--budget == 0) { gave_up = 1; break; }
             pi = NX(pi);
             diam_visit(&acc, pi, qi);
             while (HA(pi, NX(pi), NX(qi)) > HA(pi, NX(pi), qi))
             {
+                if (--budget == 0) { gave_up = 1; break; }
                 qi = NX(qi);
                 if (pi != q0 || qi != 0) diam_visit(&acc, pi, qi);
                 else break;
             }
+            if (gave_up) break;
             const double diff = HA(pi, NX(pi), NX(qi)) - HA(pi, NX(pi), qi);
             if (near_zero(diff))
             {
@@ -338,6 +346,11 @@ static void hull_diameter(const pts_t* P, const int32_t* hull, uint32_t cnt, uin
                 else break;
             }
         }
+    }
+    if (gave_up)
+    {
+        acc.best = 0.0; acc.a = 0; acc.b = 0;
+        for (uint32_t a = 0; a < cnt; ++a) for (uint32_t b = a + 1; b < cnt; ++b) diam_visit(&acc, a, b);
     }
     out[0] = (uint32_t) hull[acc.a];
     out[1] = (uint32_t) hull[acc.b];
@@ -541,7 +554,7 @@ int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax,
             uint32_t h = 0;
             int32_t* hl = (int32_t*) malloc(sizeof(int32_t) * (n + 2));
             hl[h++] = best_i;
-            while (m > 2)
+            while (m > 2 && h < n)          /* h < n: on exactly degenerate inputs a step can consume no point (count 0) */
             {
                 const int lastp = hl[h - 1];
                 const int32_t* ring_j = cw + (size_t) j * len;
@@ -826,7 +839,7 @@ static uint32_t reconstruct_AD(const pts_t* P, const tables_t* T, const int32_t*
     int32_t* right = (int32_t*) malloc(sizeof(int32_t) * (n + 4));
     uint32_t a = 0, b = 0;
     if (en.side >= SIDE_RR) left[a++] = E; else right[b++] = S;
-    while (k > 0)
+    while (k > 0 && a + b < n + 2)     /* the bound only matters on exactly degenerate inputs (a step that consumes no point) */
     {
         uint64_t key = 0; int done = 0;
         switch (en.side)

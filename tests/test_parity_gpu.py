@@ -138,6 +138,36 @@ def test_device_counters_match_the_oracle(golden, solver, oracle):
         assert g["pairs"] == o["pairs"], name
 
 
+@pytest.mark.timeout(120)
+def test_exactly_degenerate_inputs_terminate(pkg, solver):
+    """Lattice subsets: many exactly collinear triples and equal coordinates.  The reference's answers on such inputs hinge on
+    80-bit tie-breaks, so there is no parity claim; what is guaranteed is that every call returns
+    (step budgets in the calipers and in both back-walks) with a status, and that whatever is returned is well-formed."""
+    rng = random.Random(99)
+    done = 0
+    for trial in range(60):
+        g = rng.choice([4, 5, 6, 7])
+        n = min(rng.choice([6, 10, 16, 24, 36]), g * g)
+        cells = rng.sample([(i, j) for i in range(g) for j in range(g)], n)
+        sc = rng.choice([1.0, 0.5, 1.7])
+        x = [c[0] * sc for c in cells]
+        y = [c[1] * sc for c in cells]
+        k = rng.choice([None, 4, 6])
+        a = rng.choice([2.0, 6.0, float("inf")])
+        d = rng.choice([2.0, 3.5, float("inf")])
+        for call in (lambda: solver.solve_area(x, y, k, a, True), lambda: solver.solve_area_diameter(x, y, k, a, d, True)):
+            try:
+                r = call()
+            except pkg.AdkError as e:
+                assert "reconstruct" in str(e) or "walked off" in str(e), e      # a refused witness, never a crash
+                continue
+            done += 1
+            if r["found"]:
+                assert 3 <= r["count"] <= n and r["area"] >= 0.0 and (a == float("inf") or r["area"] <= a * (1 + 1e-9))
+                assert len(r["hull"]) <= n and all(0 <= v < n for v in r["hull"])
+    assert done >= 100
+
+
 def test_benchmark_info_counters_match_the_reference(golden, solver):
     """MT::BenchmarkInfo (Utils.h:35-39; SURVEY 8f N2): myAllocatedEntriesCount / myRequiredEntriesCount of both paths equal the
     unmodified reference's on every frozen run (path A: table size and prefix-minimum change points, Eppstein.cpp:171-175,228-232;
