@@ -81,19 +81,37 @@ __device__ __forceinline__ double proj_dist2(double sx, double sy, double tx, do
 
 // --------------------------------------------------------------------------------------------- candidate enumeration
 
-// One warp per pair (i < j) within the diameter bound: count its lune, size its tables, queue it.
-__global__ void k_ad_pairs(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, double dmax2,
-                           uint64_t kmax, uint32_t shard, uint32_t nshards,
-                           PairRec* __restrict__ pairs, PairStats* __restrict__ stats)
+// Queues a candidate of this shard and folds it into the launch statistics.
+__device__ __forceinline__ void queue_pair(PairRec* __restrict__ pairs, PairStats* __restrict__ stats, uint32_t i, uint32_t j,
+                                           uint32_t nl, uint32_t nr, unsigned int lim)
 {
+    const uint32_t slot = atomicAdd(&stats->nqueued, 1u);
+    pairs[slot] = PairRec{i, j, nl, nr};
+    const unsigned long long cells = (unsigned long long) nl * nr;
+    atomicMax(&stats->max_nl, nl); atomicMax(&stats->max_nr, nr); atomicMax(&stats->max_lim, lim);
+    atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2) / 2);
+    atomicAdd(&stats->hist[cost_bucket(nl, nr)], 1u);
+    const unsigned long long cost = cells * (nl + nr);
+    atomicAdd(&stats->cost_sum, cost); atomicMax(&stats->cost_max, cost);
+}
+
+// One warp per pair (i < j) within the diameter bound: count its lune, size its tables.  With one shard the pair is queued
+// right away; with several (dense != nullptr) every rank writes the sizes of ALL candidates into a dense n x n table plus a
+// per-row histogram of cost classes, and k_ad_deal deals them out (below).
+__global__ void k_ad_pairs(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, double dmax2,
+                           uint64_t kmax, PairRec* __restrict__ pairs, PairStats* __restrict__ stats,
+                           uint32_t* __restrict__ dense, uint32_t* __restrict__ rowhist)
+{
+    __shared__ uint32_t s_hist[kCostBuckets];
     const uint32_t i = blockIdx.x;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    if (dense) { for (uint32_t b = threadIdx.x; b < (uint32_t) kCostBuckets; b += blockDim.x) s_hist[b] = 0; __syncthreads(); }
     const double sx = x[i], sy = y[i];
     for (uint32_t j = i + 1 + warp; j < n; j += nwarps)
     {
         const double tx = x[j], ty = y[j];
         const double d2 = dist2(sx, sy, tx, ty);
-        if (!(d2 <= dmax2)) continue;                        // AntipodalOptimized.cpp:500
+        if (!(d2 <= dmax2)) { if (dense && lane == 0) dense[(size_t) i * n + j] = 0; continue; }      // AntipodalOptimized.cpp:500
         uint32_t cl = 0, cr = 0;
         for (uint32_t p = lane; p < n; p += 32)
         {
@@ -108,18 +126,67 @@ __global__ void k_ad_pairs(const double* __restrict__ x, const double* __restric
             const uint32_t nl = cl + 2, nr = cr + 2;
             const uint64_t inner = (uint64_t) cl + cr;
             const uint64_t lim = kmax - 2 < inner ? kmax - 2 : inner;      // :137
-            const uint64_t key = (uint64_t) i * n + j;
-            if (lim > 0 && key % nshards == shard)
+            if (dense)
             {
-                const uint32_t slot = atomicAdd(&stats->nqueued, 1u);
-                pairs[slot] = PairRec{i, j, nl, nr};
-                const unsigned long long cells = (unsigned long long) nl * nr;
-                atomicMax(&stats->max_nl, nl); atomicMax(&stats->max_nr, nr); atomicMax(&stats->max_lim, (unsigned int) lim);
-                atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2) / 2);
-                atomicAdd(&stats->hist[cost_bucket(nl, nr)], 1u);
-                const unsigned long long cost = cells * (nl + nr);
-                atomicAdd(&stats->cost_sum, cost); atomicMax(&stats->cost_max, cost);
+                dense[(size_t) i * n + j] = lim > 0 ? (nl | (nr << 16)) : 0u;
+                if (lim > 0) atomicAdd(&s_hist[cost_bucket(nl, nr)], 1u);
             }
+            else if (lim > 0) queue_pair(pairs, stats, i, j, nl, nr, (unsigned int) lim);
+        }
+    }
+    if (dense)
+    {
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b < (uint32_t) kCostBuckets; b += blockDim.x) rowhist[(size_t) i * kCostBuckets + b] = s_hist[b];
+    }
+}
+
+// Deals the candidates over the shards of a multi-GPU solve.  Every rank sees the same dense table, so every rank can
+// compute each candidate's position in the common order (cost class descending, then pair key ascending) with integer
+// arithmetic only, and keeps the candidates whose position is congruent to its shard: a round-robin over the sorted
+// list.  The loads of the shards then differ by well under 1 % (by key modulo they differed by 5-22 % at 8 shards on
+// the bench sweep), and no rank needs to talk to another one.  One CTA per row i; warp 0 walks the row in key order.
+__global__ void k_ad_deal(uint32_t n, uint64_t kmax, uint32_t shard, uint32_t nshards, const uint32_t* __restrict__ dense,
+                          const uint32_t* __restrict__ rowhist, PairRec* __restrict__ pairs, PairStats* __restrict__ stats)
+{
+    __shared__ uint32_t s_run[kCostBuckets];     // candidates of the class in earlier rows (then: earlier in key order)
+    __shared__ uint32_t s_off[kCostBuckets];     // candidates of heavier classes
+    const uint32_t i = blockIdx.x, lane = threadIdx.x & 31;
+    if (threadIdx.x < (uint32_t) kCostBuckets)
+    {
+        uint32_t before = 0, total = 0;
+        for (uint32_t r = 0; r < n; ++r)
+        {
+            const uint32_t h = rowhist[(size_t) r * kCostBuckets + threadIdx.x];
+            before += r < i ? h : 0u; total += h;
+        }
+        s_run[threadIdx.x] = before; s_off[threadIdx.x] = total;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        uint32_t run = 0;
+        for (int b = kCostBuckets - 1; b >= 0; --b) { const uint32_t t = s_off[b]; s_off[b] = run; run += t; }
+    }
+    __syncthreads();
+    if (threadIdx.x >= 32) return;
+    for (uint32_t j0 = i + 1; j0 < n; j0 += 32)
+    {
+        const uint32_t j = j0 + lane;
+        const uint32_t v = j < n ? dense[(size_t) i * n + j] : 0u;
+        const uint32_t nl = v & 0xffffu, nr = v >> 16;
+        const uint32_t cls = v ? cost_bucket(nl, nr) : 0xffffffffu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, cls);
+        const uint32_t r = __popc(peers & ((1u << lane) - 1u));
+        uint32_t pos = 0;
+        if (v) pos = s_off[cls] + s_run[cls] + r;
+        __syncwarp();
+        if (v && r + 1 == (uint32_t) __popc(peers)) s_run[cls] += r + 1;
+        __syncwarp();
+        if (v && pos % nshards == shard)
+        {
+            const uint64_t inner = (uint64_t) nl + nr - 4;
+            queue_pair(pairs, stats, i, j, nl, nr, (unsigned int) (kmax - 2 < inner ? kmax - 2 : inner));
         }
     }
 }
@@ -1134,10 +1201,24 @@ int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, 
     ADK_TRY(ensure(c, c->small, sizeof(AdSmall)));
     AdSmall* sm = c->small.as<AdSmall>();
     ADK_CUDA(c, cudaMemsetAsync(sm, 0, sizeof(AdSmall), c->stream));
-    k_ad_pairs<<<n, 256, 0, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, dmax2, kmax, shard, nshards,
-                                         c->scratch0.as<PairRec>(), &sm->stats);
+    uint32_t* dense = nullptr; uint32_t* rowhist = nullptr;
+    if (nshards > 1)
+    {
+        if (n > 0xffffu) { c->err = "area+diameter shards: n too large for the dense candidate table"; return ADK_ERR_ARG; }
+        ADK_TRY(ensure(c, c->scratch1, sizeof(uint32_t) * (size_t) n * n));
+        ADK_TRY(ensure(c, c->scratch2, sizeof(uint32_t) * (size_t) n * kCostBuckets));
+        dense = c->scratch1.as<uint32_t>(); rowhist = c->scratch2.as<uint32_t>();
+    }
+    k_ad_pairs<<<n, 256, 0, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, dmax2, kmax, c->scratch0.as<PairRec>(), &sm->stats,
+                                         dense, rowhist);
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());
+    if (nshards > 1)
+    {
+        k_ad_deal<<<n, 128, 0, c->stream>>>(n, kmax, shard, nshards, dense, rowhist, c->scratch0.as<PairRec>(), &sm->stats);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+    }
     PairStats ps;
     ADK_CUDA(c, cudaMemcpyAsync(&ps, &sm->stats, sizeof(ps), cudaMemcpyDeviceToHost, c->stream));
     ADK_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -34,6 +34,40 @@ def merge_partials(parts):
     return best if best is not None else {"found": 0, "count": 0, "area": 0.0, "tie_key": 0, "w0": 0, "w1": 0}
 
 
+def owner_of(best, parts):
+    """The rank whose partial IS the merged best (a candidate pair / anchor belongs to exactly one shard, and tie_key names
+    it): the winner's records are still resident on that rank, so it reconstructs without re-running anything."""
+    if not best["found"]:
+        return 0
+    for r, p in enumerate(parts):
+        if p["found"] and p["count"] == best["count"] and p["tie_key"] == best["tie_key"] and p["area"] == best["area"]:
+            return r
+    return 0
+
+
+def share_result(result, owner, n, device=None, group=None):
+    """The witness travels from the rank that reconstructed it to every rank: one broadcast of (n + 8) 8-byte words
+    (found, count, area, diameter pair, hull).  `result` is the owner's result dict (ignored elsewhere)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return result
+    dev = device if device is not None else torch.device("cpu")
+    rank = dist.get_rank(group)
+    if rank == owner:
+        hull = [int(v) for v in result["hull"]]
+        d = result["diam"]
+        words = [int(result["found"]), int(result["count"]), struct.unpack("<q", struct.pack("<d", float(result["area"])))[0],
+                 len(hull), 1 if d else 0, int(d[0]) if d else 0, int(d[1]) if d else 0, 0]
+        t = torch.tensor(words + hull + [0] * (n - len(hull)), dtype=torch.int64).to(dev)
+    else:
+        t = torch.empty(n + 8, dtype=torch.int64, device=dev)
+    dist.broadcast(t, src=dist.get_global_rank(group, owner) if group is not None else owner, group=group)
+    if rank == owner:
+        return result
+    w = t.cpu().tolist()
+    return {"found": w[0], "count": w[1], "area": struct.unpack("<d", struct.pack("<q", w[2]))[0], "hull": w[8:8 + w[3]],
+            "diam": [w[5], w[6]] if w[4] else None}
+
+
 def gather_partials(partial, device=None, group=None):
     """All-gather of one 32-byte record per rank; returns the list of every rank's partial."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
@@ -77,7 +111,7 @@ def solve_batch_pair_sharded(solver, point_sets, kmax, amax, dmax, reconstruct=T
     """A batch of area+diameter instances with EVERY instance's candidate pairs sharded over the ranks (instead of whole
     instances): the right split when one instance dominates the batch (the densest cell sample is 60 % of config 5).
     Per instance: adk_area_diameter_partial on every rank, one 32-byte all-gather, and the rank that owns the winning
-    pair (tie key mod world: its records are still resident) reconstructs.  Returns (complete result list, my cell count)."""
+    pair (owner_of: its records are still resident) reconstructs.  Returns (complete result list, my cell count)."""
     world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
     rank = dist.get_rank(group) if world > 1 else 0
     results, my_cells, my_dp_ms = [None] * len(point_sets), 0, 0.0
@@ -87,8 +121,9 @@ def solve_batch_pair_sharded(solver, point_sets, kmax, amax, dmax, reconstruct=T
         part, st = solver.area_diameter_partial(x, y, kmax, amax, dmax, rank, world)
         my_cells += st["cells_executed"]
         my_dp_ms += st["dp_ms"]
-        best = merge_partials(gather_partials(part, device=device, group=group))
-        owner = best["tie_key"] % world if best["found"] else 0
+        parts = gather_partials(part, device=device, group=group)
+        best = merge_partials(parts)
+        owner = owner_of(best, parts)
         if rank == owner:
             results[i] = solver.area_diameter_finish(x, y, kmax, amax, dmax, best, reconstruct)
     return gather_batch_results(results, group=group), my_cells, my_dp_ms

@@ -3,8 +3,9 @@
 n = 200, diameter sweep D in {2,3,4,5,6}, A = 4, K = inf, reconstruct = true — the call shape of src/bench/main.cpp:57-59,100).
 
 One STEP = the whole diameter sweep on one point set: five MT::AntipodalOptimizedAlgorithm-equivalent solves.
-Candidate diameter pairs are sharded over the ranks (adk_area_diameter_partial*, shard = rank), the only exchange is a
-32-byte record per rank per solve (all-gather), rank 0 reconstructs the witness.  Total work is fixed as N grows: "strong".
+Candidate diameter pairs are dealt over the ranks (adk_area_diameter_partial*, shard = rank; cost-sorted round robin), the
+only exchanges are a 32-byte record per rank per solve (all-gather) and the witness (one broadcast of n + 8 words from the
+rank that owns the winning pair, which reconstructs it from its resident records).  Total work is fixed as N grows: "strong".
 
   value : DP cell updates/s (one cell = one iteration of AntipodalOptimized.cpp:198,225,271,298; counted in-kernel and
           equal to the instrumented oracle's count), inputs resident in HBM, device-timed over K steps, max over ranks.
@@ -247,12 +248,16 @@ def run_b200_arm(args):
             else:
                 part, st = solver.area_diameter_partial_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, rank, world)
             cells += st["cells_executed"]; states += st["states"]; dp_ms += st["dp_ms"]
-            best = adist.merge_partials(adist.gather_partials(part, device=dev))
-            if rank == 0:
+            parts = adist.gather_partials(part, device=dev)
+            best = adist.merge_partials(parts)
+            owner = adist.owner_of(best, parts)          # its records are still resident: no re-run of the winning pair
+            r = None
+            if rank == owner:
                 if resident:
-                    results.append(solver.area_diameter_finish_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, d, best, True))
+                    r = solver.area_diameter_finish_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, d, best, True)
                 else:
-                    results.append(solver.area_diameter_finish_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, best, True))
+                    r = solver.area_diameter_finish_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, best, True)
+            results.append(adist.share_result(r, owner, n, device=dev))
         return cells, states, dp_ms, results
 
     def timed(resident, steps, warmup):

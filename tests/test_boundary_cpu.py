@@ -88,12 +88,15 @@ def _gloo_worker(rank, world, port, q):
     parts = d.gather_partials(mine)
     best = d.merge_partials(parts)
     tot = d.gather_stats_sum([10.0 * (rank + 1), 1.0])
+    owner = d.owner_of(best, parts)
+    res = {"found": 1, "count": 9, "area": 2.5, "hull": [1, 3, 7, 2], "diam": [1, 7], "kernel_ms": 0.1} if rank == owner else None
+    shared = d.share_result(res, owner, 12)
     dist.destroy_process_group()
-    q.put((rank, best, len(parts), tot))
+    q.put((rank, best, len(parts), tot, owner, shared))
 
 
 def test_two_rank_gather_and_merge_over_gloo(built):
-    """The only exchange of the multi-GPU path (one 32-byte record per rank), world_size 2 on CPU."""
+    """The exchanges of the multi-GPU path (one 32-byte record per rank, then the witness from its owner), world_size 2 on CPU."""
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -105,10 +108,12 @@ def test_two_rank_gather_and_merge_over_gloo(built):
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, best, nparts, tot in got:
+    for rank, best, nparts, tot, owner, shared in got:
         assert nparts == 2
         assert best == dict(found=1, count=9, area=2.5, tie_key=17, w0=1, w1=7)
         assert tot == [30.0, 2.0]
+        assert owner == 1                                    # the rank whose partial is the merged best reconstructs ...
+        assert (shared["found"], shared["count"], shared["area"], shared["hull"], shared["diam"]) == (1, 9, 2.5, [1, 3, 7, 2], [1, 7])   # ... and every rank gets the witness
 
 
 def test_batch_assignment_is_lpt_and_deterministic(pkg):

@@ -219,6 +219,40 @@ def test_shards_merge_to_the_whole_solve(golden, solver, nshards):
         assert sum(p[1]["cells_executed"] for p in ps) == whole["cells_executed"]
 
 
+def test_dealt_shards_are_balanced_and_the_owner_reconstructs_from_resident_records(pkg, solver):
+    """Multi-GPU shape on one device: one context per rank.  The candidates are dealt cost-sorted round robin (k_ad_deal), so
+    the shards' executed cells differ by a few per cent at most; the context that owns the winning pair reconstructs it from
+    its resident records, and gets the whole solve's answer."""
+    dist = importlib.import_module("area_diameter_algorithm_b200.dist")
+    pts = _synth().gaussian_points(200, 1.5, 200)
+    x, y = xy(pts)
+    world = 4
+    ranks = [pkg.Solver(0) for _ in range(world)]
+    try:
+        for r in ranks:
+            r.set_memory_budget(16 << 30)          # four contexts share this one device
+        for d in (3.0, 6.0):
+            whole = solver.solve_area_diameter(x, y, None, 4.0, d, True)
+            ps = [ranks[r].area_diameter_partial(x, y, None, 4.0, d, r, world) for r in range(world)]
+            cells = [p[1]["cells_executed"] for p in ps]
+            assert sum(cells) == whole["cells_executed"]
+            assert max(cells) <= 1.05 * (sum(cells) / world), cells
+            parts = [p[0] for p in ps]
+            best = dist.merge_partials(parts)
+            assert best == solver.merge(parts)
+            owner = dist.owner_of(best, parts)
+            assert parts[owner]["tie_key"] == best["tie_key"]
+            before = ranks[owner].launch_count()
+            fin = ranks[owner].area_diameter_finish(x, y, None, 4.0, d, best, True)
+            assert ranks[owner].launch_count() - before <= 2          # the back-walk only: no re-run of the winning pair
+            assert_same_solution(fin, whole, ("AD owner", d))
+            other = ranks[(owner + 1) % world].area_diameter_finish(x, y, None, 4.0, d, best, True)     # re-run path, same answer
+            assert_same_solution(other, whole, ("AD non-owner", d))
+    finally:
+        for r in ranks:
+            r.close()
+
+
 # ------------------------------------------------------------------------------------------------ batches (config 5)
 def test_batch_of_cell_samples_equals_the_reference_and_single_solves(golden, solver):
     """adk_solve_batch on real cell samples, the call of Area-Selector's quality_of_results_comparison.py:48-55 (A = 4, D = 4,
