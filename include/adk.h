@@ -97,7 +97,9 @@ int adk_solve_area(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
 int adk_solve_area_diameter(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
                             uint64_t kmax, double amax, double dmax, uint32_t flags, adk_result* out, uint32_t* hull);
 
-/* ---- sharded solves: shard `shard` of `nshards` takes every nshards-th unit of the cost-ordered work list ------- */
+/* ---- sharded solves: shard `shard` of `nshards` takes every nshards-th unit of the cost-ordered work list (anchors; candidate
+ *      pairs by cost class, then pair key: the same deal on every rank, nothing is exchanged to agree on it).  finish is cheapest
+ *      on the rank whose partial won the merge (its records are still resident); elsewhere it re-runs the winning unit. ------- */
 int adk_area_partial(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
                      uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* stats);
 int adk_area_finish(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
