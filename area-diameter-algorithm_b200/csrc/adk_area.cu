@@ -17,7 +17,10 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 namespace adk
 {
@@ -47,6 +50,7 @@ struct AnchorInfo
     uint64_t required;     // prefix-minimum change points beyond the first list element (Eppstein.cpp:228-232)
     unsigned long long lvl[3];   // best area (order-preserving bits) of the level in flight and its two neighbours
     int32_t best_row_any, pad_;
+    unsigned long long t0_ns, t1_ns;   // development: when the row pipeline started / finished this anchor (ADK_DEBUG)
 };
 
 // --------------------------------------------------------------------------------------------- PREP kernel
@@ -374,6 +378,211 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
     }
 }
 
+// --------------------------------------------------------------------------------------------- DP kernel, row sweep
+//
+// The same recurrence, swept the other way round.  A source l of row j lies to the left of anchor->j, i.e. it comes EARLIER
+// in the clockwise row order, so rows can be completed one after the other with ALL levels of a row handled together:
+// lanes hold 32 consecutive levels (a band); per source a warp reads one contiguous 256-byte level vector of the
+// predecessor entry (shifted by c), adds the triangle, folds it into the running minimum and writes one contiguous
+// 256-byte vector.  Traffic per cell = 8 B read + 8 B written (the algorithmic 16 B); the level wavefront above re-reads
+// the 16-byte source record at every level and pulls a 64-byte DRAM burst for every 8-byte gather (80 B per cell measured).
+// Table layout: T[compact source index][ring of Wb bands][32 levels].
+// One CTA per anchor, one row at a time: the warps take 32 sources each, request all their predecessor vectors at once
+// (one memory round trip per 32 x warps sources), form local prefix minima in registers, exchange the segment minima
+// through shared memory and write the final vectors.  Rows are strictly ordered inside the CTA, so no flags are needed;
+// bands are swept one after the other, and after each band the stop rule of the wavefront applies.
+constexpr int kRowThreads = 256;
+constexpr uint32_t kRowWarps = kRowThreads / 32;
+constexpr uint32_t kBand = 32;
+
+__device__ __forceinline__ uint32_t level_pos(uint32_t lvl, uint32_t Wb)      // lvl >= 3
+{
+    const uint32_t z = lvl - 3u;
+    return ((z >> 5) % Wb) * kBand + (z & 31u);
+}
+
+__global__ void __launch_bounds__(kRowThreads)
+k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
+            const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc,
+            const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, uint64_t K, double amax, uint32_t cap_rows)
+{
+    __shared__ __align__(16) SrcRec s_rec[kRowWarps][32];
+    __shared__ double s_tot[2][kRowWarps][32];
+    __shared__ unsigned long long s_best[kBand];
+    __shared__ long long s_req;
+    __shared__ unsigned int s_q;
+    __shared__ int s_row;
+    __shared__ uint32_t s_top, s_stop, s_levels;
+    __shared__ double s_best_area;
+    extern __shared__ uint32_t s_rowtab[];     // [cap_rows] source counts, [cap_rows] row bases (anchors with more rows read them from global memory)
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    SrcRec* st_rec = s_rec[warp];
+    for (;;)
+    {
+        __syncthreads();
+        if (threadIdx.x == 0) s_q = atomicAdd(queue, 1u);
+        __syncthreads();
+        const uint32_t q = s_q;
+        if (q >= count) break;
+        AnchorInfo& A = info[first + q];
+        const uint32_t rows = A.rows, U = A.U, W = A.W, acap = (uint32_t) A.a, cmax = A.cmax;
+        const uint32_t Wb = W / kBand;
+        const SrcRec* arec = recs + A.meta_off;
+        const uint32_t* ansrc = nsrc + A.row_off;
+        const uint32_t* abase = rowbase + A.row_off;
+        if (rows <= cap_rows)
+        {
+            for (uint32_t t = threadIdx.x; t < rows; t += blockDim.x) { s_rowtab[t] = ansrc[t]; s_rowtab[cap_rows + t] = abase[t]; }
+            ansrc = s_rowtab; abase = s_rowtab + cap_rows;
+        }
+        double* T = Tbuf + A.t_off;
+        if (threadIdx.x == 0)
+        {
+            s_top = 2; s_best_area = 0.0; s_req = 0; s_row = 0x7fffffff; s_stop = 0; s_levels = 0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t0_ns));
+        }
+        __syncthreads();
+        long long req = 0;
+        if (U > 0)
+        {
+            uint32_t par = 0;                   // which s_tot buffer the next chunk uses
+            for (uint32_t b = 0;; ++b)
+            {
+                const uint32_t lo = 3u + kBand * b;
+                const uint32_t m = lo + lane;
+                const bool active = (uint64_t) m <= K;
+                const uint32_t bm = b % Wb;
+                const uint32_t mypos = bm * kBand + lane;
+                double band_best = INFINITY;    // warp 0: best final value of level m over the rows
+                // the source records of a chunk are requested one chunk ahead (they depend on nothing)
+                uint32_t nj = 0, nk = 0;
+                while (nj < rows && ansrc[nj] == 0) ++nj;
+                SrcRec nxt = SrcRec{0.0, kNoPrev, 0, 0};
+                if (nj < rows && nk + warp * 32 + lane < ansrc[nj]) nxt = arec[(size_t) nj * acap + nk + warp * 32 + lane];
+                for (uint32_t jj = 0; jj < rows; ++jj)
+                {
+                    const uint32_t ns = ansrc[jj];
+                    if (ns == 0) continue;
+                    const uint32_t obase = abase[jj];
+                    double carry = INFINITY;
+                    for (uint32_t k0 = 0; k0 < ns; k0 += kRowThreads)
+                    {
+                        const uint32_t base = k0 + warp * 32;
+                        const uint32_t cnt = base < ns ? min(32u, ns - base) : 0u;
+                        __syncwarp();
+                        if (lane < cnt) st_rec[lane] = nxt;
+                        __syncwarp();
+                        nk += kRowThreads;
+                        if (nk >= ns) { nk = 0; ++nj; while (nj < rows && ansrc[nj] == 0) ++nj; }
+                        if (nj < rows && nk + warp * 32 + lane < ansrc[nj]) nxt = arec[(size_t) nj * acap + nk + warp * 32 + lane];
+                        // every predecessor vector of the segment is requested before any of them is used
+                        double pv[32];
+#pragma unroll
+                        for (uint32_t u = 0; u < 32; ++u)
+                        {
+                            pv[u] = INFINITY;
+                            if (u < cnt)
+                            {
+                                const SrcRec r = st_rec[u];
+                                const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
+                                if (r.gidx != kNoPrev && active && c + 3u <= m)
+                                {   // level m - c = 3 + 32 b + (lane - c): its band is b + floor((lane - c) / 32), at most Wb - 1 bands back
+                                    const int d = (int) lane - (int) c;
+                                    int slot = (int) bm + (d >> 5);
+                                    if (slot < 0) slot += (int) Wb;
+                                    pv[u] = __ldcg(&T[(size_t) r.gidx * W + (uint32_t) slot * kBand + ((uint32_t) d & 31u)]);
+                                }
+                            }
+                        }
+                        // local prefix minima (pv[u] becomes the running minimum of the segment up to u)
+                        double run = INFINITY;
+                        bool head_finite = false;
+#pragma unroll
+                        for (uint32_t u = 0; u < 32; ++u)
+                        {
+                            if (u < cnt)
+                            {
+                                const SrcRec r = st_rec[u];
+                                const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
+                                double val = INFINITY;
+                                if (active && c + 2u <= m)
+                                {   // Eppstein.cpp:210-216 with T[0], T[1] = +inf and T[2] = 0
+                                    const double prev = m - c == 2u ? 0.0 : pv[u];
+                                    const double cur = __dadd_rn(prev, r.area);
+                                    if (cur <= amax) val = cur;
+                                }
+                                if (u == 0 && base == 0) head_finite = (r.c3 & 0x8000u) && val < INFINITY;
+                                run = fmin(run, val);
+                                pv[u] = run;
+                            }
+                        }
+                        s_tot[par][warp][lane] = run;
+                        __syncthreads();
+                        double cin = carry, all = carry;
+#pragma unroll
+                        for (uint32_t w = 0; w < kRowWarps; ++w)
+                        {
+                            const double t = s_tot[par][w][lane];
+                            if (w < warp) cin = fmin(cin, t);
+                            all = fmin(all, t);
+                        }
+                        par ^= 1u;
+                        double before = cin;
+                        if (head_finite) --req;                                          // the list's first element is no change point
+#pragma unroll
+                        for (uint32_t u = 0; u < 32; ++u)
+                        {
+                            if (u < cnt)
+                            {
+                                const double g = fmin(cin, pv[u]);
+                                if (g < before) ++req;                                   // Eppstein.cpp:228-232
+                                before = g;
+                                if (active) __stcg(&T[(size_t) (obase + base + u) * W + mypos], g);   // Eppstein.cpp:234
+                            }
+                        }
+                        carry = all;
+                    }
+                    band_best = fmin(band_best, carry);
+                    __syncthreads();            // the row is complete before any warp reads it as a source of the next rows
+                }
+                if (warp == 0) s_best[lane] = area_bits(band_best);
+                __syncthreads();
+                if (threadIdx.x == 0)
+                {
+                    for (uint32_t l = 0; l < kBand; ++l)
+                        if (s_best[l] != kInfBits) { s_top = lo + l; s_best_area = bits_area(s_best[l]); }
+                    const uint64_t hi = K < (uint64_t) lo + kBand - 1 ? K : (uint64_t) lo + kBand - 1;
+                    s_levels = (uint32_t) (hi - 2);
+                    s_stop = (hi >= K || hi >= (uint64_t) s_top + cmax) ? 1u : 0u;      // no deeper level can be finite
+                }
+                __syncthreads();
+                if (s_stop) break;
+            }
+            const uint32_t top = s_top;
+            if (top > 2)
+            {   // first row (in j order) that attains the best area at the best level (Eppstein.cpp:219-224)
+                const double best_area = s_best_area;
+                const uint32_t tp = level_pos(top, Wb);
+                for (uint32_t jj = threadIdx.x; jj < rows; jj += blockDim.x)
+                {
+                    const uint32_t ns = ansrc[jj];
+                    if (ns && __ldcg(&T[(size_t) (abase[jj] + ns - 1) * W + tp]) == best_area) atomicMin(&s_row, (int) jj);
+                }
+            }
+        }
+        for (int o = 16; o; o >>= 1) req += __shfl_xor_sync(0xffffffffu, req, o);
+        if (lane == 0 && req) atomicAdd(reinterpret_cast<unsigned long long*>(&s_req), (unsigned long long) req);
+        __syncthreads();
+        if (threadIdx.x == 0)
+        {
+            A.levels_run = s_levels;
+            A.required = (uint64_t) s_req;
+            if (s_top > 2) { A.best_m = s_top; A.best_area = s_best_area; A.best_row = s_row; }
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t1_ns));
+        }
+    }
+}
+
 struct AreaBest { int32_t found; uint32_t m; double area; uint32_t order; int32_t row; int32_t pt; int32_t jpt;
                   uint64_t cells_nominal, cells_executed, required; };
 
@@ -638,6 +847,10 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     ADK_CUDA(c, cudaStreamSynchronize(c->stream));
 
     // table plan: ring of (cmax + 1) levels, or every level up to full_m
+    // Ring mode runs the row pipeline (k_area_rows, bands of 32 levels); keeping every level for the walk back (one anchor)
+    // stays on the level wavefront.  ADK_AREA_WAVEFRONT=1 forces the wavefront everywhere (A/B measurements).
+    static const bool force_wavefront = [] { const char* e = std::getenv("ADK_AREA_WAVEFRONT"); return e && e[0] == '1'; }();
+    const bool by_rows = full_m == 0 && !force_wavefront;
     const uint64_t budget_entries = std::max<uint64_t>(workspace_budget(c, c->scratch5) / sizeof(double), 1u << 20);
     uint32_t b0 = 0;
     while (b0 < cnt)
@@ -650,6 +863,12 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             const uint64_t levels = K >= 3 ? K - 2 : 0;
             uint64_t W = full_m ? (uint64_t) full_m + 1 : std::min<uint64_t>((uint64_t) A.cmax + 1, std::max<uint64_t>(levels, 1));
             if (W < 1) W = 1;
+            if (by_rows)
+            {   // bands: enough to reach back cmax levels, never more than the levels an anchor with this many rows can fill
+                const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
+                const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
+                W = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + 1, nb_max) * kBand;
+            }
             const uint64_t need = W * (uint64_t) A.U;
             if (b1 > b0 && total + need > budget_entries) break;
             if (need > budget_entries) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
@@ -667,6 +886,15 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
         while (cs < 8 && max_rows >= 128u * cs) cs *= 2;
         const uint32_t nclusters = std::max<uint32_t>(1, std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 2 / cs));
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
+        if (by_rows)
+        {
+            const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 3));
+            SmallOut* so_ = c->small.as<SmallOut>();
+            const uint32_t cap_rows = std::min<uint32_t>(max_rows, 4096);
+            k_area_rows<<<grid, kRowThreads, sizeof(uint32_t) * 2 * cap_rows, c->stream>>>(d_info, b0, b1 - b0, &so_->queue, d_recs, d_nsrc, d_rowbase,
+                                                                                           c->scratch5.as<double>(), K, amax, cap_rows);
+        }
+        else
         {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(nclusters * cs); cfg.blockDim = dim3(kDpThreads); cfg.dynamicSmemBytes = 0; cfg.stream = c->stream;
@@ -687,6 +915,25 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             float ms = 0.f;
             ADK_CUDA(c, cudaEventElapsedTime(&ms, c->ev2, c->ev3));
             if (dp_ms) *dp_ms += ms;
+        }
+        static const bool debug = std::getenv("ADK_DEBUG") != nullptr;
+        if (debug && by_rows)
+        {
+            std::vector<AnchorInfo> h(b1 - b0);
+            ADK_CUDA(c, cudaMemcpyAsync(h.data(), d_info + b0, sizeof(AnchorInfo) * (b1 - b0), cudaMemcpyDeviceToHost, c->stream));
+            ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+            unsigned long long tmin = ~0ull, tmax = 0; double sum = 0.0;
+            for (auto& a : h) { tmin = std::min(tmin, a.t0_ns); tmax = std::max(tmax, a.t1_ns); sum += (double) (a.t1_ns - a.t0_ns); }
+            std::fprintf(stderr, "[adk] rows kernel: %u anchors, span %.2f ms, sum of anchor times %.2f ms\n", b1 - b0, (tmax - tmin) * 1e-6, sum * 1e-6);
+            std::vector<uint32_t> idx(h.size());
+            for (uint32_t t = 0; t < idx.size(); ++t) idx[t] = t;
+            std::sort(idx.begin(), idx.end(), [&](uint32_t p, uint32_t q) { return h[p].t1_ns - h[p].t0_ns > h[q].t1_ns - h[q].t0_ns; });
+            for (uint32_t t = 0; t < std::min<size_t>(6, idx.size()); ++t)
+            {
+                const AnchorInfo& a = h[idx[t]];
+                std::fprintf(stderr, "[adk]   anchor %u: rows %u U %u cmax %u W %u levels %u  start %.2f ms  took %.2f ms\n", idx[t], a.rows, a.U, a.cmax, a.W,
+                             a.levels_run, (a.t0_ns - tmin) * 1e-6, (a.t1_ns - a.t0_ns) * 1e-6);
+            }
         }
         b0 = b1;
     }
