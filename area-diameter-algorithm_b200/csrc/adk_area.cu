@@ -401,6 +401,18 @@ __device__ __forceinline__ uint32_t level_pos(uint32_t lvl, uint32_t Wb)      //
     return ((z >> 5) % Wb) * kBand + (z & 31u);
 }
 
+// Segment of round `rd` of a row with ns sources that warp `warp` handles: the row is cut into ceil(ns / kRowThreads) rounds
+// of equal size, a round into kRowWarps equal segments of at most 32 sources.
+__device__ __forceinline__ void row_segment(uint32_t ns, uint32_t rd, uint32_t warp, uint32_t& base, uint32_t& cnt)
+{
+    const uint32_t rounds = (ns + kRowThreads - 1) / kRowThreads;
+    const uint32_t per_round = rounds == 1 ? ns : (ns + rounds - 1) / rounds;
+    const uint32_t seg = (per_round + kRowWarps - 1) / kRowWarps;
+    const uint32_t end = min(ns, (rd + 1) * per_round);
+    base = rd * per_round + warp * seg;
+    cnt = base < end ? min(seg, end - base) : 0u;
+}
+
 __global__ void __launch_bounds__(kRowThreads)
 k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
             const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc,
@@ -454,67 +466,72 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                 const uint32_t bm = b % Wb;
                 const uint32_t mypos = bm * kBand + lane;
                 double band_best = INFINITY;    // warp 0: best final value of level m over the rows
-                // the source records of a chunk are requested one chunk ahead (they depend on nothing)
-                uint32_t nj = 0, nk = 0;
+                // A row's sources are cut into rounds of at most kRowThreads, and a round evenly into one segment per warp.
+                // The source records of a round are requested one round ahead (they depend on nothing).
+                uint32_t nj = 0, nr = 0;
                 while (nj < rows && ansrc[nj] == 0) ++nj;
                 SrcRec nxt = SrcRec{0.0, kNoPrev, 0, 0};
-                if (nj < rows && nk + warp * 32 + lane < ansrc[nj]) nxt = arec[(size_t) nj * acap + nk + warp * 32 + lane];
+                {
+                    uint32_t nb = 0, nc = 0;
+                    if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
+                    if (lane < nc) nxt = arec[(size_t) nj * acap + nb + lane];
+                }
                 for (uint32_t jj = 0; jj < rows; ++jj)
                 {
                     const uint32_t ns = ansrc[jj];
                     if (ns == 0) continue;
                     const uint32_t obase = abase[jj];
+                    const uint32_t rounds = (ns + kRowThreads - 1) / kRowThreads;
                     double carry = INFINITY;
-                    for (uint32_t k0 = 0; k0 < ns; k0 += kRowThreads)
+                    for (uint32_t rd = 0; rd < rounds; ++rd)
                     {
-                        const uint32_t base = k0 + warp * 32;
-                        const uint32_t cnt = base < ns ? min(32u, ns - base) : 0u;
+                        uint32_t base, cnt;
+                        row_segment(ns, rd, warp, base, cnt);
                         __syncwarp();
                         if (lane < cnt) st_rec[lane] = nxt;
                         __syncwarp();
-                        nk += kRowThreads;
-                        if (nk >= ns) { nk = 0; ++nj; while (nj < rows && ansrc[nj] == 0) ++nj; }
-                        if (nj < rows && nk + warp * 32 + lane < ansrc[nj]) nxt = arec[(size_t) nj * acap + nk + warp * 32 + lane];
+                        if (++nr >= rounds) { nr = 0; ++nj; while (nj < rows && ansrc[nj] == 0) ++nj; }
+                        {
+                            uint32_t nb = 0, nc = 0;
+                            if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
+                            if (lane < nc) nxt = arec[(size_t) nj * acap + nb + lane];
+                        }
                         // every predecessor vector of the segment is requested before any of them is used
                         double pv[32];
-#pragma unroll
-                        for (uint32_t u = 0; u < 32; ++u)
-                        {
-                            pv[u] = INFINITY;
-                            if (u < cnt)
-                            {
-                                const SrcRec r = st_rec[u];
-                                const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
-                                if (r.gidx != kNoPrev && active && c + 3u <= m)
-                                {   // level m - c = 3 + 32 b + (lane - c): its band is b + floor((lane - c) / 32), at most Wb - 1 bands back
-                                    const int d = (int) lane - (int) c;
-                                    int slot = (int) bm + (d >> 5);
-                                    if (slot < 0) slot += (int) Wb;
-                                    pv[u] = __ldcg(&T[(size_t) r.gidx * W + (uint32_t) slot * kBand + ((uint32_t) d & 31u)]);
-                                }
-                            }
-                        }
-                        // local prefix minima (pv[u] becomes the running minimum of the segment up to u)
                         double run = INFINITY;
                         bool head_finite = false;
 #pragma unroll
                         for (uint32_t u = 0; u < 32; ++u)
                         {
-                            if (u < cnt)
-                            {
-                                const SrcRec r = st_rec[u];
-                                const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
-                                double val = INFINITY;
-                                if (active && c + 2u <= m)
-                                {   // Eppstein.cpp:210-216 with T[0], T[1] = +inf and T[2] = 0
-                                    const double prev = m - c == 2u ? 0.0 : pv[u];
-                                    const double cur = __dadd_rn(prev, r.area);
-                                    if (cur <= amax) val = cur;
-                                }
-                                if (u == 0 && base == 0) head_finite = (r.c3 & 0x8000u) && val < INFINITY;
-                                run = fmin(run, val);
-                                pv[u] = run;
+                            if (u >= cnt) break;
+                            pv[u] = INFINITY;
+                            const SrcRec r = st_rec[u];
+                            const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
+                            if (r.gidx != kNoPrev && active && c + 3u <= m)
+                            {   // level m - c = 3 + 32 b + (lane - c): its band is b + floor((lane - c) / 32), at most Wb - 1 bands back
+                                const int d = (int) lane - (int) c;
+                                int slot = (int) bm + (d >> 5);
+                                if (slot < 0) slot += (int) Wb;
+                                pv[u] = __ldcg(&T[(size_t) r.gidx * W + (uint32_t) slot * kBand + ((uint32_t) d & 31u)]);
                             }
+                        }
+                        // local prefix minima (pv[u] becomes the running minimum of the segment up to u)
+#pragma unroll
+                        for (uint32_t u = 0; u < 32; ++u)
+                        {
+                            if (u >= cnt) break;
+                            const SrcRec r = st_rec[u];
+                            const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
+                            double val = INFINITY;
+                            if (active && c + 2u <= m)
+                            {   // Eppstein.cpp:210-216 with T[0], T[1] = +inf and T[2] = 0
+                                const double prev = m - c == 2u ? 0.0 : pv[u];
+                                const double cur = __dadd_rn(prev, r.area);
+                                if (cur <= amax) val = cur;
+                            }
+                            if (u == 0 && base == 0) head_finite = (r.c3 & 0x8000u) && val < INFINITY;
+                            run = val < run ? val : run;
+                            pv[u] = run;
                         }
                         s_tot[par][warp][lane] = run;
                         __syncthreads();
@@ -523,22 +540,21 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         for (uint32_t w = 0; w < kRowWarps; ++w)
                         {
                             const double t = s_tot[par][w][lane];
-                            if (w < warp) cin = fmin(cin, t);
-                            all = fmin(all, t);
+                            if (w < warp) cin = t < cin ? t : cin;
+                            all = t < all ? t : all;
                         }
                         par ^= 1u;
                         double before = cin;
                         if (head_finite) --req;                                          // the list's first element is no change point
+                        double* outp = T + (size_t) (obase + base) * W + mypos;
 #pragma unroll
                         for (uint32_t u = 0; u < 32; ++u)
                         {
-                            if (u < cnt)
-                            {
-                                const double g = fmin(cin, pv[u]);
-                                if (g < before) ++req;                                   // Eppstein.cpp:228-232
-                                before = g;
-                                if (active) __stcg(&T[(size_t) (obase + base + u) * W + mypos], g);   // Eppstein.cpp:234
-                            }
+                            if (u >= cnt) break;
+                            const double g = pv[u] < cin ? pv[u] : cin;
+                            req += g < before ? 1 : 0;                                   // Eppstein.cpp:228-232
+                            before = g;
+                            if (active) __stcg(outp + (size_t) u * W, g);                // Eppstein.cpp:234
                         }
                         carry = all;
                     }
