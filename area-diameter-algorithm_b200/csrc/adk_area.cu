@@ -892,6 +892,18 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             total += need;
             ++b1;
         }
+        if (by_rows && b1 < cnt)
+        {   // the anchors do not fit in one launch: do not leave a short second wave of heavy anchors behind the resident CTAs
+            int per_sm = 0;
+            ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_area_rows, kRowThreads, sizeof(uint32_t) * 2 * 4096));
+            const uint32_t resident = (uint32_t) std::max(per_sm, 1) * (uint32_t) c->sm_count;
+            if (b1 - b0 > resident && b1 - b0 < 2 * resident)
+            {
+                b1 = b0 + resident;
+                total = 0;
+                for (uint32_t t = b0; t < b1; ++t) total += (uint64_t) P.info[t].W * P.info[t].U;
+            }
+        }
         ADK_TRY(ensure(c, c->scratch5, sizeof(double) * std::max<uint64_t>(total, 1)));
         ADK_CUDA(c, cudaMemcpyAsync(d_info + b0, P.info.data() + b0, sizeof(AnchorInfo) * (b1 - b0), cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(c->small.p, 0, sizeof(unsigned int) * 2, c->stream));

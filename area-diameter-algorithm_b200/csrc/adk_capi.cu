@@ -117,7 +117,7 @@ int adk_create(adk_ctx** out_ctx, int device)
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return ADK_ERR_CUDA; }
     cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1); cudaEventCreate(&c->ev2); cudaEventCreate(&c->ev3);
     size_t free_b = 0, total_b = 0;
-    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->budget = (uint64_t) (free_b * 0.6);
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->budget = (uint64_t) (free_b * 0.75);
     else c->budget = 8ull << 30;
     *out_ctx = h;
     return ADK_OK;

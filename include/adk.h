@@ -86,7 +86,7 @@ typedef struct adk_stats
 int adk_create(adk_ctx** out_ctx, int device);        /* device = CUDA ordinal; -1 = current device */
 void adk_destroy(adk_ctx* ctx);
 const char* adk_last_error(const adk_ctx* ctx);       /* text of the last failure on this context */
-int adk_set_memory_budget(adk_ctx* ctx, uint64_t bytes);   /* cap for DP workspaces (default: 60 % of free memory) */
+int adk_set_memory_budget(adk_ctx* ctx, uint64_t bytes);   /* cap for DP workspaces (default: 75 % of free memory) */
 int adk_set_stream(adk_ctx* ctx, void* cuda_stream);       /* run on the caller's cudaStream_t (NULL = legacy default stream) */
 uint64_t adk_launch_count(const adk_ctx* ctx);             /* kernels launched by this context since adk_create */
 
