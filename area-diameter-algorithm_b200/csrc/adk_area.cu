@@ -391,7 +391,10 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
 // (one memory round trip per 32 x warps sources), form local prefix minima in registers, exchange the segment minima
 // through shared memory and write the final vectors.  Rows are strictly ordered inside the CTA, so no flags are needed;
 // bands are swept one after the other, and after each band the stop rule of the wavefront applies.
-constexpr int kRowThreads = 256;
+#ifndef ADK_ROW_THREADS
+#define ADK_ROW_THREADS 256
+#endif
+constexpr int kRowThreads = ADK_ROW_THREADS;
 constexpr uint32_t kRowWarps = kRowThreads / 32;
 constexpr uint32_t kBand = 32;
 
@@ -413,10 +416,11 @@ __device__ __forceinline__ void row_segment(uint32_t ns, uint32_t rd, uint32_t w
     cnt = base < end ? min(seg, end - base) : 0u;
 }
 
-__global__ void __launch_bounds__(kRowThreads)
+__global__ void __launch_bounds__(kRowThreads, kRowThreads >= 512 ? 1 : 2)
 k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
             const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc,
-            const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, uint64_t K, double amax, uint32_t cap_rows)
+            const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, uint64_t slot_entries, uint64_t K, double amax,
+            uint32_t cap_rows)
 {
     __shared__ __align__(16) SrcRec s_rec[kRowWarps][32];
     __shared__ double s_tot[2][kRowWarps][32];
@@ -447,7 +451,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
             for (uint32_t t = threadIdx.x; t < rows; t += blockDim.x) { s_rowtab[t] = ansrc[t]; s_rowtab[cap_rows + t] = abase[t]; }
             ansrc = s_rowtab; abase = s_rowtab + cap_rows;
         }
-        double* T = Tbuf + A.t_off;
+        double* T = Tbuf + (size_t) blockIdx.x * slot_entries;      // the CTA's own table slot, reused for every anchor it takes
         if (threadIdx.x == 0)
         {
             s_top = 2; s_best_area = 0.0; s_req = 0; s_row = 0x7fffffff; s_stop = 0; s_levels = 0;
@@ -868,6 +872,59 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     static const bool force_wavefront = [] { const char* e = std::getenv("ADK_AREA_WAVEFRONT"); return e && e[0] == '1'; }();
     const bool by_rows = full_m == 0 && !force_wavefront;
     const uint64_t budget_entries = std::max<uint64_t>(workspace_budget(c, c->scratch5) / sizeof(double), 1u << 20);
+    if (by_rows)
+    {
+        // One launch for all anchors: every resident CTA owns one table slot sized for the largest anchor and reuses it for the
+        // anchors it pulls from the queue, so the table memory is (resident CTAs) x (largest ring), whatever the number of anchors.
+        uint64_t slot_entries = 1;
+        uint32_t max_rows = 1;
+        for (uint32_t t = 0; t < cnt; ++t)
+        {
+            AnchorInfo& A = P.info[t];
+            // bands: enough to reach back cmax levels, never more than the levels an anchor with this many rows can fill
+            const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
+            const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
+            const uint64_t W = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + 1, nb_max) * kBand;
+            A.W = (uint32_t) W; A.t_off = 0;
+            slot_entries = std::max<uint64_t>(slot_entries, W * (uint64_t) A.U);
+            max_rows = std::max<uint32_t>(max_rows, (uint32_t) A.a);
+        }
+        slot_entries = (slot_entries + 31) & ~(uint64_t) 31;
+        const uint32_t cap_rows = std::min<uint32_t>(max_rows, 4096);
+        const size_t smem = sizeof(uint32_t) * 2 * cap_rows;
+        int per_sm = 0;
+        ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_area_rows, kRowThreads, smem));
+        const uint64_t resident = (uint64_t) std::max(per_sm, 1) * (uint64_t) c->sm_count;
+        const uint64_t slots = std::min<uint64_t>(std::min<uint64_t>(cnt, resident), budget_entries / slot_entries);
+        if (slots == 0) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
+        ADK_TRY(ensure(c, c->scratch5, sizeof(double) * slots * slot_entries));
+        ADK_CUDA(c, cudaMemcpyAsync(d_info, P.info.data(), sizeof(AnchorInfo) * cnt, cudaMemcpyHostToDevice, c->stream));
+        ADK_CUDA(c, cudaMemsetAsync(c->small.p, 0, sizeof(unsigned int) * 2, c->stream));
+        ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
+        SmallOut* so_ = c->small.as<SmallOut>();
+        k_area_rows<<<(uint32_t) slots, kRowThreads, smem, c->stream>>>(d_info, 0, cnt, &so_->queue, d_recs, d_nsrc, d_rowbase,
+                                                                       c->scratch5.as<double>(), slot_entries, K, amax, cap_rows);
+        ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
+        ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
+        if (dp_ms)
+        {
+            ADK_CUDA(c, cudaEventSynchronize(c->ev3));
+            ADK_CUDA(c, cudaEventElapsedTime(dp_ms, c->ev2, c->ev3));
+        }
+        static const bool debug = std::getenv("ADK_DEBUG") != nullptr;
+        if (debug)
+        {
+            std::vector<AnchorInfo> h(cnt);
+            ADK_CUDA(c, cudaMemcpyAsync(h.data(), d_info, sizeof(AnchorInfo) * cnt, cudaMemcpyDeviceToHost, c->stream));
+            ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+            unsigned long long tmin = ~0ull, tmax = 0; double sum = 0.0, longest = 0.0;
+            for (auto& a : h) { tmin = std::min(tmin, a.t0_ns); tmax = std::max(tmax, a.t1_ns); sum += (double) (a.t1_ns - a.t0_ns); longest = std::max(longest, (double) (a.t1_ns - a.t0_ns)); }
+            std::fprintf(stderr, "[adk] rows kernel: %u anchors on %llu CTAs, span %.2f ms, sum of anchor times %.2f ms, longest anchor %.2f ms\n",
+                         cnt, (unsigned long long) slots, (tmax - tmin) * 1e-6, sum * 1e-6, longest * 1e-6);
+        }
+        return ADK_OK;
+    }
     uint32_t b0 = 0;
     while (b0 < cnt)
     {
@@ -879,30 +936,12 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             const uint64_t levels = K >= 3 ? K - 2 : 0;
             uint64_t W = full_m ? (uint64_t) full_m + 1 : std::min<uint64_t>((uint64_t) A.cmax + 1, std::max<uint64_t>(levels, 1));
             if (W < 1) W = 1;
-            if (by_rows)
-            {   // bands: enough to reach back cmax levels, never more than the levels an anchor with this many rows can fill
-                const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
-                const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
-                W = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + 1, nb_max) * kBand;
-            }
             const uint64_t need = W * (uint64_t) A.U;
             if (b1 > b0 && total + need > budget_entries) break;
             if (need > budget_entries) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
             A.W = (uint32_t) W; A.t_off = total;
             total += need;
             ++b1;
-        }
-        if (by_rows && b1 < cnt)
-        {   // the anchors do not fit in one launch: do not leave a short second wave of heavy anchors behind the resident CTAs
-            int per_sm = 0;
-            ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_area_rows, kRowThreads, sizeof(uint32_t) * 2 * 4096));
-            const uint32_t resident = (uint32_t) std::max(per_sm, 1) * (uint32_t) c->sm_count;
-            if (b1 - b0 > resident && b1 - b0 < 2 * resident)
-            {
-                b1 = b0 + resident;
-                total = 0;
-                for (uint32_t t = b0; t < b1; ++t) total += (uint64_t) P.info[t].W * P.info[t].U;
-            }
         }
         ADK_TRY(ensure(c, c->scratch5, sizeof(double) * std::max<uint64_t>(total, 1)));
         ADK_CUDA(c, cudaMemcpyAsync(d_info + b0, P.info.data() + b0, sizeof(AnchorInfo) * (b1 - b0), cudaMemcpyHostToDevice, c->stream));
@@ -914,15 +953,6 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
         while (cs < 8 && max_rows >= 128u * cs) cs *= 2;
         const uint32_t nclusters = std::max<uint32_t>(1, std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 2 / cs));
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
-        if (by_rows)
-        {
-            const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(b1 - b0, (uint32_t) c->sm_count * 3));
-            SmallOut* so_ = c->small.as<SmallOut>();
-            const uint32_t cap_rows = std::min<uint32_t>(max_rows, 4096);
-            k_area_rows<<<grid, kRowThreads, sizeof(uint32_t) * 2 * cap_rows, c->stream>>>(d_info, b0, b1 - b0, &so_->queue, d_recs, d_nsrc, d_rowbase,
-                                                                                           c->scratch5.as<double>(), K, amax, cap_rows);
-        }
-        else
         {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(nclusters * cs); cfg.blockDim = dim3(kDpThreads); cfg.dynamicSmemBytes = 0; cfg.stream = c->stream;
@@ -943,25 +973,6 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             float ms = 0.f;
             ADK_CUDA(c, cudaEventElapsedTime(&ms, c->ev2, c->ev3));
             if (dp_ms) *dp_ms += ms;
-        }
-        static const bool debug = std::getenv("ADK_DEBUG") != nullptr;
-        if (debug && by_rows)
-        {
-            std::vector<AnchorInfo> h(b1 - b0);
-            ADK_CUDA(c, cudaMemcpyAsync(h.data(), d_info + b0, sizeof(AnchorInfo) * (b1 - b0), cudaMemcpyDeviceToHost, c->stream));
-            ADK_CUDA(c, cudaStreamSynchronize(c->stream));
-            unsigned long long tmin = ~0ull, tmax = 0; double sum = 0.0;
-            for (auto& a : h) { tmin = std::min(tmin, a.t0_ns); tmax = std::max(tmax, a.t1_ns); sum += (double) (a.t1_ns - a.t0_ns); }
-            std::fprintf(stderr, "[adk] rows kernel: %u anchors, span %.2f ms, sum of anchor times %.2f ms\n", b1 - b0, (tmax - tmin) * 1e-6, sum * 1e-6);
-            std::vector<uint32_t> idx(h.size());
-            for (uint32_t t = 0; t < idx.size(); ++t) idx[t] = t;
-            std::sort(idx.begin(), idx.end(), [&](uint32_t p, uint32_t q) { return h[p].t1_ns - h[p].t0_ns > h[q].t1_ns - h[q].t0_ns; });
-            for (uint32_t t = 0; t < std::min<size_t>(6, idx.size()); ++t)
-            {
-                const AnchorInfo& a = h[idx[t]];
-                std::fprintf(stderr, "[adk]   anchor %u: rows %u U %u cmax %u W %u levels %u  start %.2f ms  took %.2f ms\n", idx[t], a.rows, a.U, a.cmax, a.W,
-                             a.levels_run, (a.t0_ns - tmin) * 1e-6, (a.t1_ns - a.t0_ns) * 1e-6);
-            }
         }
         b0 = b1;
     }
