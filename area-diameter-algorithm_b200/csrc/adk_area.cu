@@ -442,7 +442,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
         if (q >= count) break;
         AnchorInfo& A = info[first + q];
         const uint32_t rows = A.rows, U = A.U, W = A.W, acap = (uint32_t) A.a, cmax = A.cmax;
-        const uint32_t Wb = W / kBand;
+        const uint32_t Wb = W / kBand, W8 = W * 8u;     // W8: bytes per table row
         const SrcRec* arec = recs + A.meta_off;
         const uint32_t* ansrc = nsrc + A.row_off;
         const uint32_t* abase = rowbase + A.row_off;
@@ -516,7 +516,10 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                                 const int d = (int) lane - (int) c;
                                 int slot = (int) bm + (d >> 5);
                                 if (slot < 0) slot += (int) Wb;
-                                pv[u] = __ldcg(&T[(size_t) r.gidx * W + (uint32_t) slot * kBand + ((uint32_t) d & 31u)]);
+                                // row address and offset inside the row as two 32 x 32 + 64 bit multiply-adds
+                                const char* rowp = reinterpret_cast<const char*>(T) + (uint64_t) r.gidx * W8;
+                                const uint32_t off = (uint32_t) slot * kBand + ((uint32_t) d & 31u);
+                                pv[u] = __ldcg(reinterpret_cast<const double*>(rowp + (uint64_t) off * 8u));
                             }
                         }
                         // local prefix minima (pv[u] becomes the running minimum of the segment up to u)
@@ -550,16 +553,19 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         par ^= 1u;
                         double before = cin;
                         if (head_finite) --req;                                          // the list's first element is no change point
-                        double* outp = T + (size_t) (obase + base) * W + mypos;
+                        char* outp = reinterpret_cast<char*>(T + mypos) + (uint64_t) (obase + base) * W8;
+                        uint32_t changes = 0;
 #pragma unroll
                         for (uint32_t u = 0; u < 32; ++u)
                         {
                             if (u >= cnt) break;
                             const double g = pv[u] < cin ? pv[u] : cin;
-                            req += g < before ? 1 : 0;                                   // Eppstein.cpp:228-232
+                            changes += g < before ? 1u : 0u;                             // Eppstein.cpp:228-232
                             before = g;
-                            if (active) __stcg(outp + (size_t) u * W, g);                // Eppstein.cpp:234
+                            if (active) __stcg(reinterpret_cast<double*>(outp), g);      // Eppstein.cpp:234
+                            outp += W8;
                         }
+                        req += changes;
                         carry = all;
                     }
                     band_best = fmin(band_best, carry);
