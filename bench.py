@@ -391,7 +391,7 @@ def run_aux_workload(args):
         h_x = torch.tensor(x, dtype=torch.float64).pin_memory(); h_y = torch.tensor(y, dtype=torch.float64).pin_memory()
         nominal = (n - 2) * n * (n - 1) * (n - 2) // 3
         desc = f"area-bounded DP (Eppstein), synthetic Gaussian n={n} sigma=2.0 seed=1000 in [0,20]^2, A={amax}, K=inf, reconstruct (BASELINE config 3)"
-        kernel, bytes_per_cell = "k_area_dp", 16
+        kernel, bytes_per_cell = "k_area_rows", 16
 
         def step(resident):
             flush.zero_()
