@@ -55,7 +55,7 @@ struct AnchorInfo
 
 // --------------------------------------------------------------------------------------------- PREP kernel
 
-constexpr int kPrepThreads = 256;
+constexpr int kPrepThreads = 1024;   // one CTA per SM (64 registers): the heaviest anchor and the winner's single-anchor re-run are one CTA's critical path
 
 __global__ void __launch_bounds__(kPrepThreads)
 k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
@@ -73,8 +73,12 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
     const uint32_t len = n - 1;
     uint16_t* Q = qscratch + (size_t) blockIdx.x * qstride;
 
-    for (uint32_t idx = first + blockIdx.x; idx < first + count; idx += gridDim.x)
+    // anchors arrive heaviest first: deal them to the CTAs in snake order so that every CTA gets the same mix
+    for (uint32_t round = 0; round * gridDim.x < count; ++round)
     {
+        const uint32_t off = round * gridDim.x + ((round & 1u) ? gridDim.x - 1u - blockIdx.x : blockIdx.x);
+        if (off >= count) continue;                  // uniform per CTA: no barrier is skipped by part of a block
+        const uint32_t idx = first + off;
         AnchorInfo& A = info[idx];
         const int i = A.pt;
         const uint32_t acap = (uint32_t) A.a;
@@ -848,7 +852,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     ADK_TRY(ensure(c, c->scratch1, sizeof(SrcRec) * std::max<uint64_t>(P.meta_total, 1)));
     ADK_TRY(ensure(c, c->scratch2, sizeof(uint16_t) * std::max<uint64_t>(P.meta_total, 1)));
     ADK_TRY(ensure(c, c->scratch3, sizeof(int32_t) * 3 * std::max<uint64_t>(P.row_total, 1)));
-    const uint32_t prep_grid = std::min<uint32_t>(cnt, (uint32_t) c->sm_count * 4);
+    const uint32_t prep_grid = std::min<uint32_t>(cnt, (uint32_t) c->sm_count);   // 1024-thread CTAs, one per SM
     const uint32_t qstride = P.amax_rows * P.amax_rows;
     ADK_TRY(ensure(c, c->scratch4, sizeof(uint16_t) * std::max<uint64_t>((uint64_t) qstride * prep_grid, 1)));
     ADK_TRY(ensure(c, c->small, sizeof(SmallOut)));

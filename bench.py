@@ -392,6 +392,10 @@ def run_aux_workload(args):
         nominal = (n - 2) * n * (n - 1) * (n - 2) // 3
         desc = f"area-bounded DP (Eppstein), synthetic Gaussian n={n} sigma=2.0 seed=1000 in [0,20]^2, A={amax}, K=inf, reconstruct (BASELINE config 3)"
         kernel, bytes_per_cell = "k_area_rows", 16
+        try:
+            area_traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("k_area_rows_dram_bytes_per_launch")
+        except Exception:
+            area_traffic = None
 
         def step(resident):
             flush.zero_()
@@ -413,6 +417,7 @@ def run_aux_workload(args):
         desc = (f"area+diameter-bounded DP on the ten cell samples (n={[len(s_) for s_ in sets]}), A={amax}, D={dmax}, K=inf, reconstruct, "
                 "one adk_solve_batch call (BASELINE config 5)")
         kernel, bytes_per_cell, nominal = "k_ad_cells", BYTES_PER_CELL, None
+        area_traffic = None
 
         def step(resident):
             flush.zero_()
@@ -475,7 +480,9 @@ def run_aux_workload(args):
                         "timer": "host wall clock around the C-ABI calls, max over ranks"},
                 "gpu_launches": res["launches"],
                 "roofline": {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "peak_source": peak_src, "share_of_step": res["my_dp_ms"] / res["dev_ms"]},
+                             "traffic": area_traffic if world == 1 else None, "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": res["my_cells"] * bytes_per_cell / args.steps,
+                             "avg_launch_ms": res["my_dp_ms"] / args.steps, "share_of_step": res["my_dp_ms"] / res["dev_ms"]},
                 "clocks": clocks}
         last = res["last"]
         if nominal:
