@@ -303,6 +303,22 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 // [cell (a,i)] and LEFT(b; a->i), i > a [cell (i,b)]: destination d of cell (a,b) is
 //   d <  nr-1-b : RIGHT(a; b -> b+1+d)          d >= nr-1-b : LEFT(b; a -> a+1+(d-(nr-1-b)))
 // and the whole layer vector of a destination is produced inside this one cell.
+//
+// The suffix sweep (round 2).  The sources of a cell fall into two groups, the RIGHT edges R[s]->R[b] and the LEFT edges
+// L[s]->L[a].  Sort each group by the direction of its edge around the head (a pseudo-angle in the frame of the candidate
+// segment, sources in the half plane in front of the head).  Every transition test of the reference is a half-plane test on
+// that direction: "stay" is Orientation(q, head, p_s) >= 0 (:201, :274) and "switch" compares the pseudo-distances of q and of
+// the other head from the line p_s -> head (:226, :299), so for ONE destination the sources that pass form a SUFFIX of the
+// sorted group (measured: every one of 8.5e7 (destination, group) sets on the bench instance; tools/ad_interval_stats.c).
+// The minimum over the passing sources is then a suffix minimum: per cell ONE backward sweep over each group with the
+// running minimum in registers (lanes = layers) serves every destination, instead of one relaxation per passing pair:
+//   dest(d)[k] = min( SufR[loR(d)][k], SufL[loL(d)][k] ),   Suf_g[r][k] = min over sorted positions p >= r of S_p[k],
+//   S_p[k] = area_p[k - c_p] + triangle_p (<= A).
+// The tests themselves are still the reference's, evaluated pair by pair in FP64 — a destination whose passing set is NOT
+// a suffix (possible only for eps-degenerate inputs) is relaxed pair by pair ("explicit" path), so the result never
+// depends on the sort.  Two more consequences: the "stay" tests depend on (s, b, i) only, not on the other head, so their
+// suffix starts are tabulated once per candidate; and destinations with equal (loR, loL) have equal layer vectors, which
+// are stored once and shared (3.6x fewer records on the bench instance).
 
 #ifndef ADK_CELL_WARPS
 #define ADK_CELL_WARPS 4
@@ -310,19 +326,24 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 constexpr int kCellWarps = ADK_CELL_WARPS;       // warps per CTA (one candidate per CTA) when candidates are plentiful
 constexpr int kMaxCellWarps = 16;                // ... and when few, heavy candidates set the critical path (chosen per launch)
 constexpr int kCellThreads = kCellWarps * 32;
-#ifndef ADK_KBT
-#define ADK_KBT 32
-#endif
-constexpr int kBT = ADK_KBT;                     // layers per accumulator tile
-constexpr int kRS = kBT + 1;                     // accumulator row stride: acc[destination][layer], padded against bank conflicts
-constexpr int kSrcCap = 64;                      // source edges of a cell kept in shared memory (larger cells use the global spill)
+constexpr int kBT = 32;                          // layers per tile = lanes
+constexpr int kGrp = 32;                         // sources per group in shared memory = rows of the suffix table
+constexpr int kDstCap = 128;                     // destinations per pass with their state in shared memory
+constexpr uint32_t kFB = 0xffffu;                // suffix start "none": the destination takes the explicit path for that group
+constexpr uint32_t kNil = 0xffffu;
 
 // Layer vector of one (cell, destination): areas of layers kmin .. kmin+len-1 at vpool[off ..], +inf where unreached.
 struct DirEnt { uint32_t off; uint16_t kmin, len; };
-struct SrcRec { double tri, refd; uint32_t off; uint16_t len, sidx; uint16_t c, cx; uint16_t kmin, pad; };   // sidx bit 15: LEFT
-static_assert(sizeof(SrcRec) == 32 && sizeof(DirEnt) == 8, "record layouts");
+// One live source edge of a cell, in two records: what the transition tests read (first vertex of the edge, pseudo-distance
+// of the other chain's head from the edge's line, :222 / :295) and what the sweeps read.  ceff = points added by the edge's
+// fan triangle (:188-190, with the extra collinear term of a layer-0 seed); pos = position in the sorted order of ALL s < head.
+struct SrcGeo { double refd, psx, psy; };
+struct SrcVal { double tri; uint32_t off; uint16_t len, kmin, ceff, pos; };
+static_assert(sizeof(SrcGeo) == 24 && sizeof(SrcVal) == 24 && sizeof(DirEnt) == 8, "record layouts");
+template <bool SPILL> struct LoType { typedef uint8_t type; };      // suffix starts / list links: bytes while a group has <= kGrp sources
+template <> struct LoType<true> { typedef uint16_t type; };
 
-// Per-CTA slice of the arena.
+// Per-CTA slice of the arena (two per CTA: the one being written and the one holding the CTA's best candidate so far).
 struct CellSlice
 {
     unsigned char* alive;     // nl*nr flags: cell wrote its directory ([a][b])
@@ -330,28 +351,23 @@ struct CellSlice
     DirEnt* dir;              // directory entries at fixed positions (dir_right / dir_left)
     uint16_t* nfin;           // per directory entry: number of finite layers (for the cell-update counter)
     double* vpool;            // layer vectors
-    SrcRec* spill;            // kCellWarps * spill_cap source records
-    uint32_t* spill_pred;     // kCellWarps * spill_cap predicate words
 };
 
-struct CellLayout { size_t off_aliveT, off_dir, off_nfin, off_v, off_spill, off_pred, bytes; uint32_t cap, spill_cap; };
+struct CellLayout { size_t off_aliveT, off_dir, off_nfin, off_v, bytes; uint32_t cap, pad; };
 
-__host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, uint32_t max_src, size_t slice_bytes)
+__host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, size_t slice_bytes)
 {
     CellLayout Lo;
     auto up = [](size_t v) { return (v + 255) & ~(size_t) 255; };
-    Lo.spill_cap = max_src;
     size_t o = up((size_t) max_cells);
     Lo.off_aliveT = o; o = up(o + (size_t) max_cells);
     Lo.off_dir = o; o = up(o + sizeof(DirEnt) * (size_t) max_dirs);
     Lo.off_nfin = o; o = up(o + sizeof(uint16_t) * (size_t) max_dirs);
-    Lo.off_spill = o; o = up(o + sizeof(SrcRec) * (size_t) kMaxCellWarps * max_src);
-    Lo.off_pred = o; o = up(o + sizeof(uint32_t) * (size_t) kMaxCellWarps * max_src);
     Lo.off_v = o;
     const size_t rest = slice_bytes > o + 4096 ? slice_bytes - o - 4096 : 0;
     const size_t cap = rest / sizeof(double);
     Lo.cap = (uint32_t) (cap > 0xfffffff0ull ? 0xfffffff0ull : cap) & ~31u;
-    Lo.bytes = slice_bytes;
+    Lo.bytes = slice_bytes; Lo.pad = 0;
     return Lo;
 }
 
@@ -364,9 +380,36 @@ __device__ __forceinline__ CellSlice carve_cells(unsigned char* arena, const Cel
     s.dir = reinterpret_cast<DirEnt*>(base + Lo.off_dir);
     s.nfin = reinterpret_cast<uint16_t*>(base + Lo.off_nfin);
     s.vpool = reinterpret_cast<double*>(base + Lo.off_v);
-    s.spill = reinterpret_cast<SrcRec*>(base + Lo.off_spill);
-    s.spill_pred = reinterpret_cast<uint32_t*>(base + Lo.off_pred);
     return s;
+}
+
+// Per-CTA auxiliary region (not kept between candidates): the per-candidate order / suffix-start tables and one spill
+// workspace per warp for the cells that outgrow the shared-memory workspace.
+//   sigR[b(b-1)/2 + r] = index s < b at sorted position r around R[b]          (sigL: the same around L[a])
+//   stayR[b*nr + i]    = first sorted position whose edge R[s]->R[b] may continue to R[i] (npot = none, kFB = not a suffix)
+struct AuxLayout { size_t off_sigL, off_stayR, off_stayL, off_spill, spill_bytes, bytes; uint32_t grp_cap, dst_cap; };
+
+// workspace of one warp: [suffix table: grp rows x 32 layers][sources: 2 groups x grp x 2 records][loR, loL, next: dst entries][heads: grp+1 x u32]
+__host__ __device__ inline size_t warp_ws_bytes(uint32_t grp, uint32_t dst, uint32_t lo_bytes)
+{
+    return ((size_t) grp * 256 + (size_t) 2 * grp * (sizeof(SrcGeo) + sizeof(SrcVal)) + (size_t) dst * 3 * lo_bytes + (size_t) (grp + 1) * 4 + 15) & ~(size_t) 15;
+}
+constexpr size_t kWarpWsBytes = ((size_t) kGrp * 256 + (size_t) 2 * kGrp * 48 + (size_t) kDstCap * 3 + (size_t) (kGrp + 1) * 4 + 15) & ~(size_t) 15;
+
+__host__ __device__ inline AuxLayout aux_layout(uint32_t max_nl, uint32_t max_nr)
+{
+    AuxLayout A;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t) 255; };
+    size_t o = up(sizeof(uint16_t) * ((size_t) max_nr * max_nr / 2 + 1));
+    A.off_sigL = o; o = up(o + sizeof(uint16_t) * ((size_t) max_nl * max_nl / 2 + 1));
+    A.off_stayR = o; o = up(o + sizeof(uint16_t) * (size_t) max_nr * max_nr);
+    A.off_stayL = o; o = up(o + sizeof(uint16_t) * (size_t) max_nl * max_nl);
+    A.off_spill = o;
+    A.grp_cap = max_nl > max_nr ? max_nl : max_nr;
+    A.dst_cap = (max_nl + max_nr + 3) & ~3u;
+    A.spill_bytes = up(warp_ws_bytes(A.grp_cap, A.dst_cap, 2));
+    A.bytes = up(o + A.spill_bytes * kMaxCellWarps);
+    return A;
 }
 
 // Directory position of the state vector "pending edge s -> e on one chain, head h on the other chain".  Consumer-major:
@@ -390,12 +433,12 @@ struct CellCtx
     LuneSmem S;
     CellSlice sl;
     uint32_t cap;
-    // warp-private shared memory
-    double* acc;            // 32 destinations x kRS layer rows
-    SrcRec* src;            // kSrcCap
-    uint32_t* pred;         // kSrcCap
-    SrcRec* spill;          // this warp's spill region (global)
-    uint32_t* spill_pred;
+    // per-candidate tables (global, per CTA)
+    uint16_t* sigR; uint16_t* sigL; uint16_t* stayR; uint16_t* stayL;
+    // warp-private workspaces: shared memory (kGrp / kDstCap) and the global spill (spill_grp / spill_dst)
+    unsigned char* wsmem;
+    unsigned char* wspill;
+    uint32_t spill_grp, spill_dst;
     // CTA-shared
     volatile uint32_t* rowdone;   // rowdone[a] = cells of row a finished (they finish in b order)
     volatile uint32_t* coldone;   // coldone[b] = cells of column b finished (in a order)
@@ -406,61 +449,127 @@ struct CellCtx
 
 constexpr unsigned kFull = 0xffffffffu;
 
-// Accumulates, for the 32 destinations of one tile, the layer rows [k0, k0 + rows) of acc (all +inf on entry):
-// acc[destination][row] = min over sources with a set predicate bit of (area + triangle), at layer k + c (:188-195, :207-217).
-// Only ~1 in 8 (source, destination) pairs passes the tests, so the sweep is sparse in the destinations: every lane holds
-// one LAYER ENTRY of the source (area + triangle) and relaxes it into the column of each passing destination in turn.
-// REG: the lane's predicate bits over the (at most 64) sources are in `mask`; otherwise preds[p] holds one word per source.
-template <bool REG>
-__device__ __forceinline__ void cell_accumulate(const CellCtx& C, const SrcRec* __restrict__ srcs, const uint32_t* __restrict__ preds,
-                                                unsigned long long mask, uint32_t P, uint32_t lane, uint32_t k0, uint32_t rows)
+// Direction of p seen from the head h as a monotone pseudo-angle in the frame of the candidate segment: x axis = sgn * (t - s)
+// (towards the side of the chain the sources lie on), sources in (-1, 1), increasing counter-clockwise.  Only the ORDER it
+// induces is used, and only for speed (see the header comment), so plain arithmetic is fine here.
+__device__ __forceinline__ double pseudo_angle(double fx, double fy, double sgn, double hx, double hy, double px, double py)
 {
-    const uint32_t dmax = min(C.lim, C.nlayers - 1);          // :192-195; layers beyond lim are never read
-    const uint32_t khi = min(k0 + rows - 1, dmax);
-    for (uint32_t p = 0; p < P; ++p)
+    const double dx = px - hx, dy = py - hy;
+    const double u = sgn * (dx * fx + dy * fy), v = sgn * (fx * dy - fy * dx);
+    const double den = fabs(u) + fabs(v);
+    if (den == 0.0) return 0.0;
+    const double r = v / den;
+    return u >= 0.0 ? r : (v >= 0.0 ? 2.0 - r : -2.0 - r);
+}
+
+// Builds, for one chain of the candidate, the sorted orders and the "stay" suffix starts.  All warps of the CTA take part
+// (heads dealt round robin); `keys` is the calling warp's scratch (>= n doubles).
+__device__ __noinline__ void build_chain_tables(const CellCtx& C, bool left, double* keys, uint32_t lane, uint32_t warp, uint32_t nw)
+{
+    const LuneSmem& S = C.S;
+    const uint32_t nc = left ? C.nl : C.nr;
+    const double* X = left ? S.Lx : S.Rx; const double* Y = left ? S.Ly : S.Ry;
+    uint16_t* sig = left ? C.sigL : C.sigR; uint16_t* stay = left ? C.stayL : C.stayR;
+    const double fx = C.Ex - C.Sx, fy = C.Ey - C.Sy, sgn = left ? -1.0 : 1.0;
+    const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;          // second "stay" test: the chain's own fan apex (:201, :274)
+    for (uint32_t h = 1 + warp; h < nc; h += nw)
     {
-        uint32_t dm;                                           // destinations of this tile that take source p
-        if (REG) dm = __ballot_sync(kFull, (mask >> p) & 1ull); else dm = preds[p];
-        if (!dm) continue;
-        __syncwarp();                                          // the previous source's relaxations (other lanes, same cells) are done
-        const SrcRec r = REG ? C.src[p] : srcs[p];
-        const double tri = r.tri;
-        if (r.kmin == 0)
-        {   // a layer-0 seed (:149-160): one record, and the count carries the extra collinear term
-            const uint32_t dst = (uint32_t) r.c + r.cx;
-            if (dst < k0 || dst > khi) continue;
-            const double v2 = __dadd_rn(C.sl.vpool[r.off], tri);
-            if (((dm >> lane) & 1u) && v2 <= C.amax) { double* q = C.acc + lane * kRS + (dst - k0); if (v2 < *q) *q = v2; }
-            continue;
-        }
-        // entries e (layer kmin + e) land on row kmin + e + c - k0
-        const int shift = (int) r.kmin + (int) r.c - (int) k0;
-        const int elo = max(0, -shift), ehi = min((int) r.len, (int) khi - (int) k0 + 1 - shift);
-        for (int e0 = elo; e0 < ehi; e0 += 32)
+        const double hx = X[h], hy = Y[h];
+        uint16_t* sg = sig + h * (h - 1) / 2;
+        for (uint32_t s = lane; s < h; s += 32) keys[s] = pseudo_angle(fx, fy, sgn, hx, hy, X[s], Y[s]);
+        __syncwarp();
+        for (uint32_t s = lane; s < h; s += 32)
         {
-            const int e = e0 + (int) lane;
-            double v2 = INFINITY;
-            int row = 0;
-            if (e < ehi)
+            const double ks = keys[s];
+            uint32_t r = 0;
+#pragma unroll 1
+            for (uint32_t t = 0; t < h; ++t) { const double kt = keys[t]; r += (kt < ks || (kt == ks && t < s)) ? 1u : 0u; }
+            sg[r] = (uint16_t) s;
+        }
+        __syncwarp();
+        for (uint32_t i0 = h + 1; i0 < nc; i0 += 32)
+        {
+            const uint32_t i = i0 + lane;
+            if (i < nc)
             {
-                row = e + shift;
-                v2 = __dadd_rn(C.sl.vpool[r.off + e], tri);
-                if (!(v2 <= C.amax)) v2 = INFINITY;                // :203, :229, :276, :302
-            }
-            double* q0 = C.acc + row;
-            for (uint32_t m = dm; m; m &= m - 1u)
-            {
-                double* q = q0 + (__ffs((int) m) - 1) * kRS;
-                if (v2 < *q) *q = v2;
+                const double qx = X[i], qy = Y[i];
+                uint32_t first = h, cnt = 0;
+                if (orientation(qx, qy, hx, hy, apx, apy) >= 0)
+#pragma unroll 1
+                    for (uint32_t r = 0; r < h; ++r)
+                    {
+                        const uint32_t s = sg[r];
+                        if (orientation(qx, qy, hx, hy, X[s], Y[s]) >= 0) { ++cnt; first = min(first, r); }
+                    }
+                stay[h * nc + i] = (uint16_t) (cnt == 0 ? h : (cnt == h - first ? first : kFB));
             }
         }
+        __syncwarp();
     }
 }
 
-// One warp expands every state of cell (a,b).  bk/bv: this lane's best terminal (layer, area).
-__device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint32_t b, uint32_t lane,
-                             uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
+// The complete transition test of one (source edge, destination) pair, exactly as the reference evaluates it
+// (:198-201, :225-229, :271-274, :298-302).  left = the source is a LEFT edge; dR = the destination is on the right chain.
+__device__ __forceinline__ bool dest_side_ok(const CellCtx& C, bool left, bool dR, uint32_t a, uint32_t b, double qx, double qy,
+                                             double Lax, double Lay, double Rbx, double Rby)
 {
+    if (dR)
+        return left ? (b == 0 || (orientation(Rbx, Rby, C.Sx, C.Sy, qx, qy) >= 0 && orientation(qx, qy, Rbx, Rby, C.Ex, C.Ey) >= 0))   // :301
+                    : orientation(qx, qy, Rbx, Rby, C.Sx, C.Sy) >= 0;                                                                 // :201
+    return left ? orientation(qx, qy, Lax, Lay, C.Ex, C.Ey) >= 0                                                                       // :274
+                : (a == 0 || (orientation(Lax, Lay, C.Ex, C.Ey, qx, qy) >= 0 && orientation(qx, qy, Lax, Lay, C.Sx, C.Sy) >= 0));     // :228
+}
+__device__ __forceinline__ bool pair_ok(bool left, bool dR, double psx, double psy, double hx, double hy, double refd, double qx, double qy)
+{
+    if (left != dR) return orientation(qx, qy, hx, hy, psx, psy) >= 0;     // stay on the edge's chain (:201, :274)
+    return pseudo_dist(psx, psy, hx, hy, qx, qy) <= refd;                   // switch chains (:226-227, :299-300)
+}
+
+// S_p[k]: what source r contributes to layer k of any destination it may continue to (:188-195, :203): area + triangle.
+__device__ __forceinline__ double src_value(const SrcVal& r, const double* __restrict__ vpool, uint32_t k, bool kact, double amax)
+{
+    const int e = (int) k - (int) r.ceff - (int) r.kmin;
+    double v = INFINITY;
+    if (kact && e >= 0 && e < (int) r.len)
+    {
+        v = __dadd_rn(vpool[r.off + e], r.tri);
+        if (!(v <= amax)) v = INFINITY;
+    }
+    return v;
+}
+
+// Minimum over the sources of one group that pass the tests of destination dd, pair by pair (lanes = layers): the path of a
+// destination whose passing sources are not a suffix of the sorted group (eps-degenerate inputs only).
+__device__ __noinline__ double explicit_min(const CellCtx& C, bool left, uint32_t dd, uint32_t k, bool kact, uint32_t a, uint32_t b,
+                                            const SrcGeo* sg, const SrcVal* sv, uint32_t P)
+{
+    const LuneSmem& S = C.S;
+    const uint32_t nDR = C.nr - 1 - b;
+    const bool dR = dd < nDR;
+    const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
+    const double qx = dR ? S.Rx[i] : S.Lx[i], qy = dR ? S.Ry[i] : S.Ly[i];
+    const double Lax = S.Lx[a], Lay = S.Ly[a], Rbx = S.Rx[b], Rby = S.Ry[b];
+    double v = INFINITY;
+    if (!dest_side_ok(C, left, dR, a, b, qx, qy, Lax, Lay, Rbx, Rby)) return v;
+    const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
+#pragma unroll 1
+    for (uint32_t p = 0; p < P; ++p)
+    {
+        const SrcGeo g = sg[p];
+        if (pair_ok(left, dR, g.psx, g.psy, hx, hy, g.refd, qx, qy)) v = fmin(v, src_value(sv[p], C.sl.vpool, k, kact, C.amax));
+    }
+    return v;
+}
+
+// One warp expands every state of cell (a,b).  bk/bv: this lane's best terminal (layer, area).
+// SPILL = false: the warp's workspace is in shared memory (at most kGrp sources per group); returns false, with nothing
+// written, when the cell does not fit.  SPILL = true: the same code over the warp's global workspace.
+template <bool SPILL>
+__device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint32_t b, uint32_t lane,
+                                             uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
+{
+    typedef typename LoType<SPILL>::type lo_t;
+    constexpr uint32_t FB = SPILL ? 0xffffu : 0xffu;     // suffix start "not a suffix" / list end, in lo_t
     const uint32_t nl = C.nl, nr = C.nr;
     const LuneSmem& S = C.S;
     const double Lax = S.Lx[a], Lay = S.Ly[a], Rbx = S.Rx[b], Rby = S.Ry[b];
@@ -470,241 +579,327 @@ __device__ void process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint
     const uint32_t nDR = nr - 1 - b, nDL = nl - 1 - a, D = nDR + nDL;
     const uint32_t lt = (1u << lane) - 1u;
     const uint32_t dmax = min(C.lim, C.nlayers - 1);
+    const double* __restrict__ vpool = C.sl.vpool;
 
-    // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b)
-    uint32_t P = 0, klo = 0xffffffffu, khi = 0;
-    const uint32_t npot = a + b;
-    // The directory reads of the NEXT block of 32 potential sources are issued before this block is worked on: they
-    // are L2 / HBM round trips (the entries were written by other warps), the geometry below hides them.
-    auto fetch = [&](uint32_t u0, unsigned char& al, DirEnt& dd, uint32_t& nf)
+    unsigned char* wbase = SPILL ? C.wspill : C.wsmem;
+    const uint32_t gcap = SPILL ? C.spill_grp : (uint32_t) kGrp;
+    const uint32_t dcap = SPILL ? C.spill_dst : (uint32_t) kDstCap;
+    double* tab = reinterpret_cast<double*>(wbase);                              // suffix minima of the LEFT group, [row][layer lane]
+    SrcGeo* geo = reinterpret_cast<SrcGeo*>(wbase + (size_t) gcap * 256);        // [0, gcap): RIGHT group, [gcap, 2 gcap): LEFT group
+    SrcVal* val = reinterpret_cast<SrcVal*>(geo + 2 * gcap);
+    lo_t* loRs = reinterpret_cast<lo_t*>(val + 2 * gcap);
+    lo_t* loLs = loRs + dcap;
+    lo_t* nxt = loLs + dcap;
+    uint32_t* head = reinterpret_cast<uint32_t*>(nxt + dcap);
+
+    // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b),
+    //      each group in its sorted order (the compaction keeps it)
+    uint32_t PR = 0, PL = 0;
+    uint32_t klo = 0xffffffffu, khi = 0;
+    unsigned long long cells_add = 0;
+#pragma unroll 1
+    for (int g = 0; g < 2; ++g)
     {
-        const uint32_t u = u0 + lane;
-        al = 0; dd.off = 0; dd.kmin = 0; dd.len = 0; nf = 0;
-        if (u < npot)
+        const bool left = g == 1;
+        const uint32_t npot = left ? a : b;
+        const uint16_t* sg = left ? C.sigL + a * (a - 1) / 2 : C.sigR + b * (b - 1) / 2;
+        const bool term = left ? term_l : term_r;
+        const double* GX = left ? S.Lx : S.Rx; const double* GY = left ? S.Ly : S.Ry;
+        const int32_t* GI = left ? S.Lidx : S.Ridx;
+        const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
+        const int hidx = left ? Laidx : Rbidx;
+        const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;      // fan apex of the edge's own chain
+        const int ap = left ? C.Ep : C.Sp;
+        const double ox = left ? Rbx : Lax, oy = left ? Rby : Lay;            // head of the other chain
+        const uint32_t obase = left ? gcap : 0u;
+        uint32_t P = 0;
+        // The directory reads of the NEXT block of 32 potential sources are issued before this block is worked on (and the
+        // sorted indices one block further ahead): they are L2 / HBM round trips, the geometry below hides them.
+        uint32_t s_n = lane < npot ? (uint32_t) sg[lane] : 0u, s_nn = 32 + lane < npot ? (uint32_t) sg[32 + lane] : 0u;
+        unsigned char al_n = 0; DirEnt dd_n; dd_n.off = 0; dd_n.kmin = 0; dd_n.len = 0; uint32_t nf_n = 0;
+        if (lane < npot)
         {
-            const bool left = u >= b; const uint32_t s = left ? u - b : u;
-            const uint32_t dix = left ? dir_left(b, a, s, nl, nr) : dir_right(a, b, s, nr);
-            al = left ? C.sl.aliveT[b * nl + s] : C.sl.alive[a * nr + s];       // the flag and the entry are loaded together: the entry
-            dd = C.sl.dir[dix];                  // of a cell that produced nothing is stale and ignored
-            nf = C.sl.nfin[dix];
+            const uint32_t dix = left ? dir_left(b, a, s_n, nl, nr) : dir_right(a, b, s_n, nr);
+            al_n = left ? C.sl.aliveT[b * nl + s_n] : C.sl.alive[a * nr + s_n];
+            dd_n = C.sl.dir[dix]; nf_n = C.sl.nfin[dix];
         }
-    };
-    unsigned char al_n; DirEnt dd_n; uint32_t nf_n;
-    fetch(0, al_n, dd_n, nf_n);
-    for (uint32_t u0 = 0; u0 < npot; u0 += 32)
-    {
-        const uint32_t u = u0 + lane;
-        bool live = false, left = false;
-        uint32_t s = 0, nfin_src = 0;
-        DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
-        const unsigned char al = al_n; const DirEnt dd = dd_n; nfin_src = nf_n;
-        if (u0 + 32 < npot) fetch(u0 + 32, al_n, dd_n, nf_n);
-        if (u < npot)
+#pragma unroll 1
+        for (uint32_t u0 = 0; u0 < npot; u0 += 32)
         {
-            left = u >= b; s = left ? u - b : u;
-            if (al) { de = dd; live = de.len > 0; }
+            const uint32_t u = u0 + lane;
+            const uint32_t s = s_n;
+            const unsigned char al = al_n; const DirEnt dd = dd_n; const uint32_t nfin_src = nf_n;
+            s_n = s_nn;
+            if (u + 32 < npot)
+            {   // the flag and the entry are loaded together: the entry of a cell that produced nothing is stale and ignored
+                const uint32_t dix = left ? dir_left(b, a, s_n, nl, nr) : dir_right(a, b, s_n, nr);
+                al_n = left ? C.sl.aliveT[b * nl + s_n] : C.sl.alive[a * nr + s_n];
+                dd_n = C.sl.dir[dix]; nf_n = C.sl.nfin[dix];
+            }
+            s_nn = u + 64 < npot ? (uint32_t) sg[u + 64] : 0u;
+            bool live = u < npot && al && dd.len > 0;
+            const DirEnt de = dd;
             if (live)
             {   // pull the layer vector towards L1 while the geometry below is computed
-                const char* v0 = reinterpret_cast<const char*>(C.sl.vpool + de.off);
-                const char* v1 = reinterpret_cast<const char*>(C.sl.vpool + de.off + de.len - 1);
-#ifndef ADK_PREFETCH
-#define ADK_PREFETCH 1
-#endif
-#if ADK_PREFETCH == 1
-                for (const char* q = v0; q <= v1; q += 128) asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
+                const char* v0 = reinterpret_cast<const char*>(vpool + de.off);
+                const char* v1 = reinterpret_cast<const char*>(vpool + de.off + de.len - 1);
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(v0));
                 asm volatile("prefetch.global.L1 [%0];" ::"l"(v1));
-#elif ADK_PREFETCH == 2
-                for (const char* q = v0; q <= v1; q += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(v1));
-#else
-                (void) v0; (void) v1;
-#endif
+                if (v1 - v0 > 256) asm volatile("prefetch.global.L1 [%0];" ::"l"(v0 + 128));
             }
-        }
-        const uint32_t kmax = (uint32_t) de.kmin + de.len - 1;
-        if (live && (left ? term_l : term_r))
-        {   // terminal states only report (:167-175): the deepest layer of this edge is its best
-            if (kmax > 0)
+            const uint32_t kmax = (uint32_t) de.kmin + de.len - 1;
+            if (live && term)
+            {   // terminal states only report (:167-175): the deepest layer of this edge is its best
+                if (kmax > 0)
+                {
+                    const double v = vpool[de.off + de.len - 1];
+                    if (kmax > bk || (kmax == bk && v < bv)) { bk = kmax; bv = v; }
+                }
+                live = false;
+            }
+            if (dead) live = false;
+            SrcGeo rg; rg.refd = 0.0; rg.psx = 0.0; rg.psy = 0.0;
+            SrcVal rv; rv.tri = 0.0; rv.off = de.off; rv.len = de.len; rv.kmin = de.kmin; rv.ceff = 0; rv.pos = (uint16_t) u;
+            if (live)
             {
-                const double v = C.sl.vpool[de.off + de.len - 1];
-                if (kmax > bk || (kmax == bk && v < bv)) { bk = kmax; bv = v; }
+                const double psx = GX[s], psy = GY[s];
+                const int pidx = GI[s];
+                rg.psx = psx; rg.psy = psy;
+                rv.tri = fabs(signed_area(apx, apy, psx, psy, hx, hy));               // :188 / :261
+                const uint32_t c = 1u + (uint32_t) tri_count_ad(T, false, pidx, psx, psy, hidx, hx, hy, ap, apx, apy);
+                const uint32_t ceff = c + (de.kmin == 0 ? (uint32_t) T.C(pidx, ap) : 0u);   // only the seeds sit on layer 0 (:33-36)
+                rv.ceff = (uint16_t) ceff;
+                rg.refd = pseudo_dist(psx, psy, hx, hy, ox, oy);                      // :222 / :295
+                // cell updates the reference performs for these states (:198,225,271,298), and the output layer range
+                uint32_t nvalid = nfin_src;
+                if (kmax + ceff >= C.nlayers)
+                {
+                    nvalid = 0;
+#pragma unroll 1
+                    for (uint32_t e = 0; e < de.len; ++e)
+                        nvalid += (vpool[de.off + e] < INFINITY && de.kmin + e + ceff < C.nlayers) ? 1u : 0u;
+                }
+                cells_add += (unsigned long long) nvalid * D;
+                const uint32_t lo = de.kmin + ceff, hi = min(kmax + ceff, dmax);
+                if (nvalid == 0 || lo > hi || !(rv.tri <= C.amax)) live = false;
+                else { klo = min(klo, lo); khi = max(khi, hi); }
             }
-            live = false;
-        }
-        if (dead) live = false;
-        SrcRec r; r.tri = 0.0; r.refd = 0.0; r.off = de.off; r.len = de.len; r.kmin = de.kmin; r.sidx = 0; r.c = 0; r.cx = 0; r.pad = 0;
-        if (live)
-        {
-            const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
-            const int pidx = left ? S.Lidx[s] : S.Ridx[s];
-            const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
-            const int hidx = left ? Laidx : Rbidx;
-            const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;      // fan apex of the edge's own chain
-            const int ap = left ? C.Ep : C.Sp;
-            const double ox = left ? Rbx : Lax, oy = left ? Rby : Lay;            // head of the other chain
-            r.tri = fabs(signed_area(apx, apy, psx, psy, hx, hy));               // :188 / :261
-            const uint32_t c = 1u + (uint32_t) tri_count_ad(T, false, pidx, psx, psy, hidx, hx, hy, ap, apx, apy);
-            const uint32_t cx = (uint32_t) T.C(pidx, ap);
-            r.c = (uint16_t) c; r.cx = (uint16_t) cx;
-            r.refd = pseudo_dist(psx, psy, hx, hy, ox, oy);                      // :222 / :295
-            r.sidx = (uint16_t) (s | (left ? 0x8000u : 0u));
-            // cell updates the reference performs for these states (:198,225,271,298), and the output layer range
-            const uint32_t ceff = c + (de.kmin == 0 ? cx : 0u);                  // only the seeds sit on layer 0
-            uint32_t nvalid = nfin_src;
-            if (kmax + ceff >= C.nlayers)
-            {
-                nvalid = 0;
-                for (uint32_t e = 0; e < de.len; ++e)
-                    nvalid += (C.sl.vpool[de.off + e] < INFINITY && de.kmin + e + ceff < C.nlayers) ? 1u : 0u;
-            }
-            my_cells += (unsigned long long) nvalid * D;
-            const uint32_t lo = de.kmin + ceff, hi = min(kmax + ceff, dmax);
-            if (nvalid == 0 || lo > hi || !(r.tri <= C.amax)) live = false;
-            else { klo = min(klo, lo); khi = max(khi, hi); }
-        }
-        const uint32_t lm = __ballot_sync(kFull, live);
-        if (live)
-        {
+            const uint32_t lm = __ballot_sync(kFull, live);
             const uint32_t at = P + __popc(lm & lt);
-            if (at < (uint32_t) kSrcCap) C.src[at] = r; else C.spill[at] = r;
+            P += __popc(lm);
+            if (!SPILL && P > gcap) return false;          // does not fit in shared memory: nothing has been written yet
+            if (live) { geo[obase + at] = rg; val[obase + at] = rv; }
         }
-        P += __popc(lm);
+        if (left) PL = P; else PR = P;
     }
-    if (P == 0 || D == 0) return;
+    my_cells += cells_add;
+    if (PR + PL == 0 || D == 0) return true;
     klo = __reduce_min_sync(kFull, klo); khi = __reduce_max_sync(kFull, khi);
     __syncwarp();
-    const bool spilled = P > (uint32_t) kSrcCap;       // rare: the whole source list then lives in the global spill
-    if (spilled) { for (uint32_t t = lane; t < (uint32_t) kSrcCap; t += 32) C.spill[t] = C.src[t]; __syncwarp(); }
-    const SrcRec* srcs = spilled ? C.spill : C.src;
-    uint32_t* preds = C.spill_pred;                    // only used when spilled
     const uint32_t ntiles = (khi - klo + kBT) / kBT;
 
-    for (uint32_t d0 = 0; d0 < D; d0 += 32)
+#pragma unroll 1
+    for (uint32_t dc0 = 0; dc0 < D; dc0 += dcap)
     {
-        const uint32_t d = d0 + lane;
-        const bool have = d < D, dR = d < nDR;
-        const uint32_t i = dR ? b + 1 + d : a + 1 + (d - nDR);
-        double qx = 0.0, qy = 0.0;
-        bool okR = false, okL = false;      // the part of the transition test that does not depend on the source edge
-        if (have)
-        {
-            qx = dR ? S.Rx[i] : S.Lx[i]; qy = dR ? S.Ry[i] : S.Ly[i];
-            if (dR)
-            {
-                okR = orientation(qx, qy, Rbx, Rby, C.Sx, C.Sy) >= 0;                                                        // :201 second test
-                okL = b == 0 || (orientation(Rbx, Rby, C.Sx, C.Sy, qx, qy) >= 0 && orientation(qx, qy, Rbx, Rby, C.Ex, C.Ey) >= 0);   // :301
-            }
-            else
-            {
-                okL = orientation(qx, qy, Lax, Lay, C.Ex, C.Ey) >= 0;                                                        // :274 second test
-                okR = a == 0 || (orientation(Lax, Lay, C.Ex, C.Ey, qx, qy) >= 0 && orientation(qx, qy, Lax, Lay, C.Sx, C.Sy) >= 0);   // :228
-            }
-        }
-        // per (source edge, destination) geometry, once for all layers
-        uint32_t anyp = 0;
-        unsigned long long mask = 0ull;
-        for (uint32_t p = 0; p < P; ++p)
-        {
-            const uint32_t sx = srcs[p].sidx;
-            const double refd = srcs[p].refd;
-            const bool left = (sx & 0x8000u) != 0;
-            const uint32_t s = sx & 0x7fffu;
-            const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
-            const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
-            bool ok = false;
-            if (have && (left ? okL : okR))
-            {
-                if (left != dR) ok = orientation(qx, qy, hx, hy, psx, psy) >= 0;     // stay on the edge's chain (:201, :274)
-                else ok = pseudo_dist(psx, psy, hx, hy, qx, qy) <= refd;             // switch chains (:226-227, :299-300)
-            }
-            if (!spilled) mask |= (unsigned long long) ok << p;
-            else
-            {
-                const uint32_t m = __ballot_sync(kFull, ok);
-                if (lane == 0) preds[p] = m;
-                anyp |= m;
-            }
-        }
-        if (!spilled) anyp = __any_sync(kFull, mask != 0ull) ? 1u : 0u;
+        const uint32_t nd = min(dcap, D - dc0);
+#pragma unroll 1
+        for (uint32_t t = lane; t <= PR; t += 32) head[t] = FB;
         __syncwarp();
-        // the destination's layer vector: first .. last finite layer, holes stay +inf
-        // A cell deeper than one accumulator tile is still swept once: the vector is given room up to the cell's last
-        // layer when its first finite layer shows up, later tiles append to it (the unused tail is never read).
-        uint32_t first = 0, last = 0, nfin = 0, off = 0;
-        bool fits = true, started = false;
-        if (anyp)
+        // ---- suffix starts: lanes = destinations
+#pragma unroll 1
+        for (uint32_t d0 = 0; d0 < nd; d0 += 32)
         {
-            for (uint32_t t = 0; t < ntiles; ++t)
+            const uint32_t dl = d0 + lane, dd = dc0 + dl;
+            const bool have = dl < nd;
+            uint32_t loR = PR, loL = PL;
+            if (have)
             {
-                const uint32_t k0 = klo + t * kBT, rows = min((uint32_t) kBT, khi + 1 - k0);
-                if (!spilled) cell_accumulate<true>(C, srcs, preds, mask, P, lane, k0, rows);
-                else cell_accumulate<false>(C, srcs, preds, 0ull, P, lane, k0, rows);
-                uint32_t tfirst = 0xffffffffu, tlast = 0, tn = 0;
-                for (uint32_t rr = 0; rr < rows; ++rr)
-                    if (C.acc[lane * kRS + rr] < INFINITY) { tfirst = min(tfirst, k0 + rr); tlast = k0 + rr; ++tn; }
-                const uint32_t need = (tn && !started) ? (ntiles == 1 ? tlast - tfirst + 1 : khi - tfirst + 1) : 0u;
-                if (__any_sync(kFull, need != 0u))
-                {   // allocate the vectors that start in this tile: exclusive scan over the lanes, one bump of the CTA's pool
-                    uint32_t incl = need;
-                    for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(kFull, incl, o); if ((int) lane >= o) incl += v; }
-                    const uint32_t total = __shfl_sync(kFull, incl, 31);
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(C.bump, total);
-                    base = __shfl_sync(kFull, base, 0);
-                    const bool ok = (unsigned long long) base + total <= C.cap;
-                    if (!ok && lane == 0) *C.overflow = 1u;
-                    if (need) { started = true; first = tfirst; off = base + incl - need; fits = ok; }
-                }
-                if (started)
-                {   // copy this lane's rows out (holes stay +inf) and leave the column clean
-                    const uint32_t r0 = max(first, k0), r1 = ntiles == 1 ? tlast : k0 + rows - 1;
-                    for (uint32_t k = r0; k <= r1; ++k)
-                    {
-                        double* q = C.acc + lane * kRS + (k - k0);
-                        if (fits) C.sl.vpool[off + (k - first)] = *q;
-                        *q = INFINITY;
+                const bool dR = dd < nDR;
+                const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
+                const double qx = dR ? S.Rx[i] : S.Lx[i], qy = dR ? S.Ry[i] : S.Ly[i];
+#pragma unroll 1
+                for (int g = 0; g < 2; ++g)
+                {
+                    const bool left = g == 1;
+                    const uint32_t P = left ? PL : PR;
+                    const uint32_t obase = left ? gcap : 0u;
+                    uint32_t lo = P;
+                    if (P == 0) { }
+                    else if (left != dR)
+                    {   // stay: tabulated over ALL s < head (the tests do not depend on the other head); count the live sources before it
+                        const uint32_t lf = left ? C.stayL[a * nl + i] : C.stayR[b * nr + i];
+                        if (lf == kFB) lo = FB;
+                        else
+                        {   // lower bound of lf in the (ascending) sorted positions of the live sources
+                            uint32_t base = 0, len = P;
+#pragma unroll 1
+                            while (len)
+                            {
+                                const uint32_t half = len >> 1;
+                                if (val[obase + base + half].pos < lf) { base += half + 1; len -= half + 1; } else len = half;
+                            }
+                            lo = base;
+                        }
                     }
-                    if (tn) { last = tlast; nfin += tn; }
+                    else if (dest_side_ok(C, left, dR, a, b, qx, qy, Lax, Lay, Rbx, Rby))
+                    {   // switch: one pseudo-distance test per live source (:226-227, :299-300)
+                        const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
+                        const SrcGeo* gp = geo + obase;
+                        uint32_t first = P, cnt = 0;
+#pragma unroll 2
+                        for (uint32_t p = 0; p < P; ++p)
+                        {
+                            const SrcGeo q = gp[p];
+                            if (pseudo_dist(q.psx, q.psy, hx, hy, qx, qy) <= q.refd) { ++cnt; first = min(first, p); }
+                        }
+                        lo = cnt == 0 ? P : (cnt == P - first ? first : FB);
+                    }
+                    if (left) loL = lo; else loR = lo;
+                }
+                loRs[dl] = (lo_t) loR; loLs[dl] = (lo_t) loL;
+            }
+            // destinations with equal suffix starts have equal layer vectors: one of them (the leader) is swept
+            const bool fb = loR == FB || loL == FB;
+            const uint32_t key = !have ? 0xffffffffu : (fb ? (0x80000000u | dl) : (loR | (loL << 16)));
+            const uint32_t peers = __match_any_sync(kFull, key);
+            const bool empty = loR == PR && loL == PL;
+            if (have && !empty && (uint32_t) (__ffs((int) peers) - 1) == lane)
+                nxt[dl] = (lo_t) atomicExch(&head[loR == FB ? PR : loR], dl);
+        }
+        __syncwarp();
+        // ---- the sweep: lanes = layers
+#pragma unroll 1
+        for (uint32_t t = 0; t < ntiles; ++t)
+        {
+            const uint32_t k0 = klo + t * kBT, k = k0 + lane;
+            const bool kact = k <= khi;
+            {   // suffix minima of the LEFT group
+                const SrcVal* vl = val + gcap;
+                double v = INFINITY;
+#pragma unroll 2
+                for (int r = (int) PL - 1; r >= 0; --r)
+                {
+                    v = fmin(v, src_value(vl[r], vpool, k, kact, C.amax));
+                    tab[(size_t) r * 32 + lane] = v;
                 }
             }
+            // backward sweep over the RIGHT group; the destinations whose suffix starts at r are emitted when r is reached
+            double vR = INFINITY;
+            double pend = PR ? src_value(val[PR - 1], vpool, k, kact, C.amax) : INFINITY;
+#pragma unroll 1
+            for (int r = (int) PR; r >= 0; --r)
+            {
+                if (r < (int) PR)
+                {
+                    const double cur = pend;
+                    if (r > 0) pend = src_value(val[r - 1], vpool, k, kact, C.amax);
+                    vR = fmin(vR, cur);
+                }
+#pragma unroll 1
+                for (uint32_t dl = head[r]; dl != FB; dl = nxt[dl])
+                {
+                    const uint32_t dd = dc0 + dl;
+                    const uint32_t loR = loRs[dl], loL = loLs[dl];
+                    double v = vR;
+                    if (loL < PL) v = fmin(v, tab[(size_t) loL * 32 + lane]);
+                    if (loL == FB) v = fmin(v, explicit_min(C, true, dd, k, kact, a, b, geo + gcap, val + gcap, PL));
+                    if (loR == FB) v = fmin(v, explicit_min(C, false, dd, k, kact, a, b, geo, val, PR));
+                    const bool dR = dd < nDR;
+                    const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
+                    const uint32_t dix = dR ? dir_right(a, i, b, nr) : dir_left(b, i, a, nl, nr);
+                    // the destination's layer vector: first .. last finite layer, holes stay +inf.  A cell deeper than one tile
+                    // is still swept once: the vector is given room up to the cell's last layer when its first finite layer
+                    // shows up, later tiles append to it (the unused tail is never read).
+                    DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
+                    uint32_t nf = 0;
+                    if (t > 0) { de = C.sl.dir[dix]; nf = C.sl.nfin[dix]; }
+                    const uint32_t fm = __ballot_sync(kFull, v < INFINITY);
+                    bool started = de.len > 0;
+                    if (fm)
+                    {
+                        const uint32_t tfirst = k0 + (uint32_t) __ffs((int) fm) - 1u, tlast = k0 + 31u - (uint32_t) __clz((int) fm);
+                        if (!started)
+                        {
+                            const uint32_t need = ntiles == 1 ? tlast - tfirst + 1 : khi - tfirst + 1;
+                            uint32_t base = 0;
+                            if (lane == 0) base = atomicAdd(C.bump, need);
+                            base = __shfl_sync(kFull, base, 0);
+                            if ((unsigned long long) base + need <= C.cap) { started = true; de.off = base; de.kmin = (uint16_t) tfirst; }
+                            else if (lane == 0) *C.overflow = 1u;
+                        }
+                        if (started) { de.len = (uint16_t) (tlast - de.kmin + 1); nf += __popc(fm); }
+                    }
+                    if (started && kact && k >= de.kmin && (ntiles > 1 || k < (uint32_t) de.kmin + de.len))
+                        C.sl.vpool[de.off + (k - de.kmin)] = v;
+                    if (lane == 0 && (t == 0 || fm)) { C.sl.dir[dix] = de; C.sl.nfin[dix] = (uint16_t) nf; }
+                }
+            }
+            __syncwarp();
         }
-        my_states += (started && fits) ? nfin : 0u;
-        if (have)
+        // ---- every destination gets its directory entry: the leader's record is shared by its peers
+#pragma unroll 1
+        for (uint32_t d0 = 0; d0 < nd; d0 += 32)
         {
-            DirEnt de; de.off = off; de.kmin = (uint16_t) (started ? first : 0u); de.len = (uint16_t) ((fits && started) ? last - first + 1 : 0u);
-            const uint32_t dix = dR ? dir_right(a, i, b, nr) : dir_left(b, i, a, nl, nr);
-            C.sl.dir[dix] = de;
-            C.sl.nfin[dix] = (uint16_t) nfin;
+            const uint32_t dl = d0 + lane, dd = dc0 + dl;
+            const bool have = dl < nd;
+            const uint32_t loR = have ? (uint32_t) loRs[dl] : PR, loL = have ? (uint32_t) loLs[dl] : PL;
+            const bool fb = loR == FB || loL == FB;
+            const uint32_t key = !have ? 0xffffffffu : (fb ? (0x80000000u | dl) : (loR | (loL << 16)));
+            const uint32_t peers = __match_any_sync(kFull, key);
+            const int leader = __ffs((int) peers) - 1;
+            const bool empty = loR == PR && loL == PL;
+            const bool dR = dd < nDR;
+            const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
+            const uint32_t dix = have ? (dR ? dir_right(a, i, b, nr) : dir_left(b, i, a, nl, nr)) : 0u;
+            DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
+            uint32_t nf = 0;
+            if (have && !empty && leader == (int) lane) { de = C.sl.dir[dix]; nf = C.sl.nfin[dix]; }
+            const uint32_t off = __shfl_sync(kFull, de.off, leader);
+            const uint32_t kl = __shfl_sync(kFull, (uint32_t) de.kmin | ((uint32_t) de.len << 16), leader);
+            nf = __shfl_sync(kFull, nf, leader);
+            if (have && (empty || leader != (int) lane))
+            {
+                DirEnt w; w.off = empty ? 0u : off; w.kmin = (uint16_t) (empty ? 0u : (kl & 0xffffu)); w.len = (uint16_t) (empty ? 0u : (kl >> 16));
+                C.sl.dir[dix] = w;
+                C.sl.nfin[dix] = (uint16_t) (empty ? 0u : nf);
+            }
+            my_states += (have && !empty) ? nf : 0u;
         }
+        __syncwarp();
     }
-    __syncwarp();
     if (lane == 0) { C.sl.alive[a * nr + b] = 1; C.sl.aliveT[b * nl + a] = 1; }
+    return true;
+}
+
+__device__ __noinline__ void process_cell_spilled(const CellCtx& C, const Tables& T, uint32_t a, uint32_t b, uint32_t lane,
+                                                  uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
+{
+    process_cell<true>(C, T, a, b, lane, bk, bv, my_cells, my_states);
 }
 
 struct CandResult { uint32_t kbest; uint32_t states; double area; };     // best terminal layer (0 = none) of one candidate
 
-// Shared memory of k_ad_cells: [per-warp accumulators | per-warp source lists | lune coordinates + indices | done counters].
+// Shared memory of k_ad_cells: [per-warp workspaces | lune coordinates + indices | done counters].
 // The staging arrays of build_lune (projection keys, unsorted indices) are only live while the lists are built, so they
-// alias the accumulators, which are re-initialised afterwards.
-__host__ __device__ inline size_t cells_acc_bytes(uint32_t nw) { return sizeof(double) * kRS * 32 * nw; }
+// alias the workspaces.
+__host__ __device__ inline size_t cells_ws_bytes(uint32_t nw) { return kWarpWsBytes * nw; }
 __host__ __device__ inline size_t cells_stage_bytes(uint32_t capL, uint32_t capR) { return (size_t) (capL + capR) * (sizeof(double) + sizeof(int32_t)); }
 __host__ __device__ inline size_t cells_front_bytes(uint32_t capL, uint32_t capR, uint32_t nw)
 {
-    const size_t a = cells_acc_bytes(nw), b = (cells_stage_bytes(capL, capR) + 15) & ~(size_t) 15;
+    const size_t a = cells_ws_bytes(nw), b = (cells_stage_bytes(capL, capR) + 15) & ~(size_t) 15;
     return a > b ? a : b;
 }
 __host__ __device__ inline size_t cells_smem_bytes(uint32_t capL, uint32_t capR, uint32_t nw)
 {
-    return cells_front_bytes(capL, capR, nw) + sizeof(SrcRec) * kSrcCap * nw
-           + (size_t) (capL + capR) * (2 * sizeof(double) + sizeof(int32_t) + sizeof(uint32_t)) + 16;
+    return cells_front_bytes(capL, capR, nw) + (size_t) (capL + capR) * (2 * sizeof(double) + sizeof(int32_t) + sizeof(uint32_t)) + 16;
 }
 
 __device__ __forceinline__ LuneSmem carve_cells_smem(unsigned char* smem_raw, uint32_t capL, uint32_t capR, uint32_t nw, uint32_t** done)
 {
     LuneSmem S;
-    S.tproj = reinterpret_cast<double*>(smem_raw);                                  // aliases the accumulators
+    S.tproj = reinterpret_cast<double*>(smem_raw);                                  // aliases the workspaces
     S.tidx = reinterpret_cast<int32_t*>(smem_raw + sizeof(double) * (capL + capR));
-    double* d = reinterpret_cast<double*>(smem_raw + cells_front_bytes(capL, capR, nw) + sizeof(SrcRec) * kSrcCap * nw);
+    double* d = reinterpret_cast<double*>(smem_raw + cells_front_bytes(capL, capR, nw));
     S.Lx = d; d += capL; S.Ly = d; d += capL; S.Rx = d; d += capR; S.Ry = d; d += capR;
     int32_t* q = reinterpret_cast<int32_t*>(d);
     S.Lidx = q; q += capL; S.Ridx = q; q += capR;
@@ -720,11 +915,10 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
                               CellCtx& C, uint32_t* s_cnt, uint32_t* s_wk, double* s_wv, uint64_t kmax, uint32_t nlayers_ref,
                               unsigned long long& my_cells, unsigned int& my_states, CandResult& out, unsigned int* s_cstates)
 {
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const unsigned int states0 = my_states;
     if (threadIdx.x == 0) *s_cstates = 0u;
     build_lune(x, y, n, pr, C.S, s_cnt);
-    for (uint32_t t = lane; t < (uint32_t) kRS * 32; t += 32) C.acc[t] = INFINITY;     // build_lune staged its keys here
     const uint32_t nl = pr.nl, nr = pr.nr;
     const uint64_t inner = (uint64_t) nl + nr - 4;
     C.nl = nl; C.nr = nr;
@@ -733,6 +927,13 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
     C.Sx = C.S.Lx[0]; C.Sy = C.S.Ly[0]; C.Ex = C.S.Lx[nl - 1]; C.Ey = C.S.Ly[nl - 1];
     C.Sp = C.S.Lidx[0]; C.Ep = C.S.Lidx[nl - 1];
     C.seg2 = dist2(C.Sx, C.Sy, C.Ex, C.Ey);
+    // sorted orders and "stay" suffix starts of both chains (the key scratch is the warp's own workspace)
+    {
+        const uint32_t nmax = nl > nr ? nl : nr;
+        double* keys = nmax * sizeof(double) <= kWarpWsBytes ? reinterpret_cast<double*>(C.wsmem) : reinterpret_cast<double*>(C.wspill);
+        build_chain_tables(C, false, keys, lane, warp, nw);
+        build_chain_tables(C, true, keys, lane, warp, nw);
+    }
     // reset the slice: no cell has produced anything; cell (0,0) "produces" the layer-0 seeds (:149-160):
     // RIGHT(0; 0->i) and LEFT(0; 0->i) all share one record (layer 0, area 0)
     for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) { C.sl.alive[t] = t == 0 ? 1 : 0; C.sl.aliveT[t] = t == 0 ? 1 : 0; }
@@ -768,7 +969,8 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
         if (lane == 0) while (C.rowdone[a] < b || C.coldone[b] < a) __nanosleep(32);
         __syncwarp();
         __threadfence_block();
-        process_cell(C, T, a, b, lane, bk, bv, my_cells, my_states);
+        if (!process_cell<false>(C, T, a, b, lane, bk, bv, my_cells, my_states))
+            process_cell_spilled(C, T, a, b, lane, bk, bv, my_cells, my_states);
         __threadfence_block();
         __syncwarp();
         if (lane == 0) { C.rowdone[a] = b + 1; C.coldone[b] = a + 1; }
@@ -791,20 +993,21 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
 }
 
 __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, uint32_t capL, uint32_t capR, unsigned char* arena,
-                                          const CellLayout& Lo, uint32_t slice, double amax, unsigned int* next, unsigned int* bump,
-                                          unsigned int* overflow)
+                                          const CellLayout& Lo, uint32_t slice, unsigned char* aux, const AuxLayout& Ax, double amax,
+                                          unsigned int* next, unsigned int* bump, unsigned int* overflow)
 {
     const uint32_t warp = threadIdx.x >> 5;
     uint32_t* done = nullptr;
     const uint32_t nw = blockDim.x >> 5;
     C.S = carve_cells_smem(smem_raw, capL, capR, nw, &done);
-    C.acc = reinterpret_cast<double*>(smem_raw) + (size_t) warp * kRS * 32;
-    C.src = reinterpret_cast<SrcRec*>(smem_raw + cells_front_bytes(capL, capR, nw)) + (size_t) warp * kSrcCap;
-    C.pred = nullptr;                          // predicate words only exist on the (global) spill path
+    C.wsmem = smem_raw + kWarpWsBytes * warp;
+    unsigned char* ax = aux + (size_t) blockIdx.x * Ax.bytes;
+    C.sigR = reinterpret_cast<uint16_t*>(ax); C.sigL = reinterpret_cast<uint16_t*>(ax + Ax.off_sigL);
+    C.stayR = reinterpret_cast<uint16_t*>(ax + Ax.off_stayR); C.stayL = reinterpret_cast<uint16_t*>(ax + Ax.off_stayL);
+    C.wspill = ax + Ax.off_spill + Ax.spill_bytes * warp;
+    C.spill_grp = Ax.grp_cap; C.spill_dst = Ax.dst_cap;
     C.rowdone = done; C.coldone = done + capL;
     C.sl = carve_cells(arena, Lo, slice);
-    C.spill = C.sl.spill + (size_t) warp * Lo.spill_cap;
-    C.spill_pred = C.sl.spill_pred + (size_t) warp * Lo.spill_cap;
     C.cap = Lo.cap; C.amax = amax; C.next = next; C.bump = bump; C.overflow = overflow;
 }
 
@@ -814,7 +1017,7 @@ template <int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB)
 k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t n, Tables T,
            const PairRec* __restrict__ pairs, const uint32_t* __restrict__ order, uint32_t npairs, AdCounters* __restrict__ counters,
-           unsigned char* arena, CellLayout Lo, uint32_t capL, uint32_t capR,
+           unsigned char* arena, CellLayout Lo, unsigned char* aux, AuxLayout Ax, uint32_t capL, uint32_t capR,
            uint64_t kmax, uint32_t nlayers_ref, double amax, CtaBest* __restrict__ cta_best,
            uint32_t* __restrict__ ovf_list, unsigned int* __restrict__ ovf_count, uint32_t round)
 {
@@ -827,7 +1030,7 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
     CellCtx C;
     uint32_t cur = 0;                      // each CTA owns slices 2*blockIdx and 2*blockIdx+1: the one being written and the
                                            // one that holds the CTA's best candidate so far (kept for the witness walk)
-    setup_ctx(C, smem_raw, capL, capR, arena, Lo, 2 * blockIdx.x + cur, amax, &s_next, &s_bump, &s_overflow);
+    setup_ctx(C, smem_raw, capL, capR, arena, Lo, 2 * blockIdx.x + cur, aux, Ax, amax, &s_next, &s_bump, &s_overflow);
     const uint32_t lane = threadIdx.x & 31;
     unsigned long long my_cells = 0; unsigned int my_states = 0;
     if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0;
@@ -869,8 +1072,6 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
         {   // keep this candidate's records: continue in the other slice
             cur ^= 1u;
             C.sl = carve_cells(arena, Lo, 2 * blockIdx.x + cur);
-            C.spill = C.sl.spill + (size_t) (threadIdx.x >> 5) * Lo.spill_cap;
-            C.spill_pred = C.sl.spill_pred + (size_t) (threadIdx.x >> 5) * Lo.spill_cap;
         }
     }
     for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(kFull, my_cells, o); my_states += __shfl_xor_sync(kFull, my_states, o); }
@@ -1072,7 +1273,7 @@ constexpr uint64_t kDefaultPoolRecords = 4u << 20;    // first-try pool per slic
 
 // Launches the cell kernel over `count` queue entries (order == nullptr: pairs[0..count)) with `slices` CTAs.
 int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uint32_t count, uint32_t slices, const CellLayout& Lo,
-                    uint32_t capL, uint32_t capR, uint64_t kmax, uint32_t nlayers_ref, double amax, AdSmall* sm,
+                    const AuxLayout& Ax, uint32_t capL, uint32_t capR, uint64_t kmax, uint32_t nlayers_ref, double amax, AdSmall* sm,
                     CtaBest* d_cta_best, uint32_t* d_ovf_list, unsigned int* d_ovf_count, uint32_t round, uint32_t nw)
 {
     const size_t smem = cells_smem_bytes(capL, capR, nw);
@@ -1084,11 +1285,11 @@ int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uin
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
     if (nw == (uint32_t) kCellWarps)
         k_ad_cells<kCellThreads, 16 / kCellWarps><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
-                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, capL, capR, kmax, nlayers_ref,
+                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, c->ad_aux.as<unsigned char>(), Ax, capL, capR, kmax, nlayers_ref,
                                                           amax, d_cta_best, d_ovf_list, d_ovf_count, round);
     else
         k_ad_cells<kMaxCellWarps * 32, 1><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
-                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, capL, capR, kmax, nlayers_ref,
+                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, c->ad_aux.as<unsigned char>(), Ax, capL, capR, kmax, nlayers_ref,
                                                           amax, d_cta_best, d_ovf_list, d_ovf_count, round);
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());
@@ -1117,9 +1318,9 @@ int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, uint32_t nw, int* p
 int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint32_t nqueued, const PairStats& ps, uint64_t kmax, uint32_t nlayers_ref, double amax,
                  AdSmall* sm, CellLayout* used_layout, uint32_t* last_round)
 {
-    const uint32_t max_src = ps.max_nl + ps.max_nr;
     if (ps.max_dirs >= 0xffffffffull) { c->err = "area+diameter path: candidate too large for 32-bit directory offsets"; return ADK_ERR_NOMEM; }
-    const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, max_src, 0).off_v + 8192;
+    const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, 0).off_v + 8192;
+    const AuxLayout Ax = aux_layout(ps.max_nl, ps.max_nr);
     // Warps per candidate.  Plenty of candidates per CTA: 4 warps each, 4 CTAs per SM (best throughput).  Few, heavy ones
     // (a shard of a multi-GPU solve, the re-run of a winner): the longest candidate is the critical path, so wider CTAs
     // take fewer candidates at a time and finish each one sooner.  Both sides are estimated in the same cost proxy.
@@ -1138,12 +1339,13 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
             const double speed = (double) w / kCellWarps * eff[v];       // of one CTA, relative to a 4-warp CTA
             const double ctas = (double) std::min<uint64_t>(nqueued, (uint64_t) c->sm_count * (uint64_t) o);
             const double t = std::max((double) ps.cost_sum / (ctas * speed), (double) ps.cost_max / speed);
-            const char* force = getenv("ADK_FORCE_CELL_WARPS");            // experiments only
-            if (force ? (uint32_t) atoi(force) == w : (v == 0 || t < 0.9 * best_t)) { best_t = v == 0 ? t : std::min(t, best_t); nw = w; occ = o; }
-            if (getenv("ADK_DEBUG")) fprintf(stderr, "[adk] queue %u  w=%u occ=%d  load=%.3g critical=%.3g -> t=%.3g  (chosen w=%u)\n", nqueued, w, o,
+            if (c->force_cell_warps ? c->force_cell_warps == w : (v == 0 || t < 0.9 * best_t)) { best_t = v == 0 ? t : std::min(t, best_t); nw = w; occ = o; }
+            if (c->debug) fprintf(stderr, "[adk] queue %u  w=%u occ=%d  load=%.3g critical=%.3g -> t=%.3g  (chosen w=%u)\n", nqueued, w, o,
                                              (double) ps.cost_sum / (ctas * speed), (double) ps.cost_max / speed, t, nw);
         }
     }
+    // per-CTA tables + spill workspaces (not kept between candidates), sized for the widest lune of this queue
+    ADK_TRY(ensure(c, c->ad_aux, Ax.bytes * (size_t) std::min<uint64_t>(nqueued, (uint64_t) c->sm_count * (uint64_t) occ)));
     ADK_TRY(ensure(c, c->ad_ovf, sizeof(uint32_t) * 2 * (size_t) nqueued + 64));
     uint32_t* d_ovf[2] = {c->ad_ovf.as<uint32_t>(), c->ad_ovf.as<uint32_t>() + nqueued};
     const uint32_t* d_order = d_order0;
@@ -1160,14 +1362,14 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
         if (round > 0) slices = std::min<uint64_t>(slices, std::max<uint64_t>(1, budget / (2 * want_bytes)));   // fewer, larger slices
         slices = std::max<uint64_t>(1, std::min<uint64_t>(slices, budget / (2 * min_bytes)));
         size_t slice_bytes = (size_t) std::min<uint64_t>(budget / (2 * slices), want_bytes) & ~(size_t) 255;
-        const CellLayout Lo = cell_layout(ps.max_cells, ps.max_dirs, max_src, slice_bytes);
+        const CellLayout Lo = cell_layout(ps.max_cells, ps.max_dirs, slice_bytes);
         if (round > 0 && Lo.cap <= prev_cap)
         {   // the overflowing candidate already had everything the budget allows
             c->err = "area+diameter path: one candidate's record pool exceeds the memory budget"; return ADK_ERR_NOMEM;
         }
         ADK_TRY(ensure(c, c->arena, slice_bytes * 2 * (size_t) slices));
         ADK_TRY(ensure(c, c->ad_cta, sizeof(CtaBest) * slices));
-        ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
+        ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, Ax, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
                                 c->ad_cta.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round, nw));
         k_ad_reduce<<<1, 32, 0, c->stream>>>(c->ad_cta.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
         ++c->launches;

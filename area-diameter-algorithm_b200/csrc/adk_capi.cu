@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -26,7 +27,7 @@ void release_idle(Ctx* c, const DevBuf* keep)
     if (keep == &c->arena) { drop(c->scratch5); drop(c->scratch4); drop(c->scratch2); drop(c->scratch1); }
     else if (c->arena.p)
     {
-        drop(c->arena);
+        drop(c->arena); drop(c->ad_aux);
         c->ad_keep_valid = false;
         c->ad_V = c->ad_Q = 0; c->ad_L = 0; c->ad_slices = 0; c->ad_slice_bytes = 0;
     }
@@ -119,6 +120,8 @@ int adk_create(adk_ctx** out_ctx, int device)
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->budget = (uint64_t) (free_b * 0.75);
     else c->budget = 8ull << 30;
+    c->debug = getenv("ADK_DEBUG") != nullptr;
+    if (const char* f = getenv("ADK_FORCE_CELL_WARPS")) c->force_cell_warps = (uint32_t) atoi(f);
     *out_ctx = h;
     return ADK_OK;
 }
@@ -131,7 +134,7 @@ void adk_destroy(adk_ctx* h)
     if (c->stream) cudaStreamSynchronize(c->stream);
     adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
                            &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
-                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta};
+                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux};
     for (adk::DevBuf* b : bufs) adk::free_buf(*b);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->ev0) cudaEventDestroy(c->ev0);

@@ -29,6 +29,8 @@ struct Ctx
     uint64_t launches = 0;         // kernels launched by the current call
     uint64_t total_launches = 0;   // ... by all earlier calls
     bool own_stream = true;
+    bool debug = false;            // ADK_DEBUG, read once in adk_create
+    uint32_t force_cell_warps = 0; // ADK_FORCE_CELL_WARPS (experiments only), read once in adk_create
 
     // point set currently resident
     uint32_t n = 0;
@@ -46,6 +48,7 @@ struct Ctx
     DevBuf scratch0, scratch1, scratch2, scratch3, scratch4, scratch5, scratch6;
     DevBuf arena;                  // AD per-CTA slices (directories + layer vectors)
     DevBuf ad_order, ad_ovf, ad_cta;   // AD: processing order, overflow lists, per-CTA bests
+    DevBuf ad_aux;                 // AD: per-CTA order / suffix-start tables and spill workspaces
     uint64_t ad_V = 0, ad_Q = 0;   // per-slice capacities the arena was initialised for (grow-only)
     uint32_t ad_L = 0, ad_slices = 0;
     size_t ad_slice_bytes = 0;

@@ -69,3 +69,32 @@ def src(loc):
 print(f"# total warp instructions {ti}, stall samples {ts}")
 for loc, (inst, samp) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:top]:
     print(f"{100 * samp / ts:5.1f}% samples {100 * inst / ti:5.1f}% inst  {loc[0] if loc else '?'}:{loc[1] if loc else 0}  {src(loc)}")
+
+# per-phase totals: a phase starts at a "// ---- " marker or at a function definition in the source file
+import bisect
+phase_marks = {}
+def phase_of(loc):
+    if loc is None:
+        return "?"
+    f, l = loc
+    if f not in phase_marks:
+        marks = []
+        for d in ("area-diameter-algorithm_b200/csrc",):
+            pth = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), d, f)
+            if os.path.exists(pth):
+                for i, ln in enumerate(open(pth).read().splitlines(), 1):
+                    t = ln.strip()
+                    if t.startswith("// ---- ") or re.match(r"^(template <.*>\s*)?(__device__|__global__|__host__)", t):
+                        marks.append((i, t[:70]))
+        phase_marks[f] = marks
+    marks = phase_marks[f]
+    k = bisect.bisect_right([m[0] for m in marks], l) - 1
+    return f"{f}:{marks[k][0]} {marks[k][1]}" if k >= 0 else f
+pagg = collections.defaultdict(lambda: [0, 0])
+for loc, (inst, samp) in agg.items():
+    ph = phase_of(loc)
+    pagg[ph][0] += inst
+    pagg[ph][1] += samp
+print("# by phase")
+for ph, (inst, samp) in sorted(pagg.items(), key=lambda kv: -kv[1][1])[:25]:
+    print(f"{100 * samp / ts:5.1f}% samples {100 * inst / ti:5.1f}% inst  {ph}")
