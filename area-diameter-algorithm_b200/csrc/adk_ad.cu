@@ -37,7 +37,7 @@ struct PairStats
     unsigned int max_nl, max_nr, max_lim;
     unsigned int pad;
     unsigned long long max_cells;   // max over queued candidates of nl * nr                      (cells of the head grid)
-    unsigned long long max_dirs;    // max over queued candidates of nl * nr * (nl + nr - 2) / 2   (directory entries)
+    unsigned long long max_dirs;    // max over queued candidates of nl * nr * (nl + nr - 2)       (directory words)
     unsigned long long cost_sum, cost_max;   // sum / max over queued candidates of the cost proxy nl * nr * (nl + nr)
     unsigned int hist[kCostBuckets];    // queued candidates per cost bucket (heaviest candidates are started first)
     unsigned int cursor[kCostBuckets];
@@ -89,7 +89,7 @@ __device__ __forceinline__ void queue_pair(PairRec* __restrict__ pairs, PairStat
     pairs[slot] = PairRec{i, j, nl, nr};
     const unsigned long long cells = (unsigned long long) nl * nr;
     atomicMax(&stats->max_nl, nl); atomicMax(&stats->max_nr, nr); atomicMax(&stats->max_lim, lim);
-    atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2) / 2);
+    atomicMax(&stats->max_cells, cells); atomicMax(&stats->max_dirs, cells * (nl + nr - 2));
     atomicAdd(&stats->hist[cost_bucket(nl, nr)], 1u);
     const unsigned long long cost = cells * (nl + nr);
     atomicAdd(&stats->cost_sum, cost); atomicMax(&stats->cost_max, cost);
@@ -332,41 +332,60 @@ constexpr int kDstCap = 128;                     // destinations per pass with t
 constexpr uint32_t kFB = 0xffffu;                // suffix start "none": the destination takes the explicit path for that group
 constexpr uint32_t kNil = 0xffffu;
 
-// Layer vector of one (cell, destination): areas of layers kmin .. kmin+len-1 at vpool[off ..], +inf where unreached.
-struct DirEnt { uint32_t off; uint16_t kmin, len; };
+// Layer vector of one (cell, destination): areas of layers kmin .. kmin+len-1 at vpool[off ..], +inf where unreached; nfin of
+// them are finite (the states the reference holds for this pending edge: the cell-update and entry counters).  One 64-bit
+// directory word: off (28 bits) | kmin (12) | len (12) | nfin (12); layers < 4096 = ADK_MAX_POINTS, pools <= 2^28 records.
+struct DirEnt { uint32_t off; uint32_t kmin, len, nfin; };
+__device__ __forceinline__ unsigned long long dir_pack(const DirEnt& d)
+{
+    return (unsigned long long) d.off | ((unsigned long long) d.kmin << 28) | ((unsigned long long) d.len << 40) | ((unsigned long long) d.nfin << 52);
+}
+__device__ __forceinline__ DirEnt dir_unpack(unsigned long long w)
+{
+    DirEnt d; d.off = (uint32_t) (w & 0xfffffffull); d.kmin = (uint32_t) (w >> 28) & 0xfffu; d.len = (uint32_t) (w >> 40) & 0xfffu; d.nfin = (uint32_t) (w >> 52);
+    return d;
+}
+constexpr uint32_t kMaxPoolRecords = (1u << 28) - 32u;
 // One live source edge of a cell, in two records: what the transition tests read (first vertex of the edge, pseudo-distance
 // of the other chain's head from the edge's line, :222 / :295) and what the sweeps read.  ceff = points added by the edge's
 // fan triangle (:188-190, with the extra collinear term of a layer-0 seed); pos = position in the sorted order of ALL s < head.
 struct SrcGeo { double refd, psx, psy; };
 struct SrcVal { double tri; uint32_t off; uint16_t len, kmin, ceff, pos; };
-static_assert(sizeof(SrcGeo) == 24 && sizeof(SrcVal) == 24 && sizeof(DirEnt) == 8, "record layouts");
+// Per chain edge (s -> h): area and enclosed points of its fan triangle (:188-190 / :261-263), once per candidate.
+struct EdgeRec { double tri; uint16_t c, cx; uint32_t pad; };
+static_assert(sizeof(SrcGeo) == 24 && sizeof(SrcVal) == 24 && sizeof(EdgeRec) == 16, "record layouts");
 template <bool SPILL> struct LoType { typedef uint8_t type; };      // suffix starts / list links: bytes while a group has <= kGrp sources
 template <> struct LoType<true> { typedef uint16_t type; };
 
 // Per-CTA slice of the arena (two per CTA: the one being written and the one holding the CTA's best candidate so far).
+//   dir   PRODUCER-major: cell (a,b) owns the W = nl+nr-2 words at (a*nr+b)*W; word d belongs to its destination d.  A cell
+//         writes all its words with coalesced stores; a consumer reads only the words of its LIVE sources.
+//   live  CONSUMER-major bitmaps: cell (a,b) owns WB = ceil(nr/32)+ceil(nl/32) words; bit u of the first part = the RIGHT
+//         edge at sorted position u around R[b] carries states, second part = the same for the LEFT edges around L[a].
+//         Producers set the bits (atomicOr) of their non-empty destinations; empty ones cost the consumer nothing.
 struct CellSlice
 {
-    unsigned char* alive;     // nl*nr flags: cell wrote its directory ([a][b])
-    unsigned char* aliveT;    // the same flags transposed ([b][a]): a column's flags are contiguous for the gather
-    DirEnt* dir;              // directory entries at fixed positions (dir_right / dir_left)
-    uint16_t* nfin;           // per directory entry: number of finite layers (for the cell-update counter)
-    double* vpool;            // layer vectors
+    unsigned char* alive;         // nl*nr flags: cell wrote its directory words (read by the witness walk)
+    unsigned long long* dir;
+    uint32_t* live;
+    double* vpool;                // layer vectors
 };
 
-struct CellLayout { size_t off_aliveT, off_dir, off_nfin, off_v, bytes; uint32_t cap, pad; };
+struct CellLayout { size_t off_dir, off_live, off_v, bytes; uint32_t cap, pad; };
 
-__host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, size_t slice_bytes)
+__host__ __device__ inline uint32_t live_words(uint32_t nl, uint32_t nr) { return (nr + 31) / 32 + (nl + 31) / 32; }
+
+__host__ __device__ inline CellLayout cell_layout(unsigned long long max_cells, unsigned long long max_dirs, uint32_t max_nl, uint32_t max_nr, size_t slice_bytes)
 {
     CellLayout Lo;
     auto up = [](size_t v) { return (v + 255) & ~(size_t) 255; };
     size_t o = up((size_t) max_cells);
-    Lo.off_aliveT = o; o = up(o + (size_t) max_cells);
-    Lo.off_dir = o; o = up(o + sizeof(DirEnt) * (size_t) max_dirs);
-    Lo.off_nfin = o; o = up(o + sizeof(uint16_t) * (size_t) max_dirs);
+    Lo.off_dir = o; o = up(o + sizeof(unsigned long long) * (size_t) max_dirs);
+    Lo.off_live = o; o = up(o + sizeof(uint32_t) * (size_t) max_cells * live_words(max_nl, max_nr));
     Lo.off_v = o;
     const size_t rest = slice_bytes > o + 4096 ? slice_bytes - o - 4096 : 0;
     const size_t cap = rest / sizeof(double);
-    Lo.cap = (uint32_t) (cap > 0xfffffff0ull ? 0xfffffff0ull : cap) & ~31u;
+    Lo.cap = (uint32_t) (cap > kMaxPoolRecords ? kMaxPoolRecords : cap) & ~31u;
     Lo.bytes = slice_bytes; Lo.pad = 0;
     return Lo;
 }
@@ -376,18 +395,18 @@ __device__ __forceinline__ CellSlice carve_cells(unsigned char* arena, const Cel
     unsigned char* base = arena + (size_t) cta * Lo.bytes;
     CellSlice s;
     s.alive = base;
-    s.aliveT = base + Lo.off_aliveT;
-    s.dir = reinterpret_cast<DirEnt*>(base + Lo.off_dir);
-    s.nfin = reinterpret_cast<uint16_t*>(base + Lo.off_nfin);
+    s.dir = reinterpret_cast<unsigned long long*>(base + Lo.off_dir);
+    s.live = reinterpret_cast<uint32_t*>(base + Lo.off_live);
     s.vpool = reinterpret_cast<double*>(base + Lo.off_v);
     return s;
 }
 
-// Per-CTA auxiliary region (not kept between candidates): the per-candidate order / suffix-start tables and one spill
-// workspace per warp for the cells that outgrow the shared-memory workspace.
-//   sigR[b(b-1)/2 + r] = index s < b at sorted position r around R[b]          (sigL: the same around L[a])
-//   stayR[b*nr + i]    = first sorted position whose edge R[s]->R[b] may continue to R[i] (npot = none, kFB = not a suffix)
-struct AuxLayout { size_t off_sigL, off_stayR, off_stayL, off_spill, spill_bytes, bytes; uint32_t grp_cap, dst_cap; };
+// Per-CTA auxiliary region (not kept between candidates): the per-candidate chain tables and one spill workspace per warp
+// for the cells that outgrow the shared-memory workspace.  With tri(h) = h(h-1)/2:
+//   sigR[tri(b) + r]  = index s < b at sorted position r around R[b]; invR[tri(b) + s] = r          (sigL, invL: around L[a])
+//   edgeR[tri(b) + s] = fan triangle of the edge R[s]->R[b]
+//   stayR[b*nr + i]   = first sorted position whose edge R[s]->R[b] may continue to R[i] (b = none, kFB = not a suffix)
+struct AuxLayout { size_t off_sig[2], off_inv[2], off_edge[2], off_stay[2], off_spill, spill_bytes, bytes; uint32_t grp_cap, dst_cap; };
 
 // workspace of one warp: [suffix table: grp rows x 32 layers][sources: 2 groups x grp x 2 records][loR, loL, next: dst entries][heads: grp+1 x u32]
 __host__ __device__ inline size_t warp_ws_bytes(uint32_t grp, uint32_t dst, uint32_t lo_bytes)
@@ -400,28 +419,21 @@ __host__ __device__ inline AuxLayout aux_layout(uint32_t max_nl, uint32_t max_nr
 {
     AuxLayout A;
     auto up = [](size_t v) { return (v + 255) & ~(size_t) 255; };
-    size_t o = up(sizeof(uint16_t) * ((size_t) max_nr * max_nr / 2 + 1));
-    A.off_sigL = o; o = up(o + sizeof(uint16_t) * ((size_t) max_nl * max_nl / 2 + 1));
-    A.off_stayR = o; o = up(o + sizeof(uint16_t) * (size_t) max_nr * max_nr);
-    A.off_stayL = o; o = up(o + sizeof(uint16_t) * (size_t) max_nl * max_nl);
+    size_t o = 0;
+    for (int ch = 0; ch < 2; ++ch)
+    {
+        const size_t nc = ch ? max_nl : max_nr, tri = nc * nc / 2 + 1;
+        A.off_sig[ch] = o; o = up(o + sizeof(uint16_t) * tri);
+        A.off_inv[ch] = o; o = up(o + sizeof(uint16_t) * tri);
+        A.off_edge[ch] = o; o = up(o + sizeof(EdgeRec) * tri);
+        A.off_stay[ch] = o; o = up(o + sizeof(uint16_t) * nc * nc);
+    }
     A.off_spill = o;
     A.grp_cap = max_nl > max_nr ? max_nl : max_nr;
     A.dst_cap = (max_nl + max_nr + 3) & ~3u;
     A.spill_bytes = up(warp_ws_bytes(A.grp_cap, A.dst_cap, 2));
     A.bytes = up(o + A.spill_bytes * kMaxCellWarps);
     return A;
-}
-
-// Directory position of the state vector "pending edge s -> e on one chain, head h on the other chain".  Consumer-major:
-// cell (a,b) reads RIGHT(a; s->b), s = 0..b-1, and LEFT(b; s->a), s = 0..a-1, as two contiguous runs (the producing cells
-// scatter their entries instead; stores do not stall a warp, the gather's loads do).
-__device__ __forceinline__ uint32_t dir_right(uint32_t h, uint32_t e, uint32_t s, uint32_t nr)
-{
-    return h * (nr * (nr - 1) / 2) + e * (e - 1) / 2 + s;
-}
-__device__ __forceinline__ uint32_t dir_left(uint32_t h, uint32_t e, uint32_t s, uint32_t nl, uint32_t nr)
-{
-    return nl * (nr * (nr - 1) / 2) + h * (nl * (nl - 1) / 2) + e * (e - 1) / 2 + s;
 }
 
 struct CellCtx
@@ -434,7 +446,8 @@ struct CellCtx
     CellSlice sl;
     uint32_t cap;
     // per-candidate tables (global, per CTA)
-    uint16_t* sigR; uint16_t* sigL; uint16_t* stayR; uint16_t* stayL;
+    uint16_t* sig[2]; uint16_t* inv[2]; uint16_t* stay[2]; EdgeRec* edge[2];      // [0] = right chain, [1] = left chain
+    uint32_t W, WR, WB;           // directory words per cell; bitmap words of the RIGHT part / of a cell
     // warp-private workspaces: shared memory (kGrp / kDstCap) and the global spill (spill_grp / spill_dst)
     unsigned char* wsmem;
     unsigned char* wspill;
@@ -462,21 +475,34 @@ __device__ __forceinline__ double pseudo_angle(double fx, double fy, double sgn,
     return u >= 0.0 ? r : (v >= 0.0 ? 2.0 - r : -2.0 - r);
 }
 
-// Builds, for one chain of the candidate, the sorted orders and the "stay" suffix starts.  All warps of the CTA take part
-// (heads dealt round robin); `keys` is the calling warp's scratch (>= n doubles).
-__device__ __noinline__ void build_chain_tables(const CellCtx& C, bool left, double* keys, uint32_t lane, uint32_t warp, uint32_t nw)
+// Builds, for one chain of the candidate, the sorted orders, the fan triangles of its edges and the "stay" suffix starts.
+// All warps of the CTA take part (heads dealt round robin); `keys` is the calling warp's scratch (>= n doubles).
+__device__ __noinline__ void build_chain_tables(const CellCtx& C, const Tables& T, bool left, double* keys, uint32_t lane, uint32_t warp, uint32_t nw)
 {
     const LuneSmem& S = C.S;
     const uint32_t nc = left ? C.nl : C.nr;
     const double* X = left ? S.Lx : S.Rx; const double* Y = left ? S.Ly : S.Ry;
-    uint16_t* sig = left ? C.sigL : C.sigR; uint16_t* stay = left ? C.stayL : C.stayR;
+    const int32_t* I = left ? S.Lidx : S.Ridx;
+    uint16_t* sig = C.sig[left]; uint16_t* inv = C.inv[left]; uint16_t* stay = C.stay[left]; EdgeRec* edge = C.edge[left];
     const double fx = C.Ex - C.Sx, fy = C.Ey - C.Sy, sgn = left ? -1.0 : 1.0;
-    const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;          // second "stay" test: the chain's own fan apex (:201, :274)
+    const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;          // the chain's own fan apex (:188, :201 / :261, :274)
+    const int ap = left ? C.Ep : C.Sp;
     for (uint32_t h = 1 + warp; h < nc; h += nw)
     {
         const double hx = X[h], hy = Y[h];
+        const int hidx = I[h];
         uint16_t* sg = sig + h * (h - 1) / 2;
-        for (uint32_t s = lane; s < h; s += 32) keys[s] = pseudo_angle(fx, fy, sgn, hx, hy, X[s], Y[s]);
+        for (uint32_t s = lane; s < h; s += 32)
+        {
+            const double psx = X[s], psy = Y[s];
+            keys[s] = pseudo_angle(fx, fy, sgn, hx, hy, psx, psy);
+            EdgeRec e;
+            e.tri = fabs(signed_area(apx, apy, psx, psy, hx, hy));                                        // :188 / :261
+            e.c = (uint16_t) (1u + (uint32_t) tri_count_ad(T, false, I[s], psx, psy, hidx, hx, hy, ap, apx, apy));
+            e.cx = (uint16_t) T.C(I[s], ap);                                                              // extra term of a layer-0 seed (:33-36)
+            e.pad = 0;
+            edge[h * (h - 1) / 2 + s] = e;
+        }
         __syncwarp();
         for (uint32_t s = lane; s < h; s += 32)
         {
@@ -485,6 +511,7 @@ __device__ __noinline__ void build_chain_tables(const CellCtx& C, bool left, dou
 #pragma unroll 1
             for (uint32_t t = 0; t < h; ++t) { const double kt = keys[t]; r += (kt < ks || (kt == ks && t < s)) ? 1u : 0u; }
             sg[r] = (uint16_t) s;
+            inv[h * (h - 1) / 2 + s] = (uint16_t) r;
         }
         __syncwarp();
         for (uint32_t i0 = h + 1; i0 < nc; i0 += 32)
@@ -565,21 +592,21 @@ __device__ __noinline__ double explicit_min(const CellCtx& C, bool left, uint32_
 // SPILL = false: the warp's workspace is in shared memory (at most kGrp sources per group); returns false, with nothing
 // written, when the cell does not fit.  SPILL = true: the same code over the warp's global workspace.
 template <bool SPILL>
-__device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, uint32_t a, uint32_t b, uint32_t lane,
+__device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint32_t b, uint32_t lane,
                                              uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
 {
     typedef typename LoType<SPILL>::type lo_t;
     constexpr uint32_t FB = SPILL ? 0xffffu : 0xffu;     // suffix start "not a suffix" / list end, in lo_t
-    const uint32_t nl = C.nl, nr = C.nr;
+    const uint32_t nl = C.nl, nr = C.nr, W = C.W;
     const LuneSmem& S = C.S;
     const double Lax = S.Lx[a], Lay = S.Ly[a], Rbx = S.Rx[b], Rby = S.Ry[b];
-    const int Laidx = S.Lidx[a], Rbidx = S.Ridx[b];
     const bool term_r = b == nr - 1, term_l = a == nl - 1;               // R[nr-1] = s, L[nl-1] = t   (:167-175)
     const bool dead = dist2(Lax, Lay, Rbx, Rby) > C.seg2;                // :183-186 / :256-259
     const uint32_t nDR = nr - 1 - b, nDL = nl - 1 - a, D = nDR + nDL;
     const uint32_t lt = (1u << lane) - 1u;
     const uint32_t dmax = min(C.lim, C.nlayers - 1);
     const double* __restrict__ vpool = C.sl.vpool;
+    const uint32_t cell = a * nr + b;
 
     unsigned char* wbase = SPILL ? C.wspill : C.wsmem;
     const uint32_t gcap = SPILL ? C.spill_grp : (uint32_t) kGrp;
@@ -592,53 +619,61 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
     lo_t* nxt = loLs + dcap;
     uint32_t* head = reinterpret_cast<uint32_t*>(nxt + dcap);
 
-    // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b),
-    //      each group in its sorted order (the compaction keeps it)
+    // ---- gather: the pending edges that reach this cell, RIGHT(a; s->b) from cell (a,s), LEFT(b; s->a) from cell (s,b).
+    //      The cell's bitmaps name the live ones by sorted position, so the compaction keeps each group in its sorted order.
+    //      Blocks of 32 positions, RIGHT group first; the directory words of the next non-empty block are requested before
+    //      the current one is worked on (L2 / HBM round trips; the geometry below hides them).
     uint32_t PR = 0, PL = 0;
     uint32_t klo = 0xffffffffu, khi = 0;
     unsigned long long cells_add = 0;
-#pragma unroll 1
-    for (int g = 0; g < 2; ++g)
     {
-        const bool left = g == 1;
-        const uint32_t npot = left ? a : b;
-        const uint16_t* sg = left ? C.sigL + a * (a - 1) / 2 : C.sigR + b * (b - 1) / 2;
-        const bool term = left ? term_l : term_r;
-        const double* GX = left ? S.Lx : S.Rx; const double* GY = left ? S.Ly : S.Ry;
-        const int32_t* GI = left ? S.Lidx : S.Ridx;
-        const double hx = left ? Lax : Rbx, hy = left ? Lay : Rby;
-        const int hidx = left ? Laidx : Rbidx;
-        const double apx = left ? C.Ex : C.Sx, apy = left ? C.Ey : C.Sy;      // fan apex of the edge's own chain
-        const int ap = left ? C.Ep : C.Sp;
-        const double ox = left ? Rbx : Lax, oy = left ? Rby : Lay;            // head of the other chain
-        const uint32_t obase = left ? gcap : 0u;
-        uint32_t P = 0;
-        // The directory reads of the NEXT block of 32 potential sources are issued before this block is worked on (and the
-        // sorted indices one block further ahead): they are L2 / HBM round trips, the geometry below hides them.
-        uint32_t s_n = lane < npot ? (uint32_t) sg[lane] : 0u, s_nn = 32 + lane < npot ? (uint32_t) sg[32 + lane] : 0u;
-        unsigned char al_n = 0; DirEnt dd_n; dd_n.off = 0; dd_n.kmin = 0; dd_n.len = 0; uint32_t nf_n = 0;
-        if (lane < npot)
+        const uint32_t* bmp = C.sl.live + (size_t) cell * C.WB;
+        const uint32_t WR = C.WR, WB = C.WB;
+        auto fetch = [&](uint32_t wi, uint32_t m, uint32_t& s, unsigned long long& w, EdgeRec& e)
         {
-            const uint32_t dix = left ? dir_left(b, a, s_n, nl, nr) : dir_right(a, b, s_n, nr);
-            al_n = left ? C.sl.aliveT[b * nl + s_n] : C.sl.alive[a * nr + s_n];
-            dd_n = C.sl.dir[dix]; nf_n = C.sl.nfin[dix];
-        }
-#pragma unroll 1
-        for (uint32_t u0 = 0; u0 < npot; u0 += 32)
-        {
-            const uint32_t u = u0 + lane;
-            const uint32_t s = s_n;
-            const unsigned char al = al_n; const DirEnt dd = dd_n; const uint32_t nfin_src = nf_n;
-            s_n = s_nn;
-            if (u + 32 < npot)
-            {   // the flag and the entry are loaded together: the entry of a cell that produced nothing is stale and ignored
-                const uint32_t dix = left ? dir_left(b, a, s_n, nl, nr) : dir_right(a, b, s_n, nr);
-                al_n = left ? C.sl.aliveT[b * nl + s_n] : C.sl.alive[a * nr + s_n];
-                dd_n = C.sl.dir[dix]; nf_n = C.sl.nfin[dix];
+            if ((m >> lane) & 1u)
+            {
+                const bool left = wi >= WR;
+                const uint32_t h = left ? a : b, u = (left ? wi - WR : wi) * 32 + lane;
+                s = C.sig[left][h * (h - 1) / 2 + u];
+                // RIGHT(a; s->b) is destination b-s-1 of cell (a,s); LEFT(b; s->a) is destination (nr-1-b) + a-s-1 of cell (s,b)
+                w = C.sl.dir[left ? (size_t) (s * nr + b) * W + (nr - 1 - b) + (a - s - 1) : (size_t) (a * nr + s) * W + (b - s - 1)];
+                e = C.edge[left][h * (h - 1) / 2 + s];
             }
-            s_nn = u + 64 < npot ? (uint32_t) sg[u + 64] : 0u;
-            bool live = u < npot && al && dd.len > 0;
-            const DirEnt de = dd;
+        };
+        uint32_t P = 0;
+        bool in_left = false;
+#pragma unroll 1
+        for (uint32_t w0 = 0; w0 < WB; w0 += 32)
+        {   // the cell's bitmap words in one load (the producers set the bits with L2 atomics: read them around L1)
+            const uint32_t bw = w0 + lane < WB ? __ldcg(bmp + w0 + lane) : 0u;
+            uint32_t nzm = __ballot_sync(kFull, bw != 0u);
+            uint32_t wi_n = 0, m_n = 0, s_n = 0; unsigned long long w_n = 0ull; EdgeRec e_n; e_n.tri = 0.0; e_n.c = 0; e_n.cx = 0; e_n.pad = 0;
+            bool have_n = nzm != 0u;
+            if (have_n)
+            {
+                const int z = __ffs((int) nzm) - 1; nzm &= nzm - 1u;
+                wi_n = w0 + (uint32_t) z; m_n = __shfl_sync(kFull, bw, z);
+                fetch(wi_n, m_n, s_n, w_n, e_n);
+            }
+#pragma unroll 1
+            while (have_n)
+            {
+                const uint32_t q = wi_n, m = m_n, s = s_n;
+                const unsigned long long w = w_n; const EdgeRec er = e_n;
+                have_n = nzm != 0u;
+                if (have_n)
+                {   // request the next non-empty block before this one is worked on
+                    const int z = __ffs((int) nzm) - 1; nzm &= nzm - 1u;
+                    wi_n = w0 + (uint32_t) z; m_n = __shfl_sync(kFull, bw, z);
+                    fetch(wi_n, m_n, s_n, w_n, e_n);
+                }
+                const uint32_t nbR = WR;
+            const bool left = q >= nbR;
+            if (left && !in_left) { in_left = true; PR = P; P = 0; }
+            const uint32_t u = (left ? q - nbR : q) * 32 + lane;
+            bool live = (m >> lane) & 1u;
+            const DirEnt de = dir_unpack(w);
             if (live)
             {   // pull the layer vector towards L1 while the geometry below is computed
                 const char* v0 = reinterpret_cast<const char*>(vpool + de.off);
@@ -647,8 +682,8 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
                 asm volatile("prefetch.global.L1 [%0];" ::"l"(v1));
                 if (v1 - v0 > 256) asm volatile("prefetch.global.L1 [%0];" ::"l"(v0 + 128));
             }
-            const uint32_t kmax = (uint32_t) de.kmin + de.len - 1;
-            if (live && term)
+            const uint32_t kmax = de.kmin + de.len - 1;
+            if (live && (left ? term_l : term_r))
             {   // terminal states only report (:167-175): the deepest layer of this edge is its best
                 if (kmax > 0)
                 {
@@ -659,19 +694,16 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
             }
             if (dead) live = false;
             SrcGeo rg; rg.refd = 0.0; rg.psx = 0.0; rg.psy = 0.0;
-            SrcVal rv; rv.tri = 0.0; rv.off = de.off; rv.len = de.len; rv.kmin = de.kmin; rv.ceff = 0; rv.pos = (uint16_t) u;
+            SrcVal rv; rv.tri = er.tri; rv.off = de.off; rv.len = (uint16_t) de.len; rv.kmin = (uint16_t) de.kmin; rv.ceff = 0; rv.pos = (uint16_t) u;
             if (live)
             {
-                const double psx = GX[s], psy = GY[s];
-                const int pidx = GI[s];
+                const double psx = left ? S.Lx[s] : S.Rx[s], psy = left ? S.Ly[s] : S.Ry[s];
                 rg.psx = psx; rg.psy = psy;
-                rv.tri = fabs(signed_area(apx, apy, psx, psy, hx, hy));               // :188 / :261
-                const uint32_t c = 1u + (uint32_t) tri_count_ad(T, false, pidx, psx, psy, hidx, hx, hy, ap, apx, apy);
-                const uint32_t ceff = c + (de.kmin == 0 ? (uint32_t) T.C(pidx, ap) : 0u);   // only the seeds sit on layer 0 (:33-36)
+                const uint32_t ceff = (uint32_t) er.c + (de.kmin == 0 ? (uint32_t) er.cx : 0u);   // only the seeds sit on layer 0 (:33-36)
                 rv.ceff = (uint16_t) ceff;
-                rg.refd = pseudo_dist(psx, psy, hx, hy, ox, oy);                      // :222 / :295
+                rg.refd = left ? pseudo_dist(psx, psy, Lax, Lay, Rbx, Rby) : pseudo_dist(psx, psy, Rbx, Rby, Lax, Lay);   // :222 / :295
                 // cell updates the reference performs for these states (:198,225,271,298), and the output layer range
-                uint32_t nvalid = nfin_src;
+                uint32_t nvalid = de.nfin;
                 if (kmax + ceff >= C.nlayers)
                 {
                     nvalid = 0;
@@ -688,15 +720,18 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
             const uint32_t at = P + __popc(lm & lt);
             P += __popc(lm);
             if (!SPILL && P > gcap) return false;          // does not fit in shared memory: nothing has been written yet
+            const uint32_t obase = left ? gcap : 0u;
             if (live) { geo[obase + at] = rg; val[obase + at] = rv; }
+            }
         }
-        if (left) PL = P; else PR = P;
+        if (in_left) PL = P; else PR = P;
     }
     my_cells += cells_add;
     if (PR + PL == 0 || D == 0) return true;
     klo = __reduce_min_sync(kFull, klo); khi = __reduce_max_sync(kFull, khi);
     __syncwarp();
     const uint32_t ntiles = (khi - klo + kBT) / kBT;
+    unsigned long long* mydir = C.sl.dir + (size_t) cell * W;           // this cell's directory words, one per destination
 
 #pragma unroll 1
     for (uint32_t dc0 = 0; dc0 < D; dc0 += dcap)
@@ -727,7 +762,7 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
                     if (P == 0) { }
                     else if (left != dR)
                     {   // stay: tabulated over ALL s < head (the tests do not depend on the other head); count the live sources before it
-                        const uint32_t lf = left ? C.stayL[a * nl + i] : C.stayR[b * nr + i];
+                        const uint32_t lf = left ? C.stay[1][a * nl + i] : C.stay[0][b * nr + i];
                         if (lf == kFB) lo = FB;
                         else
                         {   // lower bound of lf in the (ascending) sorted positions of the live sources
@@ -804,15 +839,11 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
                     if (loL < PL) v = fmin(v, tab[(size_t) loL * 32 + lane]);
                     if (loL == FB) v = fmin(v, explicit_min(C, true, dd, k, kact, a, b, geo + gcap, val + gcap, PL));
                     if (loR == FB) v = fmin(v, explicit_min(C, false, dd, k, kact, a, b, geo, val, PR));
-                    const bool dR = dd < nDR;
-                    const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
-                    const uint32_t dix = dR ? dir_right(a, i, b, nr) : dir_left(b, i, a, nl, nr);
                     // the destination's layer vector: first .. last finite layer, holes stay +inf.  A cell deeper than one tile
                     // is still swept once: the vector is given room up to the cell's last layer when its first finite layer
                     // shows up, later tiles append to it (the unused tail is never read).
-                    DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
-                    uint32_t nf = 0;
-                    if (t > 0) { de = C.sl.dir[dix]; nf = C.sl.nfin[dix]; }
+                    DirEnt de; de.off = 0; de.kmin = 0; de.len = 0; de.nfin = 0;
+                    if (t > 0) de = dir_unpack(mydir[dd]);
                     const uint32_t fm = __ballot_sync(kFull, v < INFINITY);
                     bool started = de.len > 0;
                     if (fm)
@@ -824,19 +855,20 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
                             uint32_t base = 0;
                             if (lane == 0) base = atomicAdd(C.bump, need);
                             base = __shfl_sync(kFull, base, 0);
-                            if ((unsigned long long) base + need <= C.cap) { started = true; de.off = base; de.kmin = (uint16_t) tfirst; }
+                            if ((unsigned long long) base + need <= C.cap) { started = true; de.off = base; de.kmin = tfirst; }
                             else if (lane == 0) *C.overflow = 1u;
                         }
-                        if (started) { de.len = (uint16_t) (tlast - de.kmin + 1); nf += __popc(fm); }
+                        if (started) { de.len = tlast - de.kmin + 1; de.nfin += __popc(fm); }
                     }
-                    if (started && kact && k >= de.kmin && (ntiles > 1 || k < (uint32_t) de.kmin + de.len))
+                    if (started && kact && k >= de.kmin && (ntiles > 1 || k < de.kmin + de.len))
                         C.sl.vpool[de.off + (k - de.kmin)] = v;
-                    if (lane == 0 && (t == 0 || fm)) { C.sl.dir[dix] = de; C.sl.nfin[dix] = (uint16_t) nf; }
+                    if (lane == 0 && (t == 0 || fm)) mydir[dd] = dir_pack(de);
                 }
             }
             __syncwarp();
         }
-        // ---- every destination gets its directory entry: the leader's record is shared by its peers
+        // ---- every destination gets its directory word (the leader's record is shared by its peers), and the consumer
+        //      cell of every non-empty one learns that the edge is live
 #pragma unroll 1
         for (uint32_t d0 = 0; d0 < nd; d0 += 32)
         {
@@ -848,33 +880,32 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, const Tables& T, 
             const uint32_t peers = __match_any_sync(kFull, key);
             const int leader = __ffs((int) peers) - 1;
             const bool empty = loR == PR && loL == PL;
-            const bool dR = dd < nDR;
-            const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
-            const uint32_t dix = have ? (dR ? dir_right(a, i, b, nr) : dir_left(b, i, a, nl, nr)) : 0u;
-            DirEnt de; de.off = 0; de.kmin = 0; de.len = 0;
-            uint32_t nf = 0;
-            if (have && !empty && leader == (int) lane) { de = C.sl.dir[dix]; nf = C.sl.nfin[dix]; }
-            const uint32_t off = __shfl_sync(kFull, de.off, leader);
-            const uint32_t kl = __shfl_sync(kFull, (uint32_t) de.kmin | ((uint32_t) de.len << 16), leader);
-            nf = __shfl_sync(kFull, nf, leader);
-            if (have && (empty || leader != (int) lane))
+            unsigned long long wv = 0ull;
+            if (have && !empty && leader == (int) lane) wv = mydir[dd];
+            wv = __shfl_sync(kFull, wv, leader);
+            if (have && (empty || leader != (int) lane)) mydir[dd] = empty ? 0ull : wv;
+            const uint32_t nf = (uint32_t) (wv >> 52), ln = (uint32_t) (wv >> 40) & 0xfffu;
+            if (have && !empty && ln)
             {
-                DirEnt w; w.off = empty ? 0u : off; w.kmin = (uint16_t) (empty ? 0u : (kl & 0xffffu)); w.len = (uint16_t) (empty ? 0u : (kl >> 16));
-                C.sl.dir[dix] = w;
-                C.sl.nfin[dix] = (uint16_t) (empty ? 0u : nf);
+                const bool dR = dd < nDR;
+                const uint32_t i = dR ? b + 1 + dd : a + 1 + (dd - nDR);
+                // consumer: cell (a,i) sees this edge R[b]->R[i] in its RIGHT part, cell (i,b) sees L[a]->L[i] in its LEFT part
+                const uint32_t pos = dR ? C.inv[0][i * (i - 1) / 2 + b] : C.inv[1][i * (i - 1) / 2 + a];
+                uint32_t* cw = C.sl.live + (size_t) (dR ? a * nr + i : i * nr + b) * C.WB + (dR ? 0u : C.WR) + (pos >> 5);
+                atomicOr(cw, 1u << (pos & 31u));
+                my_states += nf;
             }
-            my_states += (have && !empty) ? nf : 0u;
         }
         __syncwarp();
     }
-    if (lane == 0) { C.sl.alive[a * nr + b] = 1; C.sl.aliveT[b * nl + a] = 1; }
+    if (lane == 0) C.sl.alive[cell] = 1;
     return true;
 }
 
-__device__ __noinline__ void process_cell_spilled(const CellCtx& C, const Tables& T, uint32_t a, uint32_t b, uint32_t lane,
+__device__ __noinline__ void process_cell_spilled(const CellCtx& C, uint32_t a, uint32_t b, uint32_t lane,
                                                   uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
 {
-    process_cell<true>(C, T, a, b, lane, bk, bv, my_cells, my_states);
+    process_cell<true>(C, a, b, lane, bk, bv, my_cells, my_states);
 }
 
 struct CandResult { uint32_t kbest; uint32_t states; double area; };     // best terminal layer (0 = none) of one candidate
@@ -931,17 +962,28 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
     {
         const uint32_t nmax = nl > nr ? nl : nr;
         double* keys = nmax * sizeof(double) <= kWarpWsBytes ? reinterpret_cast<double*>(C.wsmem) : reinterpret_cast<double*>(C.wspill);
-        build_chain_tables(C, false, keys, lane, warp, nw);
-        build_chain_tables(C, true, keys, lane, warp, nw);
+        build_chain_tables(C, T, false, keys, lane, warp, nw);
+        build_chain_tables(C, T, true, keys, lane, warp, nw);
     }
-    // reset the slice: no cell has produced anything; cell (0,0) "produces" the layer-0 seeds (:149-160):
-    // RIGHT(0; 0->i) and LEFT(0; 0->i) all share one record (layer 0, area 0)
-    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) { C.sl.alive[t] = t == 0 ? 1 : 0; C.sl.aliveT[t] = t == 0 ? 1 : 0; }
+    // reset the slice: no cell has produced anything, no edge is live
+    C.W = nl + nr - 2; C.WR = (nr + 31) / 32; C.WB = live_words(nl, nr);
+    for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) C.sl.alive[t] = t == 0 ? 1 : 0;
+    {
+        const size_t nwords = (size_t) nl * nr * C.WB;                 // slices are 256-byte aligned and sized for the widest lune
+        uint4* z = reinterpret_cast<uint4*>(C.sl.live);
+        for (size_t t = threadIdx.x; t < (nwords + 3) / 4; t += blockDim.x) z[t] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
+    // cell (0,0) "produces" the layer-0 seeds (:149-160): RIGHT(0; 0->i) and LEFT(0; 0->i) all share one record (layer 0, area 0)
     const uint32_t D0 = (nr - 1) + (nl - 1);
     for (uint32_t t = threadIdx.x; t < D0; t += blockDim.x)
     {
-        const uint32_t dix = t < nr - 1 ? dir_right(0, t + 1, 0, nr) : dir_left(0, t - (nr - 1) + 1, 0, nl, nr);
-        DirEnt de; de.off = 0; de.kmin = 0; de.len = 1; C.sl.dir[dix] = de; C.sl.nfin[dix] = 1;
+        DirEnt de; de.off = 0; de.kmin = 0; de.len = 1; de.nfin = 1;
+        C.sl.dir[t] = dir_pack(de);
+        const bool dR = t < nr - 1;
+        const uint32_t i = dR ? t + 1 : t - (nr - 1) + 1;
+        const uint32_t pos = C.inv[dR ? 0 : 1][i * (i - 1) / 2];
+        atomicOr(C.sl.live + (size_t) (dR ? i : i * nr) * C.WB + (dR ? 0u : C.WR) + (pos >> 5), 1u << (pos & 31u));
     }
     for (uint32_t t = threadIdx.x; t < nl; t += blockDim.x) C.rowdone[t] = t == 0 ? 1u : 0u;
     for (uint32_t t = threadIdx.x; t < nr; t += blockDim.x) C.coldone[t] = t == 0 ? 1u : 0u;
@@ -969,8 +1011,8 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
         if (lane == 0) while (C.rowdone[a] < b || C.coldone[b] < a) __nanosleep(32);
         __syncwarp();
         __threadfence_block();
-        if (!process_cell<false>(C, T, a, b, lane, bk, bv, my_cells, my_states))
-            process_cell_spilled(C, T, a, b, lane, bk, bv, my_cells, my_states);
+        if (!process_cell<false>(C, a, b, lane, bk, bv, my_cells, my_states))
+            process_cell_spilled(C, a, b, lane, bk, bv, my_cells, my_states);
         __threadfence_block();
         __syncwarp();
         if (lane == 0) { C.rowdone[a] = b + 1; C.coldone[b] = a + 1; }
@@ -1002,8 +1044,11 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
     C.S = carve_cells_smem(smem_raw, capL, capR, nw, &done);
     C.wsmem = smem_raw + kWarpWsBytes * warp;
     unsigned char* ax = aux + (size_t) blockIdx.x * Ax.bytes;
-    C.sigR = reinterpret_cast<uint16_t*>(ax); C.sigL = reinterpret_cast<uint16_t*>(ax + Ax.off_sigL);
-    C.stayR = reinterpret_cast<uint16_t*>(ax + Ax.off_stayR); C.stayL = reinterpret_cast<uint16_t*>(ax + Ax.off_stayL);
+    for (int ch = 0; ch < 2; ++ch)
+    {
+        C.sig[ch] = reinterpret_cast<uint16_t*>(ax + Ax.off_sig[ch]); C.inv[ch] = reinterpret_cast<uint16_t*>(ax + Ax.off_inv[ch]);
+        C.stay[ch] = reinterpret_cast<uint16_t*>(ax + Ax.off_stay[ch]); C.edge[ch] = reinterpret_cast<EdgeRec*>(ax + Ax.off_edge[ch]);
+    }
     C.wspill = ax + Ax.off_spill + Ax.spill_bytes * warp;
     C.spill_grp = Ax.grp_cap; C.spill_dst = Ax.dst_cap;
     C.rowdone = done; C.coldone = done + capL;
@@ -1103,12 +1148,11 @@ struct AdHull { uint32_t len; uint32_t ok; uint32_t nl, nr; };
 // Area pattern of the reference state Entry{o, s, ss} on the given side at layer k, or +inf if it was never reached.
 __device__ unsigned long long state_value(const CellSlice& sl, uint32_t nl, uint32_t nr, bool right, uint32_t o, uint32_t s, uint32_t ss, uint32_t k)
 {
-    uint32_t pa, pb;
-    if (right) { pa = o; pb = s; }                                       // RIGHT(o; s->ss): produced by cell (o, s)
-    else { pa = s; pb = o; }                                             // LEFT (o; s->ss): produced by cell (s, o)
-    if (!sl.alive[pa * nr + pb]) return kInfBits;
-    const DirEnt de = sl.dir[right ? dir_right(o, ss, s, nr) : dir_left(o, ss, s, nl, nr)];
-    if (de.len == 0 || k < de.kmin || k >= (uint32_t) de.kmin + de.len) return kInfBits;
+    // RIGHT(o; s->ss) is destination ss-s-1 of cell (o, s); LEFT(o; s->ss) is destination (nr-1-o) + ss-s-1 of cell (s, o)
+    const uint32_t cell = right ? o * nr + s : s * nr + o;
+    if (!sl.alive[cell]) return kInfBits;
+    const DirEnt de = dir_unpack(sl.dir[(size_t) cell * (nl + nr - 2) + (right ? ss - s - 1 : (nr - 1 - o) + (ss - s - 1))]);
+    if (de.len == 0 || k < de.kmin || k >= de.kmin + de.len) return kInfBits;
     return area_bits(sl.vpool[de.off + (k - de.kmin)]);      // holes hold +inf = kInfBits
 }
 
@@ -1319,7 +1363,7 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
                  AdSmall* sm, CellLayout* used_layout, uint32_t* last_round)
 {
     if (ps.max_dirs >= 0xffffffffull) { c->err = "area+diameter path: candidate too large for 32-bit directory offsets"; return ADK_ERR_NOMEM; }
-    const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, 0).off_v + 8192;
+    const size_t fixed = cell_layout(ps.max_cells, ps.max_dirs, ps.max_nl, ps.max_nr, 0).off_v + 8192;
     const AuxLayout Ax = aux_layout(ps.max_nl, ps.max_nr);
     // Warps per candidate.  Plenty of candidates per CTA: 4 warps each, 4 CTAs per SM (best throughput).  Few, heavy ones
     // (a shard of a multi-GPU solve, the re-run of a winner): the longest candidate is the critical path, so wider CTAs
@@ -1362,7 +1406,7 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
         if (round > 0) slices = std::min<uint64_t>(slices, std::max<uint64_t>(1, budget / (2 * want_bytes)));   // fewer, larger slices
         slices = std::max<uint64_t>(1, std::min<uint64_t>(slices, budget / (2 * min_bytes)));
         size_t slice_bytes = (size_t) std::min<uint64_t>(budget / (2 * slices), want_bytes) & ~(size_t) 255;
-        const CellLayout Lo = cell_layout(ps.max_cells, ps.max_dirs, slice_bytes);
+        const CellLayout Lo = cell_layout(ps.max_cells, ps.max_dirs, ps.max_nl, ps.max_nr, slice_bytes);
         if (round > 0 && Lo.cap <= prev_cap)
         {   // the overflowing candidate already had everything the budget allows
             c->err = "area+diameter path: one candidate's record pool exceeds the memory budget"; return ADK_ERR_NOMEM;
@@ -1516,7 +1560,7 @@ int ad_finish(Ctx* c, uint64_t kmax, double amax, double dmax, const adk_partial
         if (kopt > lim) { c->err = "ad_finish: witness count exceeds the candidate's capacity"; return ADK_ERR_ARG; }
         PairStats ps; std::memset(&ps, 0, sizeof(ps));
         ps.nqueued = 1; ps.max_nl = pr.nl; ps.max_nr = pr.nr; ps.max_lim = lim;
-        ps.max_cells = (unsigned long long) pr.nl * pr.nr; ps.max_dirs = ps.max_cells * (pr.nl + pr.nr - 2) / 2;
+        ps.max_cells = (unsigned long long) pr.nl * pr.nr; ps.max_dirs = ps.max_cells * (pr.nl + pr.nr - 2);
         ps.cost_sum = ps.cost_max = ps.max_cells * (pr.nl + pr.nr);
         ADK_CUDA(c, cudaMemcpyAsync(d_pair, &pr, sizeof(pr), cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(&sm->counters, 0, sizeof(AdCounters), c->stream));
