@@ -8,7 +8,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libadk.so")
+LIB_PATH = os.environ.get("ADK_LIB_PATH") or os.path.join(_HERE, "libadk.so")     # ADK_LIB_PATH: development builds of the same library
 
 ADK_OK, ADK_ERR_CUDA, ADK_ERR_ARG, ADK_ERR_NOMEM = 0, 1, 2, 3
 FLAG_RECONSTRUCT, FLAG_COUNTERS = 1, 2
@@ -53,13 +53,15 @@ class AdkInstance(ctypes.Structure):
 ALGO_AREA, ALGO_AREA_DIAMETER = 0, 1
 
 EXPORTS = [
-    "adk_create", "adk_destroy", "adk_last_error", "adk_set_memory_budget", "adk_set_stream", "adk_launch_count",
+    "adk_create", "adk_destroy", "adk_last_error", "adk_set_memory_budget", "adk_set_stream", "adk_launch_count", "adk_set_reuse",
     "adk_area_finish_dev", "adk_area_diameter_finish_dev",
     "adk_solve_area", "adk_solve_area_diameter",
     "adk_area_partial", "adk_area_finish", "adk_area_diameter_partial", "adk_area_diameter_finish",
     "adk_merge", "adk_area_partial_dev", "adk_area_diameter_partial_dev",
     "adk_batch_assign", "adk_solve_batch",
     "adk_count_tables", "adk_points_in_triangle", "adk_cw_order", "adk_slope_order", "adk_lune_lists",
+    "adk_multi_create", "adk_multi_destroy", "adk_multi_last_error", "adk_multi_device_count", "adk_multi_set_reuse",
+    "adk_multi_solve_area", "adk_multi_solve_area_diameter", "adk_multi_last_stats",
 ]
 
 
@@ -113,6 +115,97 @@ def batch_assign(point_sets, nshards, algo=ALGO_AREA_DIAMETER):
     return [int(owner[i]) for i in range(len(point_sets))]
 
 
+class AdkMultiStats(ctypes.Structure):
+    _fields_ = [
+        ("ndev", ctypes.c_uint32), ("pad", ctypes.c_uint32),
+        ("cells_nominal", ctypes.c_uint64), ("cells_executed", ctypes.c_uint64), ("states", ctypes.c_uint64),
+        ("pairs", ctypes.c_uint64), ("launches", ctypes.c_uint64),
+        ("max_kernel_ms", ctypes.c_double), ("max_dp_ms", ctypes.c_double), ("sum_dp_ms", ctypes.c_double),
+        ("max_exchange_ms", ctypes.c_double),
+    ]
+
+
+class MultiSolver:
+    """Several GPUs of one box behind one handle (adk_multi_*): one blocking call per solve; the shards, the NCCL all-gather of
+    the 32-byte partials and the witness broadcast all happen inside libadk.so."""
+
+    def __init__(self, devices=None):
+        self.lib = load_library()
+        L = self.lib
+        L.adk_multi_last_error.restype = ctypes.c_char_p
+        L.adk_multi_last_error.argtypes = [ctypes.c_void_p]
+        L.adk_multi_create.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p, ctypes.c_int]
+        L.adk_multi_destroy.argtypes = [ctypes.c_void_p]
+        self.h = ctypes.c_void_p()
+        if devices is None:
+            rc = L.adk_multi_create(ctypes.byref(self.h), None, 0)
+        else:
+            arr = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+            rc = L.adk_multi_create(ctypes.byref(self.h), ctypes.cast(arr, ctypes.c_void_p), len(devices))
+        if rc != ADK_OK:
+            msg = L.adk_multi_last_error(None)
+            raise AdkError(f"adk_multi_create failed ({rc}): {msg.decode() if msg else ''}")
+        L.adk_multi_device_count.argtypes = [ctypes.c_void_p]
+        self.ndev = int(L.adk_multi_device_count(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.adk_multi_destroy(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != ADK_OK:
+            msg = self.lib.adk_multi_last_error(self.h)
+            raise AdkError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def set_reuse(self, enabled):
+        self.lib.adk_multi_set_reuse.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        self._check(self.lib.adk_multi_set_reuse(self.h, ctypes.c_int(1 if enabled else 0)), "adk_multi_set_reuse")
+
+    def last_stats(self):
+        st = AdkMultiStats()
+        self.lib.adk_multi_last_stats.argtypes = [ctypes.c_void_p, ctypes.POINTER(AdkMultiStats)]
+        self._check(self.lib.adk_multi_last_stats(self.h, ctypes.byref(st)), "adk_multi_last_stats")
+        return {k: (float(getattr(st, k)) if k.endswith("_ms") else int(getattr(st, k))) for k, _ in AdkMultiStats._fields_ if k != "pad"}
+
+    def solve_area_host(self, px, py, n, kmax, amax, reconstruct=True, counters=False):
+        """Host pointers (e.g. pinned torch tensors' data_ptr()) in, dict out."""
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n, 1))()
+        flags = (FLAG_RECONSTRUCT if reconstruct else 0) | (FLAG_COUNTERS if counters else 0)
+        self.lib.adk_multi_solve_area.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64,
+                                                  ctypes.c_double, ctypes.c_uint32, ctypes.POINTER(AdkResult), ctypes.c_void_p]
+        self._check(self.lib.adk_multi_solve_area(self.h, ctypes.c_void_p(px), ctypes.c_void_p(py), n, _k(kmax), float(amax), flags,
+                                                  ctypes.byref(res), ctypes.cast(hull, ctypes.c_void_p)), "adk_multi_solve_area")
+        return Solver._pack(res, hull)
+
+    def solve_area_diameter_host(self, px, py, n, kmax, amax, dmax, reconstruct=True, counters=False):
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n, 1))()
+        flags = (FLAG_RECONSTRUCT if reconstruct else 0) | (FLAG_COUNTERS if counters else 0)
+        self.lib.adk_multi_solve_area_diameter.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64,
+                                                           ctypes.c_double, ctypes.c_double, ctypes.c_uint32, ctypes.POINTER(AdkResult),
+                                                           ctypes.c_void_p]
+        self._check(self.lib.adk_multi_solve_area_diameter(self.h, ctypes.c_void_p(px), ctypes.c_void_p(py), n, _k(kmax), float(amax),
+                                                           float(dmax), flags, ctypes.byref(res), ctypes.cast(hull, ctypes.c_void_p)),
+                    "adk_multi_solve_area_diameter")
+        return Solver._pack(res, hull)
+
+    def solve_area(self, x, y, kmax=None, amax=float("inf"), reconstruct=True, counters=False):
+        ax, ay = _darr(x), _darr(y)
+        return self.solve_area_host(ctypes.addressof(ax), ctypes.addressof(ay), len(x), kmax, amax, reconstruct, counters)
+
+    def solve_area_diameter(self, x, y, kmax=None, amax=float("inf"), dmax=float("inf"), reconstruct=True, counters=False):
+        ax, ay = _darr(x), _darr(y)
+        return self.solve_area_diameter_host(ctypes.addressof(ax), ctypes.addressof(ay), len(x), kmax, amax, dmax, reconstruct, counters)
+
+
 class Solver:
     """One context = one GPU.  Mirrors the reference's call shapes; returns plain dicts."""
 
@@ -155,6 +248,11 @@ class Solver:
         self.lib.adk_launch_count.restype = ctypes.c_uint64
         self.lib.adk_launch_count.argtypes = [ctypes.c_void_p]
         return int(self.lib.adk_launch_count(self.ctx))
+
+    def set_reuse(self, enabled):
+        """False: every solve recomputes the count tables and angular orders (what the reference does on every call)."""
+        self.lib.adk_set_reuse.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        self._check(self.lib.adk_set_reuse(self.ctx, ctypes.c_int(1 if enabled else 0)), "adk_set_reuse")
 
     def set_memory_budget(self, nbytes):
         self._check(self.lib.adk_set_memory_budget(self.ctx, ctypes.c_uint64(int(nbytes))), "adk_set_memory_budget")

@@ -552,6 +552,14 @@ __device__ __forceinline__ bool pair_ok(bool left, bool dR, double psx, double p
     return pseudo_dist(psx, psy, hx, hy, qx, qy) <= refd;                   // switch chains (:226-227, :299-300)
 }
 
+// Minimum of two areas.  Areas are non-negative doubles or +inf, whose order is the order of their bit patterns as unsigned
+// integers: an integer minimum issues at full rate, DMNMX at a fifth of the FP64 rate (tools/issue_peaks.cu: dmin_per_s).
+__device__ __forceinline__ double amin(double a, double b)
+{
+    const unsigned long long x = (unsigned long long) __double_as_longlong(a), y = (unsigned long long) __double_as_longlong(b);
+    return __longlong_as_double((long long) (x < y ? x : y));
+}
+
 // S_p[k]: what source r contributes to layer k of any destination it may continue to (:188-195, :203): area + triangle.
 __device__ __forceinline__ double src_value(const SrcVal& r, const double* __restrict__ vpool, uint32_t k, bool kact, double amax)
 {
@@ -583,7 +591,7 @@ __device__ __noinline__ double explicit_min(const CellCtx& C, bool left, uint32_
     for (uint32_t p = 0; p < P; ++p)
     {
         const SrcGeo g = sg[p];
-        if (pair_ok(left, dR, g.psx, g.psy, hx, hy, g.refd, qx, qy)) v = fmin(v, src_value(sv[p], C.sl.vpool, k, kact, C.amax));
+        if (pair_ok(left, dR, g.psx, g.psy, hx, hy, g.refd, qx, qy)) v = amin(v, src_value(sv[p], C.sl.vpool, k, kact, C.amax));
     }
     return v;
 }
@@ -814,7 +822,7 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
 #pragma unroll 2
                 for (int r = (int) PL - 1; r >= 0; --r)
                 {
-                    v = fmin(v, src_value(vl[r], vpool, k, kact, C.amax));
+                    v = amin(v, src_value(vl[r], vpool, k, kact, C.amax));
                     tab[(size_t) r * 32 + lane] = v;
                 }
             }
@@ -828,7 +836,7 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
                 {
                     const double cur = pend;
                     if (r > 0) pend = src_value(val[r - 1], vpool, k, kact, C.amax);
-                    vR = fmin(vR, cur);
+                    vR = amin(vR, cur);
                 }
 #pragma unroll 1
                 for (uint32_t dl = head[r]; dl != FB; dl = nxt[dl])
@@ -836,9 +844,9 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
                     const uint32_t dd = dc0 + dl;
                     const uint32_t loR = loRs[dl], loL = loLs[dl];
                     double v = vR;
-                    if (loL < PL) v = fmin(v, tab[(size_t) loL * 32 + lane]);
-                    if (loL == FB) v = fmin(v, explicit_min(C, true, dd, k, kact, a, b, geo + gcap, val + gcap, PL));
-                    if (loR == FB) v = fmin(v, explicit_min(C, false, dd, k, kact, a, b, geo, val, PR));
+                    if (loL < PL) v = amin(v, tab[(size_t) loL * 32 + lane]);
+                    if (loL == FB) v = amin(v, explicit_min(C, true, dd, k, kact, a, b, geo + gcap, val + gcap, PL));
+                    if (loR == FB) v = amin(v, explicit_min(C, false, dd, k, kact, a, b, geo, val, PR));
                     // the destination's layer vector: first .. last finite layer, holes stay +inf.  A cell deeper than one tile
                     // is still swept once: the vector is given room up to the cell's last layer when its first finite layer
                     // shows up, later tiles append to it (the unused tail is never read).

@@ -108,7 +108,8 @@ int adk_create(adk_ctx** out_ctx, int device)
     }
     if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) return ADK_ERR_CUDA; }
     if (device >= ndev) return ADK_ERR_ARG;
-    if (cudaSetDevice(device) != cudaSuccess) return ADK_ERR_CUDA;
+    adk::DeviceGuard guard(device);
+    if (!guard.ok) return ADK_ERR_CUDA;
     adk_ctx* h = new (std::nothrow) adk_ctx();
     if (!h) return ADK_ERR_NOMEM;
     Ctx* c = &h->c;
@@ -116,7 +117,13 @@ int adk_create(adk_ctx** out_ctx, int device)
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete h; return ADK_ERR_CUDA; }
-    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1); cudaEventCreate(&c->ev2); cudaEventCreate(&c->ev3);
+    if (cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess || cudaEventCreate(&c->ev2) != cudaSuccess ||
+        cudaEventCreate(&c->ev3) != cudaSuccess)
+    {
+        g_create_error = "cudaEventCreate failed";
+        adk_destroy(h);
+        return ADK_ERR_CUDA;
+    }
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) c->budget = (uint64_t) (free_b * 0.75);
     else c->budget = 8ull << 30;
@@ -130,7 +137,7 @@ void adk_destroy(adk_ctx* h)
 {
     if (!h) return;
     Ctx* c = &h->c;
-    cudaSetDevice(c->device);
+    adk::DeviceGuard guard(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
                            &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
@@ -158,7 +165,8 @@ int adk_set_stream(adk_ctx* h, void* cuda_stream)
 {
     if (!h) return ADK_ERR_ARG;
     Ctx* c = &h->c;
-    if (cudaSetDevice(c->device) != cudaSuccess) return ADK_ERR_CUDA;
+    adk::DeviceGuard guard(c->device);
+    if (!guard.ok) return ADK_ERR_CUDA;
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->stream && c->own_stream) cudaStreamDestroy(c->stream);
     c->stream = static_cast<cudaStream_t>(cuda_stream);
@@ -166,10 +174,17 @@ int adk_set_stream(adk_ctx* h, void* cuda_stream)
     return ADK_OK;
 }
 
+int adk_set_reuse(adk_ctx* h, int enabled)
+{
+    if (!h) return ADK_ERR_ARG;
+    h->c.reuse = enabled != 0;
+    return ADK_OK;
+}
+
 uint64_t adk_launch_count(const adk_ctx* h) { return h ? h->c.total_launches + h->c.launches : 0; }
 
 #define ADK_ENTER(h) if (!(h)) return ADK_ERR_ARG; Ctx* c = &(h)->c; c->err.clear(); c->total_launches += c->launches; c->launches = 0; \
-    if (cudaSetDevice(c->device) != cudaSuccess) return ADK_ERR_CUDA
+    adk::DeviceGuard guard__(c->device); if (!guard__.ok) return ADK_ERR_CUDA
 
 static void fill_result_from(adk_result* out, const adk_stats& st, uint32_t flags)
 {
@@ -184,7 +199,7 @@ int adk_area_partial(adk_ctx* h, const double* x, const double* y, uint32_t n, u
 {
     ADK_ENTER(h);
     if (!out) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, true));
     return adk::area_partial(c, kmax, amax, shard, nshards, out, stats);
 }
 
@@ -193,7 +208,7 @@ int adk_area_partial_dev(adk_ctx* h, const double* d_x, const double* d_y, uint3
 {
     ADK_ENTER(h);
     if (!out) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true, true));
     return adk::area_partial(c, kmax, amax, shard, nshards, out, stats);
 }
 
@@ -205,7 +220,7 @@ int adk_area_finish(adk_ctx* h, const double* x, const double* y, uint32_t n, ui
     std::memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     return adk::area_finish(c, kmax, amax, best, flags, out, hull);
 }
 
@@ -217,7 +232,7 @@ int adk_area_finish_dev(adk_ctx* h, const double* d_x, const double* d_y, uint32
     std::memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
-    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true, false));
     return adk::area_finish(c, kmax, amax, best, flags, out, hull);
 }
 
@@ -229,7 +244,7 @@ int adk_solve_area(adk_ctx* h, const double* x, const double* y, uint32_t n, uin
     std::memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
     if (n < 3 || kmax < 3) return ADK_OK;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, true));
     adk_partial part; adk_stats st;
     ADK_TRY(adk::area_partial(c, kmax, amax, 0, 1, &part, &st));
     const uint64_t launches = c->launches;
@@ -250,7 +265,7 @@ int adk_area_diameter_partial(adk_ctx* h, const double* x, const double* y, uint
 {
     ADK_ENTER(h);
     if (!out) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, true));
     return adk::ad_partial(c, kmax, amax, dmax, shard, nshards, out, stats);
 }
 
@@ -259,7 +274,7 @@ int adk_area_diameter_partial_dev(adk_ctx* h, const double* d_x, const double* d
 {
     ADK_ENTER(h);
     if (!out) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true, true));
     return adk::ad_partial(c, kmax, amax, dmax, shard, nshards, out, stats);
 }
 
@@ -271,9 +286,10 @@ int adk_area_diameter_finish(adk_ctx* h, const double* x, const double* y, uint3
     std::memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     const int rc = adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
-    out->entries_required = -1;      // ad_finish carries the winner's state count there for adk_solve_area_diameter only
+    out->states = out->entries_required > 0 ? (uint64_t) out->entries_required : 0;      // the winning candidate's states (its DP re-run in the reference, :529-535)
+    out->entries_required = -1;
     return rc;
 }
 
@@ -285,9 +301,10 @@ int adk_area_diameter_finish_dev(adk_ctx* h, const double* d_x, const double* d_
     std::memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
     if (!best->found) return ADK_OK;
-    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true));
+    ADK_TRY(adk::upload_points(c, d_x, d_y, n, true, false));
     const int rc = adk::ad_finish(c, kmax, amax, dmax, best, flags, out, hull);
-    out->entries_required = -1;      // ad_finish carries the winner's state count there for adk_solve_area_diameter only
+    out->states = out->entries_required > 0 ? (uint64_t) out->entries_required : 0;      // the winning candidate's states (its DP re-run in the reference, :529-535)
+    out->entries_required = -1;
     return rc;
 }
 
@@ -299,7 +316,7 @@ int adk_solve_area_diameter(adk_ctx* h, const double* x, const double* y, uint32
     std::memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
     if (std::min<uint64_t>(n, kmax) < 3) return ADK_OK;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, true));
     adk_partial part; adk_stats st;
     ADK_TRY(adk::ad_partial(c, kmax, amax, dmax, 0, 1, &part, &st));
     ADK_TRY(adk::ad_finish(c, kmax, amax, dmax, &part, flags, out, hull));
@@ -378,7 +395,7 @@ int adk_count_tables(adk_ctx* h, const double* x, const double* y, uint32_t n, i
 {
     ADK_ENTER(h);
     if (!below || !coll || !right_below) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     ADK_TRY(adk::run_count_tables(c));
     ADK_CUDA(c, cudaMemcpyAsync(below, c->below.p, sizeof(int32_t) * (size_t) n * n, cudaMemcpyDeviceToHost, c->stream));
     ADK_CUDA(c, cudaMemcpyAsync(coll, c->coll.p, sizeof(int32_t) * (size_t) n * n, cudaMemcpyDeviceToHost, c->stream));
@@ -392,7 +409,7 @@ int adk_points_in_triangle(adk_ctx* h, const double* x, const double* y, uint32_
     ADK_ENTER(h);
     if (!triples || !out) return ADK_ERR_ARG;
     for (uint32_t t = 0; t < 3 * m; ++t) if (triples[t] >= n) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     return adk::run_pit_query(c, triples, m, out);
 }
 
@@ -400,7 +417,7 @@ int adk_cw_order(adk_ctx* h, const double* x, const double* y, uint32_t n, int32
 {
     ADK_ENTER(h);
     if (!order || n < 2) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     ADK_TRY(adk::run_angles_and_orders(c, true, false));
     ADK_CUDA(c, cudaMemcpyAsync(order, c->cw.p, sizeof(int32_t) * (size_t) n * (n - 1), cudaMemcpyDeviceToHost, c->stream));
     ADK_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -411,7 +428,7 @@ int adk_slope_order(adk_ctx* h, const double* x, const double* y, uint32_t n, ui
 {
     ADK_ENTER(h);
     if (!out || !len) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     return adk::area_slope_order(c, i, j, out, len);
 }
 
@@ -420,7 +437,7 @@ int adk_lune_lists(adk_ctx* h, const double* x, const double* y, uint32_t n, uin
 {
     ADK_ENTER(h);
     if (!left || !right || !nleft || !nright || s >= n || t >= n || s == t) return ADK_ERR_ARG;
-    ADK_TRY(adk::upload_points(c, x, y, n, false));
+    ADK_TRY(adk::upload_points(c, x, y, n, false, false));
     return adk::ad_lune_lists(c, s, t, left, nleft, right, nright);
 }
 

@@ -58,8 +58,11 @@ struct Ctx
     uint64_t ad_keep_kmax = 0, ad_keep_states = 0;
     double ad_keep_amax = 0.0;
     unsigned char ad_keep_layout[96] = {0};   // the CellLayout the slice was written with
-    uint64_t points_hash = 0;      // content hash of the resident point set (same points => precompute products stay valid)
+    std::vector<double> host_xy;   // host copy of the resident point set (x then y): same points => precompute products stay valid
+    const double* dev_x = nullptr; // device pointers the resident set was last taken from (a finish after its own partial
+    const double* dev_y = nullptr; //   is recognised without reading anything back)
     bool points_valid = false;
+    bool reuse = true;             // keep the precompute products across solves of the same point set (adk_set_reuse)
     DevBuf small;                  // small result records
     void* h_pinned = nullptr;      // pinned host staging
     size_t h_pinned_cap = 0;
@@ -70,11 +73,19 @@ int ensure(Ctx* c, DevBuf& b, size_t bytes);
 int ensure_pinned(Ctx* c, size_t bytes);
 void release_idle(Ctx* c, const DevBuf* keep);
 uint64_t workspace_budget(Ctx* c, const DevBuf& target);
+// Makes the context's device current for the duration of an entry point and restores the caller's device afterwards.
+struct DeviceGuard
+{
+    int prev = -1, dev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int d) : dev(d) { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; ok = prev == d || cudaSetDevice(d) == cudaSuccess; }
+    ~DeviceGuard() { if (prev >= 0 && prev != dev) cudaSetDevice(prev); }
+};
 #define ADK_CUDA(ctx, call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return adk::set_cuda_error((ctx), e__, #call); } while (0)
 #define ADK_TRY(call) do { int r__ = (call); if (r__ != ADK_OK) return r__; } while (0)
 
 // ---- precompute (adk_precompute.cu) ----
-int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool device_ptrs);
+int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool device_ptrs, bool new_solve);
 int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi);
 int run_count_tables(Ctx* c);
 int run_yorder(Ctx* c);

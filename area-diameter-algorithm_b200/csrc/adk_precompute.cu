@@ -13,6 +13,8 @@
 #include "adk_internal.h"
 #include "adk_device.cuh"
 
+#include <cstring>
+
 namespace adk
 {
 
@@ -154,43 +156,61 @@ __global__ void k_pit_query(const double* __restrict__ x, const double* __restri
 
 // ------------------------------------------------------------------------------------------------ host side
 
-static uint64_t hash_points(const double* x, const double* y, uint32_t n)
-{   // FNV-1a over the raw coordinate bytes
-    uint64_t h = 1469598103934665603ull ^ n;
-    const unsigned char* px = reinterpret_cast<const unsigned char*>(x);
-    const unsigned char* py = reinterpret_cast<const unsigned char*>(y);
-    for (size_t i = 0; i < sizeof(double) * (size_t) n; ++i) { h ^= px[i]; h *= 1099511628211ull; }
-    for (size_t i = 0; i < sizeof(double) * (size_t) n; ++i) { h ^= py[i]; h *= 1099511628211ull; }
-    return h;
-}
-
-int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool device_ptrs)
+// new_solve: the call starts a solve (a whole solve or a partial), as opposed to the finish that follows a partial.
+int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool device_ptrs, bool new_solve)
 {
     if (!x || !y || n == 0 || n > ADK_MAX_POINTS) { c->err = "bad point arrays / n out of range"; return ADK_ERR_ARG; }
-    // The same point set as the resident one (a diameter sweep, a partial followed by its finish) keeps the count
-    // tables, the orders and the retained winning candidate: compare a content hash before invalidating anything.
-    const double* hx = x; const double* hy = y;
-    if (device_ptrs)
+    // The same point set as the resident one (a diameter sweep, a partial followed by its finish) keeps the count tables,
+    // the orders and the retained winning candidate.  "Same" is decided on the coordinates themselves (a host copy of the
+    // resident set), never on a hash.  With reuse switched off (adk_set_reuse) every new solve recomputes everything, as the
+    // reference does (Eppstein.cpp:143-155, AntipodalOptimized.cpp:469-481); a finish still finds its partial's products.
+    bool same = false;
+    if (c->points_valid && c->n == n && (c->reuse || !new_solve))
     {
-        ADK_TRY(ensure_pinned(c, sizeof(double) * 2 * (size_t) n));
-        double* h = static_cast<double*>(c->h_pinned);
-        ADK_CUDA(c, cudaMemcpyAsync(h, x, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
-        ADK_CUDA(c, cudaMemcpyAsync(h + n, y, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
-        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
-        hx = h; hy = h + n;
+        if (device_ptrs && !new_solve && x == c->dev_x && y == c->dev_y) same = true;     // the buffers the partial just read
+        else
+        {
+            const double* hx = x; const double* hy = y;
+            if (device_ptrs)
+            {
+                ADK_TRY(ensure_pinned(c, sizeof(double) * 2 * (size_t) n));
+                double* h = static_cast<double*>(c->h_pinned);
+                ADK_CUDA(c, cudaMemcpyAsync(h, x, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+                ADK_CUDA(c, cudaMemcpyAsync(h + n, y, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+                ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+                hx = h; hy = h + n;
+            }
+            same = c->host_xy.size() == 2 * (size_t) n && std::memcmp(c->host_xy.data(), hx, sizeof(double) * n) == 0 &&
+                   std::memcmp(c->host_xy.data() + n, hy, sizeof(double) * n) == 0;
+        }
     }
-    const uint64_t hash = hash_points(hx, hy, n);
-    const bool same = c->points_valid && c->n == n && c->points_hash == hash;
     ADK_TRY(ensure(c, c->x, sizeof(double) * n));
     ADK_TRY(ensure(c, c->y, sizeof(double) * n));
     const cudaMemcpyKind kind = device_ptrs ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     ADK_CUDA(c, cudaMemcpyAsync(c->x.p, x, sizeof(double) * n, kind, c->stream));
     ADK_CUDA(c, cudaMemcpyAsync(c->y.p, y, sizeof(double) * n, kind, c->stream));
+    c->dev_x = device_ptrs ? x : nullptr; c->dev_y = device_ptrs ? y : nullptr;
     if (same) return ADK_OK;       // the copy is still made (the caller's buffer is the input of this call); products stay valid
     c->n = n;
-    c->points_hash = hash; c->points_valid = true;
     c->have_cw = c->have_modpi = c->have_tables = c->have_yorder = false;
     c->ad_keep_valid = false;
+    c->points_valid = true;
+    if (!device_ptrs)
+    {
+        c->host_xy.resize(2 * (size_t) n);
+        std::memcpy(c->host_xy.data(), x, sizeof(double) * n);
+        std::memcpy(c->host_xy.data() + n, y, sizeof(double) * n);
+    }
+    else if (c->reuse)
+    {   // keep the host copy current for later comparisons (one small read-back per NEW device-resident point set)
+        ADK_TRY(ensure_pinned(c, sizeof(double) * 2 * (size_t) n));
+        double* h = static_cast<double*>(c->h_pinned);
+        ADK_CUDA(c, cudaMemcpyAsync(h, c->x.p, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaMemcpyAsync(h + n, c->y.p, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->host_xy.assign(h, h + 2 * (size_t) n);
+    }
+    else c->host_xy.clear();
     return ADK_OK;
 }
 
@@ -204,6 +224,7 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi)
         ADK_TRY(ensure(c, c->d2c, sizeof(double) * (size_t) n * n));
         k_angles<<<n, 256, 0, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(), c->d2c.as<double>());
         ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
     }
     const size_t smem = sizeof(double) * 4 * n;
     if (need_cw && !c->have_cw)
@@ -213,6 +234,7 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi)
         k_order_rank<0><<<n, 256, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(),
                                                      c->d2c.as<double>(), c->cw.as<int32_t>(), nullptr);
         ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
         c->have_cw = true;
     }
     if (need_modpi && !c->have_modpi)
@@ -223,6 +245,7 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi)
         k_order_rank<1><<<n, 256, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(),
                                                      c->d2c.as<double>(), c->modpi.as<int32_t>(), c->rank.as<uint16_t>());
         ++c->launches;
+        ADK_CUDA(c, cudaGetLastError());
         c->have_modpi = true;
     }
     ADK_CUDA(c, cudaGetLastError());

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <stdexcept>
 #include <string>
 
@@ -13,12 +14,52 @@ namespace MT
 {
 namespace
 {
+// ADK_DEVICES: "all", a count ("8") or a list ("0,1,2,3"); read once.
+std::vector<int> env_devices()
+{
+    std::vector<int> out;
+    const char* e = std::getenv("ADK_DEVICES");
+    if (!e || !*e) return out;
+    const std::string v(e);
+    if (v == "all") { out.push_back(-1); return out; }       // resolved by adk_multi_create
+    size_t at = 0;
+    while (at < v.size())
+    {
+        size_t end = v.find(',', at);
+        if (end == std::string::npos) end = v.size();
+        if (end > at) out.push_back(std::atoi(v.substr(at, end - at).c_str()));
+        at = end + 1;
+    }
+    if (out.size() == 1 && v.find(',') == std::string::npos && out[0] > 1)
+    {   // a bare count
+        const int cnt = out[0];
+        out.clear();
+        for (int i = 0; i < cnt; ++i) out.push_back(i);
+    }
+    return out;
+}
+
 struct ThreadSolver
 {
     adk_ctx* ctx = nullptr;
+    adk_multi* multi = nullptr;
     int device = -1;
+    std::vector<int> devices = env_devices();
     B200::LastSolveStats last{0, 0, 0, 0, 0.0, 0.0};
-    ~ThreadSolver() { if (ctx) adk_destroy(ctx); }
+    ~ThreadSolver() { if (ctx) adk_destroy(ctx); if (multi) adk_multi_destroy(multi); }
+    bool several() const { return devices.size() > 1 || (devices.size() == 1 && devices[0] == -1); }
+    adk_multi* get_multi()
+    {
+        if (!multi)
+        {
+            const bool all = devices.size() == 1 && devices[0] == -1;
+            const int rc = adk_multi_create(&multi, all ? nullptr : devices.data(), all ? 0 : (int) devices.size());
+            if (rc != ADK_OK)
+                throw std::runtime_error(std::string("adk: cannot open the configured devices (") + adk_multi_last_error(nullptr) +
+                                         "); this build has no CPU fallback");
+        }
+        return multi;
+    }
     adk_ctx* get()
     {
         if (!ctx)
@@ -88,6 +129,14 @@ std::optional<ConvexArea> run_area_diameter(const std::vector<CM::Point2>& pts, 
     adk_result r;
     std::vector<uint32_t> hull(pts.size() + 4);
     const uint32_t flags = (reconstruct ? ADK_FLAG_RECONSTRUCT : 0u) | (info ? ADK_FLAG_COUNTERS : 0u);
+    if (s.several())
+    {
+        adk_multi* m = s.get_multi();
+        if (adk_multi_solve_area_diameter(m, soa.x.data(), soa.y.data(), (uint32_t) pts.size(), narrow_count(k), (double) a, (double) d,
+                                          flags, &r, hull.data()) != ADK_OK)
+            throw std::runtime_error(std::string("adk_multi_solve_area_diameter failed: ") + adk_multi_last_error(m));
+        return widen(r, hull, info, s);
+    }
     check(adk_solve_area_diameter(s.get(), soa.x.data(), soa.y.data(), (uint32_t) pts.size(), narrow_count(k), (double) a, (double) d,
                                   flags, &r, hull.data()), s.ctx, "adk_solve_area_diameter");
     return widen(r, hull, info, s);
@@ -204,16 +253,34 @@ void SortPointsClockWiseAroundPoint(const CM::Point2& ref, std::vector<CM::Point
 
 std::optional<Diameter> ComputeDiameter(const std::vector<CM::Point2>& hull)
 {
-    // Standalone helper of the public surface; the solvers compute their diameter on the device.
+    // Standalone helper of the public surface (Utils.cpp:318-338): the farthest antipodal pair, first one met wins on ties, as
+    // in the reference; the solvers compute their diameter on the device with the same walk.
     if (hull.size() < 2) return std::nullopt;
     size_t ba = 0, bb = 0; long double best = 0;
-    for (size_t a = 0; a < hull.size(); ++a)
-        for (size_t b = a + 1; b < hull.size(); ++b)
-        {
+    if (hull.size() == 2) { ba = 0; bb = 0; }      // the reference's walk needs three vertices; it reports the first vertex twice
+    else
+        ForAllAntipodalPairs(hull, [&](const size_t a, const size_t b) {
             const long double d = CM::Distance2(hull[a], hull[b]);
             if (d > best) { best = d; ba = a; bb = b; }
-        }
+        });
     return Diameter{hull[ba].myIndex, hull[bb].myIndex};
+}
+
+int PointsInTriangle(const CM::Point2& p0, const CM::Point2& p1, const CM::Point2& p2, const PointsInTriangleCache& cache)
+{
+    // Inclusion-exclusion over the "points below the segment" counts (Utils.cpp:251-293): order the corners by (x, y), then the
+    // middle one lies either below or above the long side.
+    if (CM::AreCollinear(p0, p1, p2)) return 0;
+    const CM::Point2* v[3] = {&p0, &p1, &p2};
+    std::sort(v, v + 3, [](const CM::Point2* a, const CM::Point2* b) { return CM::SortPointsHorizontally(*a, *b); });
+    const size_t l = v[0]->myIndex, m = v[1]->myIndex, r = v[2]->myIndex;
+    const auto& B = cache.myPointsBelowSegmentCount;
+    const auto& C = cache.myCollinearPointsCount;
+    if (v[0]->myX == v[1]->myX) return B[m][r] - B[l][r] - C[l][r];                 // the two left corners share their x
+    if (v[1]->myX == v[2]->myX) return B[l][r] - B[l][m] - C[l][m];                 // the two right corners share their x
+    if (CM::Orientation(*v[2], *v[0], *v[1]) == CM::ORIENTATION::LEFT_TURN)         // the middle corner is below the long side
+        return B[l][r] - B[l][m] - B[m][r] - C[l][m] - C[m][r] - cache.myPointsRightBelowCount[m] - 1;
+    return B[l][m] + B[m][r] + cache.myPointsRightBelowCount[m] - B[l][r] - C[l][r];
 }
 
 // ------------------------------------------------------------------------------------------------- path A
@@ -226,6 +293,13 @@ std::optional<ConvexArea> EppsteinAlgorithmWithBenchmarkInfo(const std::vector<C
     adk_result r;
     std::vector<uint32_t> hull(pts.size() + 4);
     const uint32_t flags = (reconstruct ? ADK_FLAG_RECONSTRUCT : 0u) | (info ? ADK_FLAG_COUNTERS : 0u);
+    if (s.several())
+    {
+        adk_multi* m = s.get_multi();
+        if (adk_multi_solve_area(m, soa.x.data(), soa.y.data(), (uint32_t) pts.size(), narrow_count(k), (double) a, flags, &r, hull.data()) != ADK_OK)
+            throw std::runtime_error(std::string("adk_multi_solve_area failed: ") + adk_multi_last_error(m));
+        return widen(r, hull, info, s);
+    }
     check(adk_solve_area(s.get(), soa.x.data(), soa.y.data(), (uint32_t) pts.size(), narrow_count(k), (double) a, flags, &r, hull.data()),
           s.ctx, "adk_solve_area");
     return widen(r, hull, info, s);
@@ -272,7 +346,16 @@ void SetDevice(int ordinal)
 {
     ThreadSolver& s = solver();
     if (s.ctx && s.device != ordinal) { adk_destroy(s.ctx); s.ctx = nullptr; }
+    if (s.multi) { adk_multi_destroy(s.multi); s.multi = nullptr; }
     s.device = ordinal;
+    s.devices.clear();
+}
+void SetDevices(const std::vector<int>& ordinals)
+{
+    ThreadSolver& s = solver();
+    if (s.multi) { adk_multi_destroy(s.multi); s.multi = nullptr; }
+    s.devices = ordinals;
+    if (ordinals.size() == 1) SetDevice(ordinals[0]);
 }
 LastSolveStats GetLastSolveStats() { return solver().last; }
 }  // namespace B200

@@ -7,6 +7,7 @@
 //   CM::Point2, ORIENTATION, scalar predicates ........ src/common/CustomMath.h:11-58
 //   Diameter, ConvexArea, PointsInTriangleCache,
 //   BenchmarkInfo, ComputeDiameter, GetHullPoints ..... src/common/Utils.h:14-55,111-113
+//   PointsInTriangle, ForAllAntipodalPairs ............ src/common/Utils.h:45-49,57-109
 //   EppsteinAlgorithm[WithBenchmarkInfo] .............. src/common/Eppstein.h:11-24
 //   AntipodalAlgorithm[WithBenchmarkInfo] ............. src/common/Antipodal.h:10-25
 //   AntipodalOptimizedAlgorithm[WithBenchmarkInfo] .... src/common/AntipodalOptimized.h:10-25
@@ -18,6 +19,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <functional>
 #include <limits>
 #include <optional>
 #include <vector>
@@ -91,6 +93,57 @@ void CountPointsBelowAllSegments(const std::vector<CM::Point2>& somePoints,
 void SortPointsClockWiseAroundPoint(const CM::Point2& aReferencePoint, std::vector<CM::Point2>& someOutClockWiseSortedPoints);
 bool ArePointsClockwise(const CM::Point2& aReferencePoint, const CM::Point2& aFirstPoint, const CM::Point2& aSecondPoint);
 std::optional<Diameter> ComputeDiameter(const std::vector<CM::Point2>& somePoints);
+
+// O(1) number of input points strictly inside a triangle, from the three count tables (Utils.h:45-49, Utils.cpp:251-293).
+int PointsInTriangle(const CM::Point2& aFirstPoint, const CM::Point2& aSecondPoint, const CM::Point2& aThirdPoint,
+                     const PointsInTriangleCache& aCache);
+
+// Rotating calipers over the vertices of a convex polygon given in order (Utils.h:57-109): aFunction(p, q) is called for every
+// antipodal vertex pair, in the reference's order (edge p-1 -> p against the vertices farthest from it; an edge parallel to the
+// caliper reports both of its ends).  aMaxLength restricts the walk to the first aMaxLength vertices.  Unlike the reference the
+// walk is bounded (4 n + 8 steps): on an exactly degenerate polygon it ends instead of circling.
+template <typename Container>
+void ForAllAntipodalPairs(const Container& somePoints, const std::function<void(const size_t, const size_t)>& aFunction,
+                          size_t aMaxLength = (size_t) -1)
+{
+    const size_t n = aMaxLength == (size_t) -1 ? somePoints.size() : aMaxLength;
+    if (n < 3) return;
+    const auto succ = [n](size_t v) { return v + 1 == n ? (size_t) 0 : v + 1; };
+    // height gained over the edge p -> succ(p) when the far vertex moves from q to succ(q)
+    const auto gain = [&](size_t p, size_t q)
+    {
+        return CM::SignedArea(somePoints[p], somePoints[succ(p)], somePoints[succ(q)]) -
+               CM::SignedArea(somePoints[p], somePoints[succ(p)], somePoints[q]);
+    };
+    const auto rises = [&](size_t p, size_t q)
+    {
+        return CM::SignedArea(somePoints[p], somePoints[succ(p)], somePoints[succ(q)]) >
+               CM::SignedArea(somePoints[p], somePoints[succ(p)], somePoints[q]);
+    };
+    size_t budget = 4 * n + 8;
+    size_t p = n - 1, q = 0;
+    while (rises(p, q) && budget) { q = succ(q); --budget; }
+    const size_t qFirst = q;
+    while (q != 0 && budget)
+    {
+        --budget;
+        p = succ(p);
+        aFunction(p, q);
+        while (rises(p, q) && budget)
+        {
+            --budget;
+            q = succ(q);
+            if (p == qFirst && q == 0) break;          // back at the first pair
+            aFunction(p, q);
+        }
+        if (CM::IsCloseToZero(gain(p, q)))
+        {   // the edge succ(q) is parallel to the caliper: its other end is antipodal to p as well
+            if (p == qFirst && q == n - 1) break;
+            aFunction(p, succ(q));
+        }
+    }
+}
+
 void GetHullPoints(const std::vector<size_t>& someIndices, const std::vector<CM::Point2>& somePoints,
                    std::vector<CM::Point2>& someOutHullPoints);
 
@@ -144,6 +197,10 @@ namespace B200
 {
 // Selects the CUDA device used by the calling thread's solver context (default: the current device).
 void SetDevice(int aDeviceOrdinal);
+// Several devices of one box for the calling thread's solves: anchors / candidate pairs are sharded over them inside the
+// library (adk_multi_*, one NCCL all-gather + one broadcast per solve).  The environment variable ADK_DEVICES ("0,1,2,3",
+// or "all") sets the same default for every thread.  An empty list / one device = single-GPU path.
+void SetDevices(const std::vector<int>& someDeviceOrdinals);
 // Device-side statistics of the calling thread's most recent solve.
 struct LastSolveStats { uint64_t cellsNominal, cellsExecuted, states, pairs; double kernelMs, dpMs; };
 LastSolveStats GetLastSolveStats();

@@ -29,7 +29,10 @@ METRIC = "dp_cell_updates_per_sec"
 UNIT = "cells/s"
 BYTES_PER_CELL = 20      # read-modify-write of the 8-byte destination area + 4-byte packed back-pointer
 FLOPS_PER_CELL = 20      # two Orientation tests (2 x 9) + area add + compare
+INT_OPS_PER_CELL = 4      # index and count arithmetic per cell update
 FP64_NOMINAL_TFLOPS = 37.2   # 148 SM x 64 FP64 lanes x 2 x 1.965 GHz (no FP64 entry in MEASURED_PEAKS.json)
+INT32_NOMINAL_TOPS = 18.6    # 148 SM x 64 INT32 lanes x 1.965 GHz
+REF_CORES = 16            # replicas of the single-threaded reference timed side by side (fixed, so that every box reports the same arm)
 
 
 def fp64_peak():
@@ -42,6 +45,30 @@ def fp64_peak():
                                               f"{d['dfma_per_sm_per_clk_at_max']:.1f} DFMA/SM/clk); 20 flop/cell (SURVEY 8d)")
     except Exception:
         return FP64_NOMINAL_TFLOPS, "nominal 148 SM x 64 lanes x 2 x 1.965 GHz; 20 flop/cell (SURVEY 8d)"
+
+
+def int32_peak():
+    """INT32 issue peak (IMAD per SM per clock x SMs x clock) measured by tools/issue_peaks.cu, else nominal."""
+    p = os.path.join(ROOT, "profiles", "issue_peaks.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["imad_per_s"]) / 1e12, "measured IMAD issue peak (profiles/issue_peaks.json, tools/issue_peaks.cu)"
+    except Exception:
+        return INT32_NOMINAL_TOPS, "nominal 148 SM x 64 lanes x 1.965 GHz"
+
+
+def frozen_answers(sigma):
+    """The unmodified reference's answers for the sweep (tests/golden/heavy_outputs.json; D = 2 lives in bench_n200.json)."""
+    out = {}
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "heavy_outputs.json")) as f:
+            for r in json.load(f)["runs"]:
+                if r["tag"].startswith(f"bench.sigma{sigma}.D"):
+                    out[float(r["dmax"])] = r
+    except Exception:
+        pass
+    return out
 
 
 def load_workload(sigma):
@@ -150,33 +177,41 @@ def _port_worker(args):
     return time.perf_counter() - t0, r["count"], r["states"]
 
 
-def cpu_reference_run(w, steps, warmup, cores=None):
-    """Times the reference's own CPU implementation on a bounded sample: the D = 2 solve of the sweep, one replica per host
-    core (instance-level parallelism is the only kind the single-threaded reference admits).  Returns the cpu_baseline dict."""
+def cpu_reference_run(w, steps, warmup, cores=None, nsolves=1):
+    """Times the reference's own CPU implementation on a bounded sample: the first `nsolves` solves of the sweep that the
+    fixture holds reference counts for (D = 2 by default), one replica per core on a FIXED number of cores (instance-level
+    parallelism is the only kind the single-threaded reference admits).  Returns the cpu_baseline dict."""
     from multiprocessing import get_context
     from oracle.refpy import ref_available
     kind = "reference" if ref_available("x87") else "port"
     worker = _ref_worker if kind == "reference" else _port_worker
-    smp = w["sample"][0]
-    ncores = cores or max(1, min(os.cpu_count() or 1, 32))
-    job = (w["x"], w["y"], w["amax"], smp["dmax"])
+    samples = w["sample"][:max(1, nsolves)]
+    ncores = cores or max(1, min(os.cpu_count() or 1, REF_CORES))
     ctx = get_context("spawn")
-    times = []
+    times, single = [], None
     with ctx.Pool(ncores) as pool:
         for it in range(warmup + steps):
             t0 = time.perf_counter()
-            res = pool.map(worker, [job] * ncores)
+            rep = 0.0
+            for smp in samples:
+                res = pool.map(worker, [(w["x"], w["y"], w["amax"], smp["dmax"])] * ncores)
+                for _, cnt, _ in res:
+                    assert cnt == smp["count"], (cnt, smp["count"])
+                rep += min(r[0] for r in res)
             dt = time.perf_counter() - t0
-            for _, cnt, _ in res:
-                assert cnt == smp["count"], (cnt, smp["count"])
             if it >= warmup:
                 times.append(dt)
+                single = rep if single is None else min(single, rep)
     total = sum(times)
-    cells = smp["cells"] * ncores * len(times)
-    return {"value": cells / total, "unit": UNIT, "cores": ncores, "kind": kind,
-            "sample": f"D={smp['dmax']} solve of the sweep ({smp['cells']} cells, {smp['states']} states), one replica per core, "
-                      f"{len(times)} timed passes, {total / len(times):.2f} s per pass",
-            "ms_per_step": 1e3 * total / len(times), "single_replica_s": min(r[0] for r in res)}
+    cells = sum(smp["cells"] for smp in samples)
+    states = sum(smp["states"] for smp in samples)
+    what = " + ".join(f"D={smp['dmax']}" for smp in samples)
+    return {"value": cells * ncores * len(times) / total, "unit": UNIT, "cores": ncores, "kind": kind,
+            "sample": f"{what} solve(s) of the sweep ({cells} cells, {states} states = {cells / states:.1f} cells per state; the whole sweep has "
+                      f"27 cells per state), one replica per core on {ncores} cores, {len(times)} timed passes, {total / len(times):.2f} s per pass",
+            "states_per_sec": states * ncores * len(times) / total, "cells_per_sec_per_core": cells * len(times) / total,
+            "states_per_sec_per_core": states * len(times) / total,
+            "ms_per_step": 1e3 * total / len(times), "single_replica_s": single}
 
 
 def run_reference_arm(args):
@@ -184,12 +219,14 @@ def run_reference_arm(args):
     if rank != 0:
         return
     w = load_workload(args.sigma)
-    cb = cpu_reference_run(w, args.steps, args.warmup)
+    cb = cpu_reference_run(w, args.steps, args.warmup, nsolves=args.ref_solves)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f80 (x87 long double)" if cb["kind"] == "reference" else "f64", "data": "synthetic",
             "config": workload_config(w, {"reference_step": "bounded sample: " + cb["sample"]}),
-            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "states_per_sec": cb["states_per_sec"], "single_replica_s": cb["single_replica_s"],
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "states_per_sec", "cells_per_sec_per_core",
+                                                "states_per_sec_per_core", "single_replica_s")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -220,6 +257,7 @@ def run_b200_arm(args):
     solver = pkg.Solver(local)
     stream = torch.cuda.Stream(device=dev)
     solver.set_stream(stream.cuda_stream)
+    solver.set_reuse(False)      # every solve recomputes the count tables and orders, as the reference does on every call
 
     d_x = torch.tensor(w["x"], dtype=torch.float64, device=dev)
     d_y = torch.tensor(w["y"], dtype=torch.float64, device=dev)
@@ -312,12 +350,20 @@ def run_b200_arm(args):
                 traffic = None
         fp64_tflops = res["my_cells"] * FLOPS_PER_CELL / dp_s / 1e12 if dp_s > 0 else 0.0
         fp64_pk, fp64_src = fp64_peak()
-        roof = {"bound": "hbm", "kernel": "k_ad_cells", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src,
+        int_tops = res["my_cells"] * INT_OPS_PER_CELL / dp_s / 1e12 if dp_s > 0 else 0.0
+        int_pk, int_src = int32_peak()
+        # The roofline the north_star names for this config is FP64 / INT issue: the 20 B/cell read-modify-write of the
+        # reference happens in registers and shared memory here, so HBM is not the bound (measured DRAM traffic is a small
+        # fraction of the algorithmic bytes); the HBM figure is kept as `hbm_nominal`.
+        roof = {"bound": "fp64_issue", "kernel": "k_ad_cells", "achieved": fp64_tflops, "peak": fp64_pk, "unit": "TFLOP/s",
+                "frac": fp64_tflops / fp64_pk, "peak_source": fp64_src,
+                "traffic": traffic, "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum per k_ad_cells launch (ncu, profiles/roofline_traffic.json)",
+                "algorithmic_flops_per_launch": res["my_cells"] * FLOPS_PER_CELL / max(launches_dp, 1),
                 "algorithmic_bytes_per_launch": res["my_cells"] * BYTES_PER_CELL / max(launches_dp, 1),
                 "avg_launch_ms": res["my_dp_ms"] / max(launches_dp, 1), "share_of_step": res["my_dp_ms"] / res["dev_ms"],
-                "fp64_issue": {"achieved": fp64_tflops, "peak": fp64_pk, "unit": "TFLOP/s", "frac": fp64_tflops / fp64_pk,
-                               "peak_source": fp64_src}}
+                "int32_issue": {"achieved": int_tops, "peak": int_pk, "unit": "Tinst/s", "frac": int_tops / int_pk, "peak_source": int_src},
+                "hbm_nominal": {"achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                                "note": "20 B/cell (SURVEY 8d) x cells / kernel time; nominal: the bytes never reach HBM"}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": res["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
@@ -331,14 +377,23 @@ def run_b200_arm(args):
                         "d2h_bytes_per_step": len(diams) * (64 + 4 * (n + 4) + 112), "timer": "host wall clock around the C-ABI calls, max over ranks"},
                 "gpu_launches": res["launches"], "roofline": roof, "clocks": clocks,
                 "answers": [{"D": d, "count": r["count"], "area": r["area"], "diam": r["diam"]} for d, r in zip(diams, res["last"])]}
-        # the sample instance must reproduce the reference's answer (the fixture holds the unmodified reference's output)
-        for smp in w["sample"]:
-            got = [r for d, r in zip(diams, res["last"]) if d == smp["dmax"]][0]
-            assert got["count"] == smp["count"] and got["hull"] == smp["hull"] and sorted(got["diam"]) == sorted(smp["diam"]), (got, smp)
-            assert abs(got["area"] - float(smp["area"])) <= 1e-9 * float(smp["area"])
+        # every solve of the sweep must reproduce the unmodified reference's frozen answer (tests/golden/bench_n200.json for the
+        # sample, tests/golden/heavy_outputs.json for the rest)
+        want = {float(r_["dmax"]): r_ for r_ in w["sample"]}
+        want.update(frozen_answers(w["sigma"]))
+        checked = []
+        for d, got in zip(diams, res["last"]):
+            ref = want.get(float(d))
+            if ref is None:
+                continue
+            assert got["count"] == ref["count"] and got["hull"] == ref["hull"] and sorted(got["diam"]) == sorted(ref["diam"]), (d, got, ref)
+            assert abs(got["area"] - float(ref["area"])) <= 1e-9 * float(ref["area"]), (d, got["area"], ref["area"])
+            checked.append(d)
+        line["answers_checked_against_frozen_reference"] = checked
         if world == 1 and not args.no_cpu:
             cb = cpu_reference_run(w, steps=2, warmup=0)
-            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "states_per_sec", "cells_per_sec_per_core",
+                                                       "states_per_sec_per_core", "single_replica_s")}
         print(json.dumps(line), flush=True)
     solver.close()
     if world > 1:
@@ -380,6 +435,7 @@ def run_aux_workload(args):
     solver = pkg.Solver(local)
     stream = torch.cuda.Stream(device=dev)
     solver.set_stream(stream.cuda_stream)
+    solver.set_reuse(False)      # every solve recomputes the count tables and orders, as the reference does on every call
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     amax = 4.0
     if args.workload == "area_n1000":
@@ -464,7 +520,7 @@ def run_aux_workload(args):
     e2e = timed(False, args.steps, 1)
     if rank == 0:
         secs = res["dev_ms"] / 1e3
-        units = nominal * args.steps if nominal else res["cells"]
+        units = res["cells"]          # EXECUTED cell updates (the area kernels skip the levels that cannot be finite; the nominal count is beside it)
         peak, peak_src = measured_peaks()
         dp_s = res["my_dp_ms"] / 1e3
         achieved = res["my_cells"] * bytes_per_cell / dp_s / 1e9 if dp_s > 0 else 0.0     # EXECUTED cells of this rank (levels that cannot be finite are skipped)
@@ -472,10 +528,10 @@ def run_aux_workload(args):
                 "ms_per_step": res["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic" if nominal else "the reference's cell samples (tests/golden/points.json)",
                 "config": {"workload": desc, "l2": "256 MiB memset on the timed stream before every step (L2 flush)",
-                           "cells": "nominal (K-2) n (n-1) (n-2) / 3" if nominal else "counted in-kernel",
+                           "cells": "executed cell updates, counted in-kernel",
                            "cells_executed_per_step": res["cells"] // args.steps},
                 "executed_cells_per_sec": res["cells"] / secs,
-                "e2e": {"value": (nominal * args.steps if nominal else e2e["cells"]) / (e2e["wall_ms"] / 1e3), "unit": UNIT,
+                "e2e": {"value": e2e["cells"] / (e2e["wall_ms"] / 1e3), "unit": UNIT,
                         "ms_per_step": e2e["wall_ms"] / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "timer": "host wall clock around the C-ABI calls, max over ranks"},
                 "gpu_launches": res["launches"],
@@ -487,6 +543,11 @@ def run_aux_workload(args):
         last = res["last"]
         if nominal:
             line["answers"] = [{"count": last["count"], "area": last["area"], "hull": last["hull"]}]
+            line["solve_ms_per_instance"] = res["dev_ms"] / args.steps
+            line["nominal_cells_per_sec"] = nominal * args.steps / secs
+            line["config"]["nominal_cells_per_step"] = nominal
+            line["config"]["nominal_note"] = ("(K-2) n (n-1) (n-2) / 3 with K = n: what the reference's loops would execute (Eppstein.cpp:192-235); the kernels "
+                                              "stop at the deepest reachable level, so `value` counts the executed updates only")
         else:
             line["answers"] = [{"n": len(s_), "count": r["count"], "area": r["area"], "diam": r["diam"], "ms": r["kernel_ms"]} for s_, r in zip(sets, last)]
             line["config"]["parallelism"] = ("one GPU" if world == 1 else "whole instances per rank (adk_solve_batch)" if args.instance_sharding
@@ -496,12 +557,13 @@ def run_aux_workload(args):
             from multiprocessing import get_context
             from oracle.refpy import RefLib, ref_available
             if ref_available("x87"):
-                ncores = max(1, min(os.cpu_count() or 1, 32))
+                ncores = max(1, min(os.cpu_count() or 1, REF_CORES))
                 if nominal:
-                    sub, kc = 200, 16
-                    job = (RefLib.ALGO_EPPSTEIN, x[:sub], y[:sub], kc, amax, float("inf"))
-                    cpu_cells = (kc - 2) * sub * (sub - 1) * (sub - 2) // 3
-                    what = f"first {sub} points, K={kc} (nominal {cpu_cells} cells; the un-capped n=1000 table is 32 GB for the reference)"
+                    sub = 100        # same K policy as the GPU arm (K = inf); the reference executes every nominal cell
+                    job = (RefLib.ALGO_EPPSTEIN, x[:sub], y[:sub], None, amax, float("inf"))
+                    cpu_cells = (sub - 2) * sub * (sub - 1) * (sub - 2) // 3
+                    what = (f"first {sub} points of the same set, K=inf as on the GPU ({cpu_cells} cells, all executed by the reference; "
+                            "the un-capped n=1000 table is 32 GB for the reference)")
                 else:
                     k9 = names.index("real/9/0")
                     job = (RefLib.ALGO_ANTIPODAL_OPTIMIZED, sets[k9][:, 0].tolist(), sets[k9][:, 1].tolist(), None, amax, dmax)
@@ -525,6 +587,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sigma", type=float, default=1.5, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.5, 1.0, 0.5)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--ref-solves", type=int, default=1, help="--impl reference: solves of the sweep per step (1 = D=2, 2 = D=2 and D=3; "
+                    "D=3 alone is ~10 core-minutes per replica)")
     ap.add_argument("--instance-sharding", action="store_true", help="cells_batch on N > 1 GPUs: whole instances per rank (adk_solve_batch) "
                     "instead of every instance's candidate pairs")
     ap.add_argument("--workload", default="ad_n200", choices=["ad_n200", "area_n1000", "cells_batch"],

@@ -57,7 +57,8 @@ typedef struct adk_result
     int64_t entries_required;   /* myRequiredEntriesCount  (-1 when not requested) */
     uint64_t cells_nominal;     /* DP cell updates the reference executes for this call */
     uint64_t cells_executed;    /* DP cell updates the kernels executed */
-    uint64_t states;            /* area+diameter path: DP states created (reference "entries"); area path: prefix-minimum change points */
+    uint64_t states;            /* area+diameter path: DP states created (reference "entries"; after adk_area_diameter_finish: those of the
+                                   winning candidate alone); area path: prefix-minimum change points */
     uint64_t pairs;             /* area+diameter path: candidate pairs within the diameter bound */
     double kernel_ms;           /* device time of the whole call (CUDA events on the solver's stream) */
     double dp_ms;               /* device time of the dominant DP kernel alone */
@@ -89,6 +90,10 @@ const char* adk_last_error(const adk_ctx* ctx);       /* text of the last failur
 int adk_set_memory_budget(adk_ctx* ctx, uint64_t bytes);   /* cap for DP workspaces (default: 75 % of free memory) */
 int adk_set_stream(adk_ctx* ctx, void* cuda_stream);       /* run on the caller's cudaStream_t (NULL = legacy default stream) */
 uint64_t adk_launch_count(const adk_ctx* ctx);             /* kernels launched by this context since adk_create */
+/* By default a context keeps the precompute products (count tables, angular orders) while consecutive solves pass the same
+ * coordinates (a diameter sweep).  enabled = 0: every solve recomputes them, as the reference does on every call
+ * (Eppstein.cpp:143-155, AntipodalOptimized.cpp:469-481); bench.py times this mode. */
+int adk_set_reuse(adk_ctx* ctx, int enabled);
 
 /* ---- whole solves (host buffers in, host buffers out; H2D/D2H inside) ------------------------------------------ */
 int adk_solve_area(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
@@ -142,6 +147,33 @@ int adk_solve_batch(adk_ctx* ctx, const adk_instance* inst, uint32_t ninst, uint
 
 /* Lexicographic best of `count` partials: count desc, area asc, tie_key asc (host side, no device work). */
 int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out);
+
+/* ---- several GPUs of one box behind one handle (replaces the same two reference calls, src/bench/main.cpp:89,100 and
+ *      src/py-binding/main.cpp:29,59, when more than one device is configured).  One blocking call per solve, as in the reference;
+ *      inside it one host thread per device solves that device's shard of the anchors / candidate pairs, ONE ncclAllGather of the
+ *      32-byte adk_partial records + the same adk_merge on every rank is the "max-reduce of (count, area, witness)", the rank that
+ *      owns the winning unit reconstructs the witness from its resident records and ONE ncclBroadcast hands record + hull to every
+ *      rank.  NCCL is bound at run time (libnccl.so.2); without it adk_multi_create fails — there is no fallback. ----------------- */
+typedef struct adk_multi adk_multi;
+
+typedef struct adk_multi_stats
+{
+    uint32_t ndev, pad;
+    uint64_t cells_nominal, cells_executed, states, pairs, launches;   /* sums over the devices (pairs: the common candidate count) */
+    double max_kernel_ms, max_dp_ms, sum_dp_ms;                        /* device time of the slowest rank; DP kernel time, max and sum */
+    double max_exchange_ms;                                            /* all-gather + reconstruction + broadcast, slowest rank */
+} adk_multi_stats;
+
+int adk_multi_create(adk_multi** out, const int* devices, int ndev);  /* devices == NULL or ndev <= 0: CUDA devices 0 .. ndev-1 / all */
+void adk_multi_destroy(adk_multi* m);
+const char* adk_multi_last_error(const adk_multi* m);
+int adk_multi_device_count(const adk_multi* m);
+int adk_multi_set_reuse(adk_multi* m, int enabled);                    /* adk_set_reuse on every device */
+int adk_multi_solve_area(adk_multi* m, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, uint32_t flags,
+                         adk_result* out, uint32_t* hull /* capacity n */);
+int adk_multi_solve_area_diameter(adk_multi* m, const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
+                                  uint32_t flags, adk_result* out, uint32_t* hull);
+int adk_multi_last_stats(const adk_multi* m, adk_multi_stats* out);    /* of the last solve */
 
 /* ---- device-resident variants (pointers are DEVICE pointers; used by bench.py's kernel-only timing) ------------ */
 int adk_area_partial_dev(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, uint64_t kmax, double amax,

@@ -137,4 +137,31 @@ int adkref_points_in_triangle(const double* x, const double* y, uint32_t n, cons
     return 0;
 }
 
+// ForAllAntipodalPairs (Utils.h:57-109) over the polygon hull[0..m) of the point set: the (first, second) POSITIONS it reports,
+// in call order; returns their number (pairs beyond cap are counted, not stored).
+int adkref_antipodal_pairs(const double* x, const double* y, uint32_t n, const uint32_t* hull, uint32_t m, uint32_t* out_pairs, uint32_t cap)
+{
+    std::vector<MT::CM::Point2> points, poly;
+    locToPoints(x, y, n, points);
+    for (uint32_t t = 0; t < m; ++t) poly.push_back(points[hull[t]]);
+    uint32_t cnt = 0;
+    MT::ForAllAntipodalPairs(poly, [&](const size_t a, const size_t b) {
+        if (cnt < cap) { out_pairs[2 * cnt] = (uint32_t) a; out_pairs[2 * cnt + 1] = (uint32_t) b; }
+        ++cnt;
+    });
+    return (int) cnt;
+}
+
+// ComputeDiameter (Utils.cpp:318-338) of the same polygon: the two point indices.
+int adkref_compute_diameter(const double* x, const double* y, uint32_t n, const uint32_t* hull, uint32_t m, uint32_t* out_pair)
+{
+    std::vector<MT::CM::Point2> points, poly;
+    locToPoints(x, y, n, points);
+    for (uint32_t t = 0; t < m; ++t) poly.push_back(points[hull[t]]);
+    const auto d = MT::ComputeDiameter(poly);
+    if (!d) return 0;
+    out_pair[0] = (uint32_t) d->myFirstIndex; out_pair[1] = (uint32_t) d->mySecondIndex;
+    return 1;
+}
+
 }

@@ -88,3 +88,22 @@ class RefLib:
         out = (ctypes.c_int32 * m)()
         self.lib.adkref_points_in_triangle(self._arr(x), self._arr(y), ctypes.c_uint32(n), flat, ctypes.c_uint32(m), out)
         return list(out)
+
+    def antipodal_pairs(self, x, y, hull):
+        """ForAllAntipodalPairs (Utils.h:57-109) over the polygon: list of (first, second) positions in call order."""
+        n, m = len(x), len(hull)
+        cap = 8 * m + 16
+        out = (ctypes.c_uint32 * (2 * cap))()
+        h = (ctypes.c_uint32 * m)(*hull)
+        self.lib.adkref_antipodal_pairs.restype = ctypes.c_int
+        k = self.lib.adkref_antipodal_pairs(self._arr(x), self._arr(y), ctypes.c_uint32(n), h, ctypes.c_uint32(m), out, ctypes.c_uint32(cap))
+        assert k <= cap
+        return [(int(out[2 * t]), int(out[2 * t + 1])) for t in range(k)]
+
+    def compute_diameter(self, x, y, hull):
+        n, m = len(x), len(hull)
+        h = (ctypes.c_uint32 * m)(*hull)
+        out = (ctypes.c_uint32 * 2)()
+        self.lib.adkref_compute_diameter.restype = ctypes.c_int
+        ok = self.lib.adkref_compute_diameter(self._arr(x), self._arr(y), ctypes.c_uint32(n), h, ctypes.c_uint32(m), out)
+        return [int(out[0]), int(out[1])] if ok else None

@@ -8,6 +8,11 @@ set -euo pipefail
 here="$(cd "$(dirname "$0")" && pwd)"
 root="$(cd "$here/../.." && pwd)"
 ref="${ADK_REFERENCE_ROOT:-/root/reference}"
+# a caller of the reference's public helpers (PointsInTriangle, ForAllAntipodalPairs, ComputeDiameter), written against the
+# reference's header names and built against this repo's mirror; needs no reference sources
+mkdir -p "$here/_build"
+g++ -std=c++17 -O2 -I"$root/area-diameter-algorithm_b200/host" "$here/helpers_caller.cpp" -o "$here/_build/helpers_caller" \
+    -L"$root/area-diameter-algorithm_b200" -ladk_host -ladk -Wl,-rpath,"$root/area-diameter-algorithm_b200" -Wl,-rpath,'$ORIGIN/../../../area-diameter-algorithm_b200'
 [ -d "$ref/src/test" ] || { echo "build_dropin.sh: $ref not present, keeping prebuilt files" >&2; exit 0; }
 out="$here/_build"; mkdir -p "$out"
 json_inc="$(python - <<'PY'

@@ -63,7 +63,8 @@ def test_host_mirror_defines_the_reference_entry_points(built):
                 "MT::AntipodalAlgorithmWithBenchmarkInfo(", "MT::AntipodalOptimizedAlgorithm(",
                 "MT::AntipodalOptimizedAlgorithmWithBenchmarkInfo(", "MT::CM::Distance2(", "MT::CM::AreCollinear(",
                 "MT::CM::Orientation(", "MT::CM::SignedArea(", "MT::Diameter::operator==(", "MT::CountPointsBelowAllSegments(",
-                "MT::SortPointsClockWiseAroundPoint(", "MT::ComputeDiameter("]:
+                "MT::SortPointsClockWiseAroundPoint(", "MT::ComputeDiameter(", "MT::PointsInTriangle(", "MT::GetHullPoints(",
+                "MT::B200::SetDevices("]:
         assert sym in out, sym
 
 
@@ -73,6 +74,51 @@ def test_reference_callers_build_unmodified_against_this_library(built):
         pytest.skip("the reference tree is only present in the build container")
     subprocess.run([os.path.join(ROOT, "tests", "dropin", "build_dropin.sh")], check=True, capture_output=True)
     assert os.path.exists(os.path.join(ROOT, "tests", "dropin", "_build", "ref_test_dropin"))
+
+
+def test_public_helpers_of_utils_h_match_the_reference(built):
+    """A caller of MT::ForAllAntipodalPairs (Utils.h:57-109), MT::ComputeDiameter (Utils.cpp:318-338) and MT::PointsInTriangle
+    (Utils.h:45-49), compiled against this build's headers (tests/dropin/helpers_caller.cpp), reports what the unmodified
+    reference reports: the same antipodal pairs in the same order, the same diameter pair, the same counts.  Host code only."""
+    from oracle.refpy import RefLib, ref_available
+    if not ref_available("x87"):
+        pytest.skip("oracle/_ref is built in the build container")
+    exe = os.path.join(ROOT, "tests", "dropin", "_build", "helpers_caller")
+    subprocess.run([os.path.join(ROOT, "tests", "dropin", "build_dropin.sh")], check=True, capture_output=True)
+    assert os.path.exists(exe)
+    import json
+    import random
+    with open(os.path.join(ROOT, "tests", "golden", "points.json")) as f:
+        points = json.load(f)
+    with open(os.path.join(ROOT, "tests", "golden", "ref_outputs.json")) as f:
+        runs = [r for r in json.load(f)["runs"] if r["found"] and len(r["hull"]) >= 3]
+    ref = RefLib("x87")
+    rng = random.Random(5)
+    checked = 0
+    for r in rng.sample(runs, 40):
+        pts = points[r["name"]]
+        if len(pts) > 120:
+            continue
+        x = [p[0] for p in pts]
+        y = [p[1] for p in pts]
+        n = len(x)
+        below, coll, rb = ref.count_tables(x, y)
+        tri = [rng.sample(range(n), 3) for _ in range(50)]
+        text = [str(n)] + [f"{a!r} {b!r}" for a, b in zip(x, y)] + [str(len(r["hull"])), " ".join(map(str, r["hull"])), str(len(tri))]
+        text += [" ".join(map(str, t)) for t in tri] + [" ".join(map(str, below)), " ".join(map(str, coll)), " ".join(map(str, rb))]
+        out = subprocess.run([exe], input="\n".join(text) + "\n", capture_output=True, text=True, check=True).stdout.split()
+        k = int(out[1])
+        pairs = [(int(out[2 + 2 * t]), int(out[3 + 2 * t])) for t in range(k)]
+        at = 2 + 2 * k
+        assert out[at] == "diameter"
+        diam = [int(out[at + 1]), int(out[at + 2])]
+        assert out[at + 3] == "pit"
+        pit = [int(v) for v in out[at + 5:at + 5 + len(tri)]]
+        assert pairs == ref.antipodal_pairs(x, y, r["hull"]), r["name"]
+        assert diam == ref.compute_diameter(x, y, r["hull"]), r["name"]
+        assert pit == ref.points_in_triangle(x, y, tri), r["name"]
+        checked += 1
+    assert checked >= 20
 
 
 def _gloo_worker(rank, world, port, q):

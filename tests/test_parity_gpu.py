@@ -345,6 +345,53 @@ def test_full_size_properties_config3_n1000(solver, oracle):
     assert_same_solution(solver.solve_area(x[:sub], y[:sub], 16, 4.0, True), oracle.solve_area(x[:sub], y[:sub], 16, 4.0, True), "n300 K16")
 
 
+# ------------------------------------------------------------------------------------------------ the benchmarked instances
+@pytest.mark.parametrize("d", [2, 3, 4, 5, 6])
+def test_headline_sweep_equals_the_frozen_reference(golden, solver, d):
+    """bench.py's headline (BASELINE config 4: Gaussian n = 200, sigma = 1.5, A = 4, D = 2..6): count, hull cycle and diameter
+    pair equal to the unmodified reference (x87 build, tests/golden/heavy_outputs.json; D = 2 from bench_n200.json), area to
+    1e-9 relative, and the states the kernels create equal to the reference's hash entries."""
+    fx = golden["bench_n200"]
+    pts = fx["sets"]["1.5"]["points"]
+    x = [float(p[0]) for p in pts]
+    y = [float(p[1]) for p in pts]
+    if d == 2:
+        smp = fx["sets"]["1.5"]["sample"][0]
+        want = {"found": 1, "count": smp["count"], "area": float(smp["area"]), "hull": smp["hull"], "diam": smp["diam"],
+                "entries_required": smp.get("ref_entries")}
+    else:
+        want = golden["heavy"][f"bench.sigma1.5.D{d}"]
+    g = solver.solve_area_diameter(x, y, None, fx["amax"], float(d), True, counters=True)
+    assert_same_solution(g, want, ("sigma 1.5", d))
+    check_witness(x, y, g, fx["amax"], float(d))
+    if want.get("entries_required"):
+        assert g["entries_required"] == want["entries_required"], (d, g["entries_required"], want["entries_required"])
+
+
+@pytest.mark.parametrize("slide", [1, 2, 3, 4, 5])
+def test_cell_samples_at_the_real_call_shape(golden, solver, slide):
+    """BASELINE config 5 at the call shape of quality_of_results_comparison.py:194-197 (A = 4, D = 4, K = inf): real/1..5
+    against the frozen reference (real/0 and real/6..9 are pinned in the tests above)."""
+    want = golden["heavy"][f"real.{slide}.D4"]
+    x, y = xy(golden["points"][want["name"]])
+    g = solver.solve_area_diameter(x, y, None, want["amax"], want["dmax"], True, counters=True)
+    assert_same_solution(g, want, want["tag"])
+    # States: exactly those of the binary64 restatement; the x87 reference differs by a handful of knife-edge predicates on the
+    # 5-decimal real coordinates (6 of 2.66e8 states on real/2), with identical answers.
+    assert g["entries_required"] == want["entries_required_f64"], (want["tag"], g["entries_required"], want["entries_required_f64"])
+    assert abs(g["entries_required"] - want["entries_required"]) <= 1e-6 * want["entries_required"]
+
+
+def test_config3_n1000_K16_equals_the_frozen_reference(golden, solver):
+    """BASELINE config 3's point set (Gaussian n = 1000, sigma = 2, seed 1000), area path with K capped at 16 (the un-capped
+    table is 32 GB for the reference): the unmodified reference's answer, 42 core-minutes in the build container."""
+    want = golden["heavy"]["area.n1000.K16"]
+    pts = _synth().gaussian_points(1000, 2.0, 1000)
+    x, y = xy(pts)
+    g = solver.solve_area(x, y, 16, want["amax"], True)
+    assert_same_solution(g, want, "area n1000 K16")
+
+
 # ------------------------------------------------------------------------------------------------ drop-in callers
 def test_reference_gtest_binary_runs_against_the_gpu_library(golden, built):
     """The reference's own src/test/main.cpp, compiled unmodified in the build container against libadk_host.so
