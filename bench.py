@@ -333,6 +333,51 @@ def run_b200_arm(args):
     clocks = sampler.stop() if rank == 0 else None
     e2e = timed(False, args.steps, max(1, args.warmup // 3))
 
+    # Several GPUs behind the reference-facing call: ONE process (rank 0 here) hands host buffers to adk_multi_solve_area_diameter,
+    # the library shards the candidate pairs over the N devices with one host thread each and exchanges the local bests with NCCL
+    # (all-gather + witness broadcast) inside the call.  This is what the reference's C++ callers get through libadk_host.so
+    # with ADK_DEVICES set.  The other ranks free their devices' workspaces and wait.
+    multi = None
+    if world > 1:
+        solver.close()
+        del flush
+        torch.cuda.empty_cache()
+        torch.cuda.synchronize()
+        # the waiting ranks must not spin in a kernel on the devices rank 0 is about to use (an NCCL barrier does): wait on the host
+        host_group = dist.new_group(backend="gloo")
+        dist.barrier(group=host_group)
+        if rank == 0:
+            m = pkg.MultiSolver(list(range(world)))
+            m.set_reuse(False)
+            fl = [torch.empty(256 << 20, dtype=torch.uint8, device=torch.device("cuda", d)) for d in range(world)]
+
+            def msweep():
+                for f_ in fl:
+                    f_.zero_()
+                for d_ in range(world):
+                    torch.cuda.synchronize(d_)
+                t0_ = time.perf_counter()
+                cells_ = 0; states_ = 0; exch_ = 0.0; dp_ = 0.0; outs_ = []
+                for d in diams:
+                    r_ = m.solve_area_diameter_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, d, True)
+                    st_ = m.last_stats()
+                    cells_ += r_["cells_executed"]; states_ += r_["states"]; exch_ += st_["max_exchange_ms"]; dp_ += st_["max_dp_ms"]
+                    outs_.append(r_)
+                return time.perf_counter() - t0_, cells_, states_, exch_, dp_, outs_
+            for _ in range(2):
+                msweep()
+            tt = cc = ss = ee = dd_ = 0.0
+            for _ in range(args.steps):
+                t_, c_, s_, e_, d_, mouts = msweep()
+                tt += t_; cc += c_; ss += s_; ee += e_; dd_ += d_
+            multi = {"value": cc / tt, "unit": UNIT, "ms_per_step": 1e3 * tt / args.steps, "states_per_sec": ss / tt,
+                     "exchange_ms_per_step": ee / args.steps, "slowest_rank_dp_ms_per_step": dd_ / args.steps,
+                     "api": "adk_multi_solve_area_diameter (host buffers; shards, NCCL all-gather and witness broadcast inside libadk.so)",
+                     "answers": [{"D": d, "count": r_["count"], "area": r_["area"], "diam": r_["diam"], "hull": r_["hull"]} for d, r_ in zip(diams, mouts)]}
+            m.close()
+            del fl
+        dist.barrier(group=host_group)
+
     if rank == 0:
         secs = res["dev_ms"] / 1e3
         value = res["cells"] / secs
@@ -372,9 +417,18 @@ def run_b200_arm(args):
                                               "states_per_step": res["states"] // args.steps, "cells_per_step": res["cells"] // args.steps}),
                 "solve_ms_per_instance": res["dev_ms"] / args.steps / len(diams),
                 "states_per_sec": res["states"] / secs,
-                "e2e": {"value": e2e["cells"] / (e2e["wall_ms"] / 1e3), "unit": UNIT, "ms_per_step": e2e["wall_ms"] / args.steps,
-                        "h2d_bytes_per_step": len(diams) * 2 * n * 8 * (1 if world == 1 else 2),
-                        "d2h_bytes_per_step": len(diams) * (64 + 4 * (n + 4) + 112), "timer": "host wall clock around the C-ABI calls, max over ranks"},
+                "e2e": ({"value": e2e["cells"] / (e2e["wall_ms"] / 1e3), "unit": UNIT, "ms_per_step": e2e["wall_ms"] / args.steps,
+                         "h2d_bytes_per_step": len(diams) * 2 * n * 8,
+                         "d2h_bytes_per_step": len(diams) * (64 + 4 * (n + 4) + 112), "timer": "host wall clock around the C-ABI calls",
+                         "api": "adk_solve_area_diameter (host buffers)"} if multi is None else
+                        {"value": multi["value"], "unit": UNIT, "ms_per_step": multi["ms_per_step"],
+                         "h2d_bytes_per_step": len(diams) * world * 2 * n * 8,
+                         "d2h_bytes_per_step": len(diams) * world * (64 + 32 * world + 4 * (n + 16)), "timer": "host wall clock around the C-ABI calls",
+                         "api": multi["api"], "exchange_ms_per_step": multi["exchange_ms_per_step"],
+                         "slowest_rank_dp_ms_per_step": multi["slowest_rank_dp_ms_per_step"]}),
+                "e2e_one_process_per_gpu": None if multi is None else
+                        {"value": e2e["cells"] / (e2e["wall_ms"] / 1e3), "unit": UNIT, "ms_per_step": e2e["wall_ms"] / args.steps,
+                         "api": "adk_area_diameter_partial / _finish per rank + torch.distributed all-gather and broadcast"},
                 "gpu_launches": res["launches"], "roofline": roof, "clocks": clocks,
                 "answers": [{"D": d, "count": r["count"], "area": r["area"], "diam": r["diam"]} for d, r in zip(diams, res["last"])]}
         # every solve of the sweep must reproduce the unmodified reference's frozen answer (tests/golden/bench_n200.json for the
@@ -389,13 +443,19 @@ def run_b200_arm(args):
             assert got["count"] == ref["count"] and got["hull"] == ref["hull"] and sorted(got["diam"]) == sorted(ref["diam"]), (d, got, ref)
             assert abs(got["area"] - float(ref["area"])) <= 1e-9 * float(ref["area"]), (d, got["area"], ref["area"])
             checked.append(d)
+        if multi is not None:
+            for d, got in zip(diams, multi["answers"]):
+                ref = want.get(float(d))
+                if ref is not None:
+                    assert got["count"] == ref["count"] and got["hull"] == ref["hull"] and sorted(got["diam"]) == sorted(ref["diam"]), ("multi", d, got, ref)
         line["answers_checked_against_frozen_reference"] = checked
         if world == 1 and not args.no_cpu:
             cb = cpu_reference_run(w, steps=2, warmup=0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "states_per_sec", "cells_per_sec_per_core",
                                                        "states_per_sec_per_core", "single_replica_s")}
         print(json.dumps(line), flush=True)
-    solver.close()
+    if world == 1:
+        solver.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -392,6 +392,67 @@ def test_config3_n1000_K16_equals_the_frozen_reference(golden, solver):
     assert_same_solution(g, want, "area n1000 K16")
 
 
+# ------------------------------------------------------------------------------------------------ several GPUs behind the C ABI
+def _device_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("ndev", [1, 2, 4, 8])
+def test_multi_gpu_handle_equals_single_gpu_and_the_reference(golden, pkg, solver, ndev):
+    """adk_multi_* (host thread per device, NCCL all-gather of the 32-byte partials, witness broadcast from the owner; all inside
+    libadk.so): same answers and the same BenchmarkInfo counters as the single-GPU entry points and as the frozen reference.
+    ndev = 1 runs the whole NCCL path with one rank; larger ndev need that many devices."""
+    if _device_count() < ndev:
+        pytest.skip(f"needs {ndev} CUDA devices")
+    m = pkg.MultiSolver(list(range(ndev)))
+    try:
+        assert m.ndev == ndev
+        for tag in ("bench.ADopt", "bind.ADopt.75"):
+            for r in golden["runs"][tag][:6]:
+                x, y = xy(golden["points"][r["name"]])
+                g = m.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], True, counters=True)
+                assert_same_solution(g, r, (tag, r["name"], ndev))
+                assert g["entries_required"] == r["entries_required"], (tag, r["name"], g["entries_required"], r["entries_required"])
+        for r in golden["runs"]["bench.A"][:3] + golden["runs"]["test.A"][40:46]:
+            x, y = xy(golden["points"][r["name"]])
+            g = m.solve_area(x, y, r["kmax"], r["amax"], True, counters=True)
+            s1 = solver.solve_area(x, y, r["kmax"], r["amax"], True, counters=True)
+            assert_same_solution(g, r, ("A", r["name"], ndev))
+            assert (g["entries_alloc"], g["entries_required"]) == (s1["entries_alloc"], s1["entries_required"])
+        # the headline instance, D = 3: frozen reference answer, and the cells / states of the shards add up to the whole solve
+        fx = golden["bench_n200"]
+        pts = fx["sets"]["1.5"]["points"]
+        x = [float(p[0]) for p in pts]
+        y = [float(p[1]) for p in pts]
+        g = m.solve_area_diameter(x, y, None, fx["amax"], 3.0, True, counters=True)
+        want = golden["heavy"]["bench.sigma1.5.D3"]
+        assert_same_solution(g, want, ("sigma 1.5 D3", ndev))
+        assert g["entries_required"] == want["entries_required"]
+        st = m.last_stats()
+        assert st["ndev"] == ndev and st["states"] == g["states"] and st["cells_executed"] == g["cells_executed"]
+        # empty / tiny inputs keep the reference's nullopt behaviour
+        assert m.solve_area([0.0, 1.0], [0.0, 1.0], None, 4.0, True)["found"] == 0
+        assert m.solve_area_diameter([0.0, 1.0, 0.0], [0.0, 0.0, 1.0], 2, 4.0, 4.0, True)["found"] == 0
+    finally:
+        m.close()
+
+
+def test_reference_gtest_binary_runs_on_several_gpus(golden, built):
+    """The reference's unmodified src/test/main.cpp, linked against libadk_host.so, with ADK_DEVICES naming two devices: the
+    MT:: entry points shard every solve inside the library."""
+    if _device_count() < 2:
+        pytest.skip("needs 2 CUDA devices")
+    exe = os.path.join(ROOT, "tests", "dropin", "_build", "ref_test_dropin")
+    if not os.path.exists(exe):
+        pytest.skip("tests/dropin/_build is produced in the build container")
+    write_reference_layout(golden, os.path.join(ROOT, "tests", "dropin", "_data"))
+    env = dict(os.environ, ADK_DEVICES="0,1")
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=1500, env=env, cwd=ROOT)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "[  PASSED  ] 1 test" in out.stdout
+
+
 # ------------------------------------------------------------------------------------------------ drop-in callers
 def test_reference_gtest_binary_runs_against_the_gpu_library(golden, built):
     """The reference's own src/test/main.cpp, compiled unmodified in the build container against libadk_host.so
