@@ -326,8 +326,16 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 constexpr int kCellWarps = ADK_CELL_WARPS;       // warps per CTA (one candidate per CTA) when candidates are plentiful
 constexpr int kMaxCellWarps = 16;                // ... and when few, heavy candidates set the critical path (chosen per launch)
 constexpr int kCellThreads = kCellWarps * 32;
+#ifndef ADK_CELL_CTAS
+#define ADK_CELL_CTAS 5
+#endif
+constexpr int kCellCtas = ADK_CELL_CTAS;         // resident CTAs per SM the 4-warp kernel is compiled for (registers per thread follow)
 constexpr int kBT = 32;                          // layers per tile = lanes
-constexpr int kGrp = 32;                         // sources per group in shared memory = rows of the suffix table
+constexpr int kGrp = 32;                         // sources per group in shared memory
+#ifndef ADK_TAB_ROWS
+#define ADK_TAB_ROWS 16
+#endif
+constexpr int kTabRows = ADK_TAB_ROWS;           // rows of the suffix table in shared memory: one per DISTINCT suffix start of the LEFT group that a leader needs
 constexpr int kDstCap = 128;                     // destinations per pass with their state in shared memory
 constexpr uint32_t kFB = 0xffffu;                // suffix start "none": the destination takes the explicit path for that group
 constexpr uint32_t kNil = 0xffffu;
@@ -413,7 +421,7 @@ __host__ __device__ inline size_t warp_ws_bytes(uint32_t grp, uint32_t dst, uint
 {
     return ((size_t) grp * 256 + (size_t) 2 * grp * (sizeof(SrcGeo) + sizeof(SrcVal)) + (size_t) dst * 3 * lo_bytes + (size_t) (grp + 1) * 4 + 15) & ~(size_t) 15;
 }
-constexpr size_t kWarpWsBytes = ((size_t) kGrp * 256 + (size_t) 2 * kGrp * 48 + (size_t) kDstCap * 3 + (size_t) (kGrp + 1) * 4 + 15) & ~(size_t) 15;
+constexpr size_t kWarpWsBytes = ((size_t) kTabRows * 256 + (size_t) 2 * kGrp * 48 + (size_t) kDstCap * 3 + (size_t) (kGrp + 1) * 4 + 15) & ~(size_t) 15;
 
 __host__ __device__ inline AuxLayout aux_layout(uint32_t max_nl, uint32_t max_nr)
 {
@@ -436,6 +444,8 @@ __host__ __device__ inline AuxLayout aux_layout(uint32_t max_nl, uint32_t max_nr
     return A;
 }
 
+// The context of the candidate a CTA is working on.  ONE copy per CTA, in shared memory: every warp reads it from there, and the
+// out-of-line paths take its address without forcing a per-thread copy into local memory.
 struct CellCtx
 {
     // candidate
@@ -448,9 +458,11 @@ struct CellCtx
     // per-candidate tables (global, per CTA)
     uint16_t* sig[2]; uint16_t* inv[2]; uint16_t* stay[2]; EdgeRec* edge[2];      // [0] = right chain, [1] = left chain
     uint32_t W, WR, WB;           // directory words per cell; bitmap words of the RIGHT part / of a cell
-    // warp-private workspaces: shared memory (kGrp / kDstCap) and the global spill (spill_grp / spill_dst)
-    unsigned char* wsmem;
-    unsigned char* wspill;
+    // warp-private workspaces: shared memory (kGrp / kDstCap; warp w at ws_base + w * kWarpWsBytes) and the global spill
+    // (spill_grp / spill_dst; warp w at spill_base + w * spill_bytes)
+    unsigned char* ws_base;
+    unsigned char* spill_base;
+    size_t spill_bytes;
     uint32_t spill_grp, spill_dst;
     // CTA-shared
     volatile uint32_t* rowdone;   // rowdone[a] = cells of row a finished (they finish in b order)
@@ -616,11 +628,12 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
     const double* __restrict__ vpool = C.sl.vpool;
     const uint32_t cell = a * nr + b;
 
-    unsigned char* wbase = SPILL ? C.wspill : C.wsmem;
+    unsigned char* wbase = SPILL ? C.spill_base + C.spill_bytes * (threadIdx.x >> 5) : C.ws_base + kWarpWsBytes * (threadIdx.x >> 5);
     const uint32_t gcap = SPILL ? C.spill_grp : (uint32_t) kGrp;
     const uint32_t dcap = SPILL ? C.spill_dst : (uint32_t) kDstCap;
+    const uint32_t trows = SPILL ? C.spill_grp : (uint32_t) kTabRows;
     double* tab = reinterpret_cast<double*>(wbase);                              // suffix minima of the LEFT group, [row][layer lane]
-    SrcGeo* geo = reinterpret_cast<SrcGeo*>(wbase + (size_t) gcap * 256);        // [0, gcap): RIGHT group, [gcap, 2 gcap): LEFT group
+    SrcGeo* geo = reinterpret_cast<SrcGeo*>(wbase + (size_t) trows * 256);       // [0, gcap): RIGHT group, [gcap, 2 gcap): LEFT group
     SrcVal* val = reinterpret_cast<SrcVal*>(geo + 2 * gcap);
     lo_t* loRs = reinterpret_cast<lo_t*>(val + 2 * gcap);
     lo_t* loLs = loRs + dcap;
@@ -748,6 +761,7 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
 #pragma unroll 1
         for (uint32_t t = lane; t <= PR; t += 32) head[t] = FB;
         __syncwarp();
+        uint32_t needL = 0;          // suffix starts of the LEFT group that some leader reads (bit = position; shared-memory mode only)
         // ---- suffix starts: lanes = destinations
 #pragma unroll 1
         for (uint32_t d0 = 0; d0 < nd; d0 += 32)
@@ -806,14 +820,19 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
             const uint32_t key = !have ? 0xffffffffu : (fb ? (0x80000000u | dl) : (loR | (loL << 16)));
             const uint32_t peers = __match_any_sync(kFull, key);
             const bool empty = loR == PR && loL == PL;
-            if (have && !empty && (uint32_t) (__ffs((int) peers) - 1) == lane)
-                nxt[dl] = (lo_t) atomicExch(&head[loR == FB ? PR : loR], dl);
+            const bool leads = have && !empty && (uint32_t) (__ffs((int) peers) - 1) == lane;
+            if (leads) nxt[dl] = (lo_t) atomicExch(&head[loR == FB ? PR : loR], dl);
+            if (!SPILL) needL |= __reduce_or_sync(kFull, (leads && loL < PL) ? (1u << loL) : 0u);
         }
         __syncwarp();
+        // The suffix table holds one row per suffix start that a leader needs (a handful per cell); should they outnumber the
+        // rows, the sweep is repeated for the next kTabRows of them.
+        const uint32_t npass = SPILL ? 1u : max(1u, ((uint32_t) __popc(needL) + kTabRows - 1u) / kTabRows);
         // ---- the sweep: lanes = layers
 #pragma unroll 1
-        for (uint32_t t = 0; t < ntiles; ++t)
+        for (uint32_t tp = 0; tp < ntiles * npass; ++tp)
         {
+            const uint32_t t = tp / npass, pass = tp - t * npass;
             const uint32_t k0 = klo + t * kBT, k = k0 + lane;
             const bool kact = k <= khi;
             {   // suffix minima of the LEFT group
@@ -823,7 +842,12 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
                 for (int r = (int) PL - 1; r >= 0; --r)
                 {
                     v = amin(v, src_value(vl[r], vpool, k, kact, C.amax));
-                    tab[(size_t) r * 32 + lane] = v;
+                    if (SPILL) tab[(size_t) r * 32 + lane] = v;
+                    else if ((needL >> r) & 1u)
+                    {
+                        const uint32_t row = (uint32_t) __popc(needL & ((1u << r) - 1u)) - pass * kTabRows;
+                        if (row < (uint32_t) kTabRows) tab[row * 32 + lane] = v;
+                    }
                 }
             }
             // backward sweep over the RIGHT group; the destinations whose suffix starts at r are emitted when r is reached
@@ -844,7 +868,17 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
                     const uint32_t dd = dc0 + dl;
                     const uint32_t loR = loRs[dl], loL = loLs[dl];
                     double v = vR;
-                    if (loL < PL) v = amin(v, tab[(size_t) loL * 32 + lane]);
+                    if (loL < PL)
+                    {
+                        uint32_t row = loL;
+                        if (!SPILL)
+                        {
+                            row = (uint32_t) __popc(needL & ((1u << loL) - 1u)) - pass * kTabRows;
+                            if (row >= (uint32_t) kTabRows) continue;             // this leader's row belongs to another pass
+                        }
+                        v = amin(v, tab[(size_t) row * 32 + lane]);
+                    }
+                    else if (pass != 0u) continue;                              // no table row needed: emitted in the first pass
                     if (loL == FB) v = amin(v, explicit_min(C, true, dd, k, kact, a, b, geo + gcap, val + gcap, PL));
                     if (loR == FB) v = amin(v, explicit_min(C, false, dd, k, kact, a, b, geo, val, PR));
                     // the destination's layer vector: first .. last finite layer, holes stay +inf.  A cell deeper than one tile
@@ -910,10 +944,11 @@ __device__ __forceinline__ bool process_cell(const CellCtx& C, uint32_t a, uint3
     return true;
 }
 
-__device__ __noinline__ void process_cell_spilled(const CellCtx& C, uint32_t a, uint32_t b, uint32_t lane,
-                                                  uint32_t& bk, double& bv, unsigned long long& my_cells, unsigned int& my_states)
-{
-    process_cell<true>(C, a, b, lane, bk, bv, my_cells, my_states);
+struct CellOut { double bv; unsigned long long cells; uint32_t bk; unsigned int states; };
+__device__ __noinline__ CellOut process_cell_spilled(const CellCtx& C, uint32_t a, uint32_t b, uint32_t lane, CellOut io)
+{   // by value in, by value out: the caller's running totals stay in registers
+    process_cell<true>(C, a, b, lane, io.bk, io.bv, io.cells, io.states);
+    return io;
 }
 
 struct CandResult { uint32_t kbest; uint32_t states; double area; };     // best terminal layer (0 = none) of one candidate
@@ -957,24 +992,32 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const unsigned int states0 = my_states;
     if (threadIdx.x == 0) *s_cstates = 0u;
-    build_lune(x, y, n, pr, C.S, s_cnt);
+    {
+        LuneSmem S = C.S;
+        build_lune(x, y, n, pr, S, s_cnt);
+    }
     const uint32_t nl = pr.nl, nr = pr.nr;
     const uint64_t inner = (uint64_t) nl + nr - 4;
-    C.nl = nl; C.nr = nr;
-    C.lim = (uint32_t) (kmax - 2 < inner ? kmax - 2 : inner);           // :137
-    C.nlayers = nlayers_ref;                                          // :483
-    C.Sx = C.S.Lx[0]; C.Sy = C.S.Ly[0]; C.Ex = C.S.Lx[nl - 1]; C.Ey = C.S.Ly[nl - 1];
-    C.Sp = C.S.Lidx[0]; C.Ep = C.S.Lidx[nl - 1];
-    C.seg2 = dist2(C.Sx, C.Sy, C.Ex, C.Ey);
+    if (threadIdx.x == 0)
+    {
+        C.nl = nl; C.nr = nr;
+        C.lim = (uint32_t) (kmax - 2 < inner ? kmax - 2 : inner);           // :137
+        C.nlayers = nlayers_ref;                                          // :483
+        C.Sx = C.S.Lx[0]; C.Sy = C.S.Ly[0]; C.Ex = C.S.Lx[nl - 1]; C.Ey = C.S.Ly[nl - 1];
+        C.Sp = C.S.Lidx[0]; C.Ep = C.S.Lidx[nl - 1];
+        C.seg2 = dist2(C.Sx, C.Sy, C.Ex, C.Ey);
+        C.W = nl + nr - 2; C.WR = (nr + 31) / 32; C.WB = live_words(nl, nr);
+    }
+    __syncthreads();
     // sorted orders and "stay" suffix starts of both chains (the key scratch is the warp's own workspace)
     {
         const uint32_t nmax = nl > nr ? nl : nr;
-        double* keys = nmax * sizeof(double) <= kWarpWsBytes ? reinterpret_cast<double*>(C.wsmem) : reinterpret_cast<double*>(C.wspill);
+        double* keys = nmax * sizeof(double) <= kWarpWsBytes ? reinterpret_cast<double*>(C.ws_base + kWarpWsBytes * warp)
+                                                          : reinterpret_cast<double*>(C.spill_base + C.spill_bytes * warp);
         build_chain_tables(C, T, false, keys, lane, warp, nw);
         build_chain_tables(C, T, true, keys, lane, warp, nw);
     }
     // reset the slice: no cell has produced anything, no edge is live
-    C.W = nl + nr - 2; C.WR = (nr + 31) / 32; C.WB = live_words(nl, nr);
     for (uint32_t t = threadIdx.x; t < nl * nr; t += blockDim.x) C.sl.alive[t] = t == 0 ? 1 : 0;
     {
         const size_t nwords = (size_t) nl * nr * C.WB;                 // slices are 256-byte aligned and sized for the widest lune
@@ -1020,7 +1063,11 @@ __device__ void run_candidate(const double* __restrict__ x, const double* __rest
         __syncwarp();
         __threadfence_block();
         if (!process_cell<false>(C, a, b, lane, bk, bv, my_cells, my_states))
-            process_cell_spilled(C, a, b, lane, bk, bv, my_cells, my_states);
+        {
+            CellOut io; io.bk = bk; io.bv = bv; io.cells = my_cells; io.states = my_states;
+            io = process_cell_spilled(C, a, b, lane, io);
+            bk = io.bk; bv = io.bv; my_cells = io.cells; my_states = io.states;
+        }
         __threadfence_block();
         __syncwarp();
         if (lane == 0) { C.rowdone[a] = b + 1; C.coldone[b] = a + 1; }
@@ -1046,18 +1093,17 @@ __device__ __forceinline__ void setup_ctx(CellCtx& C, unsigned char* smem_raw, u
                                           const CellLayout& Lo, uint32_t slice, unsigned char* aux, const AuxLayout& Ax, double amax,
                                           unsigned int* next, unsigned int* bump, unsigned int* overflow)
 {
-    const uint32_t warp = threadIdx.x >> 5;
     uint32_t* done = nullptr;
     const uint32_t nw = blockDim.x >> 5;
     C.S = carve_cells_smem(smem_raw, capL, capR, nw, &done);
-    C.wsmem = smem_raw + kWarpWsBytes * warp;
+    C.ws_base = smem_raw;
     unsigned char* ax = aux + (size_t) blockIdx.x * Ax.bytes;
     for (int ch = 0; ch < 2; ++ch)
     {
         C.sig[ch] = reinterpret_cast<uint16_t*>(ax + Ax.off_sig[ch]); C.inv[ch] = reinterpret_cast<uint16_t*>(ax + Ax.off_inv[ch]);
         C.stay[ch] = reinterpret_cast<uint16_t*>(ax + Ax.off_stay[ch]); C.edge[ch] = reinterpret_cast<EdgeRec*>(ax + Ax.off_edge[ch]);
     }
-    C.wspill = ax + Ax.off_spill + Ax.spill_bytes * warp;
+    C.spill_base = ax + Ax.off_spill; C.spill_bytes = Ax.spill_bytes;
     C.spill_grp = Ax.grp_cap; C.spill_dst = Ax.dst_cap;
     C.rowdone = done; C.coldone = done + capL;
     C.sl = carve_cells(arena, Lo, slice);
@@ -1080,10 +1126,11 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
     __shared__ uint32_t s_wk[kMaxCellWarps];
     __shared__ double s_wv[kMaxCellWarps];
     __shared__ CtaBest s_best;
-    CellCtx C;
+    __shared__ CellCtx C;
     uint32_t cur = 0;                      // each CTA owns slices 2*blockIdx and 2*blockIdx+1: the one being written and the
                                            // one that holds the CTA's best candidate so far (kept for the witness walk)
-    setup_ctx(C, smem_raw, capL, capR, arena, Lo, 2 * blockIdx.x + cur, aux, Ax, amax, &s_next, &s_bump, &s_overflow);
+    if (threadIdx.x == 0) setup_ctx(C, smem_raw, capL, capR, arena, Lo, 2 * blockIdx.x + cur, aux, Ax, amax, &s_next, &s_bump, &s_overflow);
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
     unsigned long long my_cells = 0; unsigned int my_states = 0;
     if (threadIdx.x == 0) { s_best.found = 0; s_best.count = 0; s_best.area = 0.0; s_best.key = ~0ull; s_best.s = s_best.t = 0;
@@ -1124,7 +1171,8 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
         if (better)
         {   // keep this candidate's records: continue in the other slice
             cur ^= 1u;
-            C.sl = carve_cells(arena, Lo, 2 * blockIdx.x + cur);
+            __syncthreads();
+            if (threadIdx.x == 0) C.sl = carve_cells(arena, Lo, 2 * blockIdx.x + cur);
         }
     }
     for (int o = 16; o; o >>= 1) { my_cells += __shfl_xor_sync(kFull, my_cells, o); my_states += __shfl_xor_sync(kFull, my_states, o); }
@@ -1330,13 +1378,13 @@ int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uin
 {
     const size_t smem = cells_smem_bytes(capL, capR, nw);
     if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
-    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, 16 / kCellWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, kCellCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     else ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kMaxCellWarps * 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     ADK_CUDA(c, cudaMemsetAsync(&sm->counters.queue, 0, sizeof(unsigned int), c->stream));
     ADK_CUDA(c, cudaMemsetAsync(d_ovf_count, 0, sizeof(unsigned int), c->stream));
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
     if (nw == (uint32_t) kCellWarps)
-        k_ad_cells<kCellThreads, 16 / kCellWarps><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
+        k_ad_cells<kCellThreads, kCellCtas><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
                                                           &sm->counters, c->arena.as<unsigned char>(), Lo, c->ad_aux.as<unsigned char>(), Ax, capL, capR, kmax, nlayers_ref,
                                                           amax, d_cta_best, d_ovf_list, d_ovf_count, round);
     else
@@ -1357,10 +1405,10 @@ int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, uint32_t nw, int* p
         if (nw > (uint32_t) kCellWarps) { *per_sm = 0; return ADK_OK; }        // this CTA width is not available for such lunes
         c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM;
     }
-    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, 16 / kCellWarps>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, kCellCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     else ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kMaxCellWarps * 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     int occ = 0;
-    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kCellThreads, 16 / kCellWarps>, (int) nw * 32, smem));
+    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kCellThreads, kCellCtas>, (int) nw * 32, smem));
     else ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kMaxCellWarps * 32, 1>, (int) nw * 32, smem));
     *per_sm = occ > 0 ? occ : (nw > (uint32_t) kCellWarps ? 0 : 1);
     return ADK_OK;

@@ -49,7 +49,8 @@ struct AnchorInfo
     uint64_t nonempty_rows;
     uint64_t required;     // prefix-minimum change points beyond the first list element (Eppstein.cpp:228-232)
     unsigned long long lvl[3];   // best area (order-preserving bits) of the level in flight and its two neighbours
-    int32_t best_row_any, pad_;
+    int32_t best_row_any;
+    uint32_t defer_overflow;   // a row met more than 32 eps-collinear points beyond its vertex: outside the contract, reported as an error
     unsigned long long t0_ns, t1_ns;   // development: when the row pipeline started / finished this anchor (ADK_DEBUG)
 };
 
@@ -168,6 +169,7 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
                     const uint32_t d = ndef + __popc(dm & lt);
                     if (d < 32) s_def[warp][d] = p;
                 }
+                if (ndef + __popc(dm) > 32u && lane == 0) A.defer_overflow = 1u;     // never truncate silently
                 ns += __popc(sm); kept += __popc(km); ndef = min(32u, ndef + __popc(dm));
             }
             __syncwarp();
@@ -875,12 +877,17 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     }
     ADK_CUDA(c, cudaMemcpyAsync(P.info.data(), d_info, sizeof(AnchorInfo) * cnt, cudaMemcpyDeviceToHost, c->stream));
     ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (const AnchorInfo& A : P.info)
+        if (A.defer_overflow)
+        {
+            c->err = "area path: more than 32 collinear points beyond one polygon vertex (exactly degenerate input, outside the contract)";
+            return ADK_ERR_ARG;
+        }
 
     // table plan: ring of (cmax + 1) levels, or every level up to full_m
     // Ring mode runs the row pipeline (k_area_rows, bands of 32 levels); keeping every level for the walk back (one anchor)
     // stays on the level wavefront.  ADK_AREA_WAVEFRONT=1 forces the wavefront everywhere (A/B measurements).
-    static const bool force_wavefront = [] { const char* e = std::getenv("ADK_AREA_WAVEFRONT"); return e && e[0] == '1'; }();
-    const bool by_rows = full_m == 0 && !force_wavefront;
+    const bool by_rows = full_m == 0 && !c->area_wavefront;
     const uint64_t budget_entries = std::max<uint64_t>(workspace_budget(c, c->scratch5) / sizeof(double), 1u << 20);
     if (by_rows)
     {
@@ -922,8 +929,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             ADK_CUDA(c, cudaEventSynchronize(c->ev3));
             ADK_CUDA(c, cudaEventElapsedTime(dp_ms, c->ev2, c->ev3));
         }
-        static const bool debug = std::getenv("ADK_DEBUG") != nullptr;
-        if (debug)
+        if (c->debug)
         {
             std::vector<AnchorInfo> h(cnt);
             ADK_CUDA(c, cudaMemcpyAsync(h.data(), d_info, sizeof(AnchorInfo) * cnt, cudaMemcpyDeviceToHost, c->stream));

@@ -129,6 +129,7 @@ int adk_create(adk_ctx** out_ctx, int device)
     else c->budget = 8ull << 30;
     c->debug = getenv("ADK_DEBUG") != nullptr;
     if (const char* f = getenv("ADK_FORCE_CELL_WARPS")) c->force_cell_warps = (uint32_t) atoi(f);
+    if (const char* f = getenv("ADK_AREA_WAVEFRONT")) c->area_wavefront = f[0] == '1';
     *out_ctx = h;
     return ADK_OK;
 }

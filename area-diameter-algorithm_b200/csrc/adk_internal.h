@@ -31,6 +31,7 @@ struct Ctx
     bool own_stream = true;
     bool debug = false;            // ADK_DEBUG, read once in adk_create
     uint32_t force_cell_warps = 0; // ADK_FORCE_CELL_WARPS (experiments only), read once in adk_create
+    bool area_wavefront = false;   // ADK_AREA_WAVEFRONT=1 (A/B measurements of the old level wavefront), read once in adk_create
 
     // point set currently resident
     uint32_t n = 0;

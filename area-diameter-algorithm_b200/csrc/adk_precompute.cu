@@ -33,7 +33,10 @@ __global__ void k_angles(const double* __restrict__ x, const double* __restrict_
 }
 
 // One CTA per centre.  rank(p) = #neighbours that the comparator puts before p; O(n^2) per centre but
-// exact for the reference's (angle, then "near-tie and collinear -> nearer first") order.
+// exact for the reference's (angle, then "near-tie and collinear -> nearer first") order.  That comparator is not transitive
+// on eps-collinear triples (A before B before C before A is possible), so two points can count the same number of
+// predecessors: whenever that happens the final positions are taken from the total order (count, point index) instead, which
+// is a permutation whatever the comparator does (and equals the counts when they are distinct).
 template <int MODE>
 __global__ void k_order_rank(const double* __restrict__ x, const double* __restrict__ y, uint32_t n,
                              const double* __restrict__ ang, const double* __restrict__ d2c,
@@ -44,12 +47,17 @@ __global__ void k_order_rank(const double* __restrict__ x, const double* __restr
     double* sd = sm + n;        // squared distance from the centre
     double* sx = sm + 2 * n;
     double* sy = sm + 3 * n;
+    uint32_t* scnt = reinterpret_cast<uint32_t*>(sm + 4 * n);     // predecessor count of every point
+    uint32_t* shist = scnt + n;                                   // points per count
+    __shared__ int s_dup;
     const uint32_t c = blockIdx.x;
+    if (threadIdx.x == 0) s_dup = 0;
     for (uint32_t p = threadIdx.x; p < n; p += blockDim.x)
     {
         double a = ang[(size_t) c * n + p];
         if (MODE == 1 && a >= kPi) a = __dsub_rn(a, kPi);
         sk[p] = a; sd[p] = d2c[(size_t) c * n + p]; sx[p] = x[p]; sy[p] = y[p];
+        scnt[p] = 0xffffffffu; shist[p] = 0;
     }
     __syncthreads();
     const double cx = sx[c], cy = sy[c];
@@ -72,8 +80,28 @@ __global__ void k_order_rank(const double* __restrict__ x, const double* __restr
             else before = kq != kp ? kq > kp : q < p;
             cnt += before ? 1u : 0u;
         }
-        order[(size_t) c * (n - 1) + cnt] = (int32_t) p;
-        if (rank) rank[(size_t) c * n + p] = (uint16_t) cnt;
+        scnt[p] = cnt;
+        if (atomicAdd(&shist[cnt], 1u) != 0u) s_dup = 1;
+    }
+    __syncthreads();
+    const bool dup = s_dup != 0;
+    for (uint32_t p = threadIdx.x; p < n; p += blockDim.x)
+    {
+        if (p == c) continue;
+        uint32_t pos = scnt[p];
+        if (dup)
+        {
+            const uint32_t cp = pos;
+            pos = 0;
+            for (uint32_t q = 0; q < n; ++q)
+            {
+                if (q == c) continue;
+                const uint32_t cq = scnt[q];
+                pos += (cq < cp || (cq == cp && q < p)) ? 1u : 0u;
+            }
+        }
+        order[(size_t) c * (n - 1) + pos] = (int32_t) p;
+        if (rank) rank[(size_t) c * n + p] = (uint16_t) pos;
     }
 }
 
@@ -226,7 +254,7 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi)
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
     }
-    const size_t smem = sizeof(double) * 4 * n;
+    const size_t smem = sizeof(double) * 4 * n + sizeof(uint32_t) * 2 * n;
     if (need_cw && !c->have_cw)
     {
         ADK_TRY(ensure(c, c->cw, sizeof(int32_t) * (size_t) n * (n - 1)));

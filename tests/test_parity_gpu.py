@@ -168,6 +168,25 @@ def test_exactly_degenerate_inputs_terminate(pkg, solver):
     assert done >= 100
 
 
+def test_cyclic_eps_collinear_triple_gives_a_permutation(solver):
+    """The reference's clockwise comparator (Utils.cpp:295-309) is not transitive on eps-collinear triples: around (0,0) the
+    points A = (1e-3, 0), B = (2e-3, 1e-10), C = (100, 2e-6) compare A < B < C < A.  The device order must still be a
+    permutation of the neighbours for every centre (no slot written twice, none left stale), and the solves must run."""
+    rng = random.Random(11)
+    x = [0.0, 1e-3, 2e-3, 100.0] + [rng.uniform(-5, 5) for _ in range(12)]
+    y = [0.0, 0.0, 1e-10, 2e-6] + [rng.uniform(1, 9) for _ in range(12)]
+    n = len(x)
+    for _ in range(2):        # twice: grow-only buffers must not rely on stale contents either
+        cw = solver.cw_order(x, y)
+        for c in range(n):
+            assert sorted(cw[c]) == [p for p in range(n) if p != c], (c, cw[c])
+    a = solver.solve_area(x, y, None, 50.0, True)
+    if a["found"]:
+        check_witness(x, y, a, 50.0)
+    d = solver.solve_area_diameter(x, y, None, 50.0, 200.0, True)
+    assert d["found"] == a["found"]
+
+
 def test_benchmark_info_counters_match_the_reference(golden, solver):
     """MT::BenchmarkInfo (Utils.h:35-39; SURVEY 8f N2): myAllocatedEntriesCount / myRequiredEntriesCount of both paths equal the
     unmodified reference's on every frozen run (path A: table size and prefix-minimum change points, Eppstein.cpp:171-175,228-232;
