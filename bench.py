@@ -105,26 +105,78 @@ def measured_peaks():
 
 # ---------------------------------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi sampled every 200 ms during the timed region (B200_PROFILING.md's clocks line)."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md's clocks line).  NVML is queried from a
+    thread of this process every 500 ms (nvidia_ml_py); `nvidia-smi -lms` as a fallback.  A light sampler matters here: the
+    polling of a separate nvidia-smi process at 5 Hz slowed the timed kernels by several per cent."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, period_s=0.5):
         self.gpu = gpu_index
+        self.period = period_s
         self.proc = None
         self.path = None
+        self.thread = None
+        self.stop_flag = None
+        self.samples = []
+        self.reasons = set()
+        self.max_mhz = None
+
+    def _nvml_loop(self, nv, h):
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        while not self.stop_flag.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = int(get_reasons(h))
+                for name, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self.stop_flag.wait(self.period)
 
     def start(self):
+        if os.environ.get("ADK_BENCH_NO_CLOCKS"):
+            return
+        try:
+            import threading
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.gpu]) if vis and vis.split(",")[0].isdigit() else self.gpu
+            h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.stop_flag = threading.Event()
+            self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.thread = None
         try:
             fd, self.path = tempfile.mkstemp(prefix="adk_clocks_", suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "200"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+                                          "-lms", str(int(1000 * self.period))], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.thread is not None:
+            self.stop_flag.set()
+            self.thread.join(timeout=5)
+            sm = sorted(self.samples)
+            if sm:
+                out["sm_mhz"] = sm[len(sm) // 2]
+                out["samples"] = len(sm)
+            out["sm_max_mhz"] = self.max_mhz
+            out["reasons"] = sorted(self.reasons)
+            out["how"] = f"NVML from a thread of the bench process, every {self.period} s during the timed region"
+            return out
         if self.proc is None:
             return out
         try:
@@ -154,6 +206,7 @@ class ClockSampler:
             out["sm_mhz"] = sm[len(sm) // 2]
             out["samples"] = len(sm)
         out["reasons"] = sorted(reasons)
+        out["how"] = f"nvidia-smi -lms {int(1000 * self.period)} during the timed region"
         return out
 
 
