@@ -422,33 +422,61 @@ __device__ __forceinline__ void row_segment(uint32_t ns, uint32_t rd, uint32_t w
     cnt = base < end ? min(seg, end - base) : 0u;
 }
 
+// One anchor per thread-block CLUSTER (round 2).  Cell (row j, band b) only reads rows finished before j in bands <= b, so the
+// bands of an anchor form a pipeline: CTA r of the cluster sweeps bands r, r + CS, r + 2 CS, ... and may work on row j of band b
+// as soon as band b - 1 has finished row j (one row behind; a progress word per band in global memory, published after every row).
+// With CS = 1 this is the one-CTA-per-anchor sweep of round 1; with CS > 1 the heaviest anchor's critical path (96-120 ms at
+// n = 1000) is cut by the number of bands in flight, which is what anchors-over-8-GPUs needs.  The ring holds
+// ceil(cmax / 32) + CS bands: the oldest band in flight still reads ceil(cmax / 32) bands back while the newest one writes.
+// Bands past the last finite level may be started before the stop rule can know (at most CS - 1 of them): they produce +inf only.
+constexpr uint32_t kMaxRing = 256;           // bands on the board: covers any cmax < 32 * (kMaxRing - 8) = 7 936 > ADK_MAX_POINTS
+struct BandBoard
+{
+    unsigned long long prog[kMaxRing];      // (band + 1) << 32 | rows finished, per ring slot
+    unsigned int top[kMaxRing];             // highest finite level of the band in that slot (0 = none)
+    double area[kMaxRing];                  // its best area
+    unsigned int q, levels, pad[2];         // the anchor the cluster works on; levels executed (all bands)
+};
+
 __global__ void __launch_bounds__(kRowThreads, kRowThreads >= 512 ? 1 : 2)
 k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
             const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc,
             const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, uint64_t slot_entries, uint64_t K, double amax,
-            uint32_t cap_rows)
+            uint32_t cap_rows, BandBoard* __restrict__ boards)
 {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const uint32_t crank = cluster.block_rank(), CS = cluster.num_blocks();
+    const uint32_t cid = blockIdx.x / CS;
     __shared__ __align__(16) SrcRec s_rec[kRowWarps][32];
     __shared__ double s_tot[2][kRowWarps][32];
     __shared__ unsigned long long s_best[kBand];
     __shared__ long long s_req;
-    __shared__ unsigned int s_q;
-    __shared__ int s_row;
-    __shared__ uint32_t s_top, s_stop, s_levels;
-    __shared__ double s_best_area;
+    __shared__ int s_row, s_go;
     extern __shared__ uint32_t s_rowtab[];     // [cap_rows] source counts, [cap_rows] row bases (anchors with more rows read them from global memory)
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     SrcRec* st_rec = s_rec[warp];
+    BandBoard& B = boards[cid];
+    volatile unsigned long long* vprog = B.prog;
     for (;;)
     {
         __syncthreads();
-        if (threadIdx.x == 0) s_q = atomicAdd(queue, 1u);
-        __syncthreads();
-        const uint32_t q = s_q;
+        if (crank == 0 && threadIdx.x == 0)
+        {
+            B.q = atomicAdd(queue, 1u); B.levels = 0;
+            for (uint32_t t = 0; t < kMaxRing; ++t) { B.prog[t] = 0ull; B.top[t] = 0u; }
+            __threadfence();
+        }
+        cluster.sync();
+        const uint32_t q = *reinterpret_cast<volatile unsigned int*>(&B.q);
         if (q >= count) break;
         AnchorInfo& A = info[first + q];
         const uint32_t rows = A.rows, U = A.U, W = A.W, acap = (uint32_t) A.a, cmax = A.cmax;
         const uint32_t Wb = W / kBand, W8 = W * 8u;     // W8: bytes per table row
+        // bands this anchor can fill at all: a polygon above it has at most a + 2 points (the host sizes the ring with the same
+        // bound, so a band beyond it would wrap onto a band that is still being written)
+        const uint64_t top_level = K < (uint64_t) acap + 2 ? K : (uint64_t) acap + 2;
+        const uint32_t nb_cap = (uint32_t) (top_level >= 3 ? (top_level - 2 + kBand - 1) / kBand : 1);
         const SrcRec* arec = recs + A.meta_off;
         const uint32_t* ansrc = nsrc + A.row_off;
         const uint32_t* abase = rowbase + A.row_off;
@@ -457,24 +485,52 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
             for (uint32_t t = threadIdx.x; t < rows; t += blockDim.x) { s_rowtab[t] = ansrc[t]; s_rowtab[cap_rows + t] = abase[t]; }
             ansrc = s_rowtab; abase = s_rowtab + cap_rows;
         }
-        double* T = Tbuf + (size_t) blockIdx.x * slot_entries;      // the CTA's own table slot, reused for every anchor it takes
+        double* T = Tbuf + (size_t) cid * slot_entries;      // the cluster's own table slot, reused for every anchor it takes
         if (threadIdx.x == 0)
         {
-            s_top = 2; s_best_area = 0.0; s_req = 0; s_row = 0x7fffffff; s_stop = 0; s_levels = 0;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t0_ns));
+            s_req = 0; s_row = 0x7fffffff;
+            if (crank == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t0_ns));
         }
         __syncthreads();
         long long req = 0;
         if (U > 0)
         {
             uint32_t par = 0;                   // which s_tot buffer the next chunk uses
-            for (uint32_t b = 0;; ++b)
+            for (uint32_t b = crank;; b += CS)
             {
                 const uint32_t lo = 3u + kBand * b;
+                if ((uint64_t) lo > K || b >= nb_cap) break;
+                if (b >= CS)
+                {   // Bands finish in order, so every band up to b - CS (this CTA's previous one) is finished or about to be: had the
+                    // one-band-at-a-time sweep stopped by then (no deeper level can be finite, Eppstein.cpp:192 made adaptive), this
+                    // band is not needed.
+                    if (threadIdx.x == 0)
+                    {
+                        uint32_t ktop = 2;
+                        const uint32_t t0 = b + CS > kMaxRing ? b + CS - kMaxRing : 0u;      // bands whose board slot is still theirs
+                        for (uint32_t t = t0; t + CS <= b; ++t)
+                        {
+                            const uint32_t sl = t % kMaxRing;
+                            while (vprog[sl] != (((unsigned long long) (t + 1) << 32) | 0xffffffffull)) __nanosleep(64);
+                            __threadfence();
+                            const unsigned int tp = *reinterpret_cast<volatile unsigned int*>(&B.top[sl]);
+                            if (tp) ktop = tp;
+                        }
+                        const uint64_t lo_done = 3u + kBand * (b - CS);
+                        const uint64_t hi_done = K < lo_done + kBand - 1 ? K : lo_done + kBand - 1;
+                        s_go = (hi_done >= K || hi_done >= (uint64_t) ktop + cmax) ? 0 : 1;
+                    }
+                    __syncthreads();
+                    const int go = s_go;
+                    __syncthreads();
+                    if (!go) break;
+                }
                 const uint32_t m = lo + lane;
                 const bool active = (uint64_t) m <= K;
                 const uint32_t bm = b % Wb;
                 const uint32_t mypos = bm * kBand + lane;
+                const uint32_t bslot = b % kMaxRing, pslot = (b + kMaxRing - 1) % kMaxRing;
+                const unsigned long long ptag = (unsigned long long) b << 32;        // band b - 1 carries tag (b - 1) + 1
                 double band_best = INFINITY;    // warp 0: best final value of level m over the rows
                 // A row's sources are cut into rounds of at most kRowThreads, and a round evenly into one segment per warp.
                 // The source records of a round are requested one round ahead (they depend on nothing).
@@ -490,6 +546,23 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                 {
                     const uint32_t ns = ansrc[jj];
                     if (ns == 0) continue;
+                    if (b > 0 && CS > 1)
+                    {   // One row behind: band b - 1 must have finished row jj itself.  Then, by induction over the bands, every
+                        // earlier band has finished row jj as well — a source of this row reads rows before jj up to
+                        // ceil(cmax / 32) bands back, and "band b - 1 finished the rows before jj" alone would leave band b - 2 one
+                        // row short of that.
+                        if (lane == 0)
+                        {
+                            for (;;)
+                            {
+                                const unsigned long long pv_ = vprog[pslot];
+                                if ((pv_ >> 32) == (unsigned long long) b && (uint32_t) pv_ >= jj + 1u) break;
+                                __nanosleep(64);
+                            }
+                            __threadfence();
+                        }
+                        __syncwarp();
+                    }
                     const uint32_t obase = abase[jj];
                     const uint32_t rounds = (ns + kRowThreads - 1) / kRowThreads;
                     double carry = INFINITY;
@@ -518,7 +591,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                             const SrcRec r = st_rec[u];
                             const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
                             if (r.gidx != kNoPrev && active && c + 3u <= m)
-                            {   // level m - c = 3 + 32 b + (lane - c): its band is b + floor((lane - c) / 32), at most Wb - 1 bands back
+                            {   // level m - c = 3 + 32 b + (lane - c): its band is b + floor((lane - c) / 32), at most ceil(cmax / 32) bands back
                                 const int d = (int) lane - (int) c;
                                 int slot = (int) bm + (d >> 5);
                                 if (slot < 0) slot += (int) Wb;
@@ -576,40 +649,60 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                     }
                     band_best = fmin(band_best, carry);
                     __syncthreads();            // the row is complete before any warp reads it as a source of the next rows
+                    if (CS > 1 && threadIdx.x == 0) { __threadfence(); vprog[bslot] = ((unsigned long long) (b + 1) << 32) | (jj + 1); }
                 }
                 if (warp == 0) s_best[lane] = area_bits(band_best);
                 __syncthreads();
                 if (threadIdx.x == 0)
                 {
+                    unsigned int tp = 0; double ar = 0.0;
                     for (uint32_t l = 0; l < kBand; ++l)
-                        if (s_best[l] != kInfBits) { s_top = lo + l; s_best_area = bits_area(s_best[l]); }
+                        if (s_best[l] != kInfBits) { tp = lo + l; ar = bits_area(s_best[l]); }
                     const uint64_t hi = K < (uint64_t) lo + kBand - 1 ? K : (uint64_t) lo + kBand - 1;
-                    s_levels = (uint32_t) (hi - 2);
-                    s_stop = (hi >= K || hi >= (uint64_t) s_top + cmax) ? 1u : 0u;      // no deeper level can be finite
+                    B.top[bslot] = tp; B.area[bslot] = ar;
+                    atomicAdd(&B.levels, (unsigned int) (hi - lo + 1));
+                    __threadfence();
+                    vprog[bslot] = ((unsigned long long) (b + 1) << 32) | 0xffffffffull;      // the whole band is finished
                 }
                 __syncthreads();
-                if (s_stop) break;
             }
-            const uint32_t top = s_top;
+        }
+        for (int o = 16; o; o >>= 1) req += __shfl_xor_sync(0xffffffffu, req, o);
+        if (lane == 0 && req) atomicAdd(reinterpret_cast<unsigned long long*>(&s_req), (unsigned long long) req);
+        __syncthreads();
+        if (threadIdx.x == 0 && s_req) { atomicAdd(reinterpret_cast<unsigned long long*>(&A.required), (unsigned long long) s_req); __threadfence(); }
+        cluster.sync();                         // every band of the anchor is finished
+        // The answer of the anchor: the highest finite level over the bands that the one-band-at-a-time sweep would have run (bands
+        // started beyond its stopping point hold +inf only), and the first row (in j order) that attains the best area there
+        // (Eppstein.cpp:219-224).  The board keeps the last kMaxRing bands; a finite level is never more than cmax levels from the end.
+        uint32_t top = 2; double best_area = 0.0;
+        if (U > 0)
+        {
+            for (uint32_t b = 0; (uint64_t) (3u + kBand * b) <= K && b < nb_cap; ++b)
+            {
+                const unsigned long long tag = vprog[b % kMaxRing] >> 32;
+                if (tag < (unsigned long long) (b + 1)) break;                 // this band was never started: the sweep had stopped
+                if (tag > (unsigned long long) (b + 1)) continue;              // its slot belongs to a later band by now
+                const unsigned int tp = *reinterpret_cast<volatile unsigned int*>(&B.top[b % kMaxRing]);
+                if (tp) { top = tp; best_area = *reinterpret_cast<volatile double*>(&B.area[b % kMaxRing]); }
+            }
             if (top > 2)
-            {   // first row (in j order) that attains the best area at the best level (Eppstein.cpp:219-224)
-                const double best_area = s_best_area;
+            {
                 const uint32_t tp = level_pos(top, Wb);
-                for (uint32_t jj = threadIdx.x; jj < rows; jj += blockDim.x)
+                for (uint32_t jj = crank * blockDim.x + threadIdx.x; jj < rows; jj += CS * blockDim.x)
                 {
                     const uint32_t ns = ansrc[jj];
                     if (ns && __ldcg(&T[(size_t) (abase[jj] + ns - 1) * W + tp]) == best_area) atomicMin(&s_row, (int) jj);
                 }
             }
         }
-        for (int o = 16; o; o >>= 1) req += __shfl_xor_sync(0xffffffffu, req, o);
-        if (lane == 0 && req) atomicAdd(reinterpret_cast<unsigned long long*>(&s_req), (unsigned long long) req);
         __syncthreads();
-        if (threadIdx.x == 0)
+        if (threadIdx.x == 0 && s_row != 0x7fffffff) { atomicMin(&A.best_row_any, s_row); __threadfence(); }
+        cluster.sync();
+        if (crank == 0 && threadIdx.x == 0)
         {
-            A.levels_run = s_levels;
-            A.required = (uint64_t) s_req;
-            if (s_top > 2) { A.best_m = s_top; A.best_area = s_best_area; A.best_row = s_row; }
+            A.levels_run = *reinterpret_cast<volatile unsigned int*>(&B.levels);
+            if (top > 2) { A.best_m = top; A.best_area = best_area; A.best_row = *reinterpret_cast<volatile int*>(&A.best_row_any); }
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t1_ns));
         }
     }
@@ -891,36 +984,53 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     const uint64_t budget_entries = std::max<uint64_t>(workspace_budget(c, c->scratch5) / sizeof(double), 1u << 20);
     if (by_rows)
     {
-        // One launch for all anchors: every resident CTA owns one table slot sized for the largest anchor and reuses it for the
-        // anchors it pulls from the queue, so the table memory is (resident CTAs) x (largest ring), whatever the number of anchors.
-        uint64_t slot_entries = 1;
+        // One launch for all anchors: every resident CLUSTER owns one table slot sized for the largest anchor and reuses it for the
+        // anchors it pulls from the queue, so the table memory is (resident clusters) x (largest ring), whatever the number of anchors.
+        // Cluster size: 1 while there are anchors enough to keep every SM busy (nothing is speculated then); with few anchors
+        // per GPU (a shard of a multi-GPU solve) the bands of an anchor are pipelined over 2, 4 or 8 CTAs, which shortens the
+        // heaviest anchor's critical path.
         uint32_t max_rows = 1;
-        for (uint32_t t = 0; t < cnt; ++t)
-        {
-            AnchorInfo& A = P.info[t];
-            // bands: enough to reach back cmax levels, never more than the levels an anchor with this many rows can fill
-            const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
-            const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
-            const uint64_t W = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + 1, nb_max) * kBand;
-            A.W = (uint32_t) W; A.t_off = 0;
-            slot_entries = std::max<uint64_t>(slot_entries, W * (uint64_t) A.U);
-            max_rows = std::max<uint32_t>(max_rows, (uint32_t) A.a);
-        }
-        slot_entries = (slot_entries + 31) & ~(uint64_t) 31;
+        for (uint32_t t = 0; t < cnt; ++t) max_rows = std::max<uint32_t>(max_rows, (uint32_t) P.info[t].a);
         const uint32_t cap_rows = std::min<uint32_t>(max_rows, 4096);
         const size_t smem = sizeof(uint32_t) * 2 * cap_rows;
         int per_sm = 0;
         ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_area_rows, kRowThreads, smem));
         const uint64_t resident = (uint64_t) std::max(per_sm, 1) * (uint64_t) c->sm_count;
-        const uint64_t slots = std::min<uint64_t>(std::min<uint64_t>(cnt, resident), budget_entries / slot_entries);
+        uint32_t CS = 1;
+        if (c->area_cluster) CS = c->area_cluster;
+        else while (CS < 8 && (uint64_t) cnt * (CS * 2) <= resident) CS *= 2;
+        uint64_t slot_entries = 1;
+        for (uint32_t t = 0; t < cnt; ++t)
+        {
+            AnchorInfo& A = P.info[t];
+            // bands: enough to reach back cmax levels from the oldest band in flight, never more than the levels an anchor with this
+            // many rows can fill
+            const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
+            const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
+            const uint64_t W = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + CS, nb_max) * kBand;
+            A.W = (uint32_t) W; A.t_off = 0;
+            slot_entries = std::max<uint64_t>(slot_entries, W * (uint64_t) A.U);
+        }
+        slot_entries = (slot_entries + 31) & ~(uint64_t) 31;
+        const uint64_t slots = std::min<uint64_t>(std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1)), budget_entries / slot_entries);
         if (slots == 0) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
         ADK_TRY(ensure(c, c->scratch5, sizeof(double) * slots * slot_entries));
+        ADK_TRY(ensure(c, c->area_boards, sizeof(BandBoard) * slots));
         ADK_CUDA(c, cudaMemcpyAsync(d_info, P.info.data(), sizeof(AnchorInfo) * cnt, cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(c->small.p, 0, sizeof(unsigned int) * 2, c->stream));
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
         SmallOut* so_ = c->small.as<SmallOut>();
-        k_area_rows<<<(uint32_t) slots, kRowThreads, smem, c->stream>>>(d_info, 0, cnt, &so_->queue, d_recs, d_nsrc, d_rowbase,
-                                                                       c->scratch5.as<double>(), slot_entries, K, amax, cap_rows);
+        {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((uint32_t) slots * CS); cfg.blockDim = dim3(kRowThreads); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            ADK_CUDA(c, cudaLaunchKernelEx(&cfg, k_area_rows, d_info, 0u, cnt, &so_->queue, (const SrcRec*) d_recs, (const uint32_t*) d_nsrc,
+                                           (const uint32_t*) d_rowbase, c->scratch5.as<double>(), (uint64_t) slot_entries, K, amax, cap_rows,
+                                           c->area_boards.as<BandBoard>()));
+        }
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
         ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
@@ -937,7 +1047,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             unsigned long long tmin = ~0ull, tmax = 0; double sum = 0.0, longest = 0.0;
             for (auto& a : h) { tmin = std::min(tmin, a.t0_ns); tmax = std::max(tmax, a.t1_ns); sum += (double) (a.t1_ns - a.t0_ns); longest = std::max(longest, (double) (a.t1_ns - a.t0_ns)); }
             std::fprintf(stderr, "[adk] rows kernel: %u anchors on %llu CTAs, span %.2f ms, sum of anchor times %.2f ms, longest anchor %.2f ms\n",
-                         cnt, (unsigned long long) slots, (tmax - tmin) * 1e-6, sum * 1e-6, longest * 1e-6);
+                         cnt, (unsigned long long) slots * CS, (tmax - tmin) * 1e-6, sum * 1e-6, longest * 1e-6);
         }
         return ADK_OK;
     }

@@ -130,6 +130,7 @@ int adk_create(adk_ctx** out_ctx, int device)
     c->debug = getenv("ADK_DEBUG") != nullptr;
     if (const char* f = getenv("ADK_FORCE_CELL_WARPS")) c->force_cell_warps = (uint32_t) atoi(f);
     if (const char* f = getenv("ADK_AREA_WAVEFRONT")) c->area_wavefront = f[0] == '1';
+    if (const char* f = getenv("ADK_AREA_CLUSTER")) { const int v = atoi(f); if (v == 1 || v == 2 || v == 4 || v == 8) c->area_cluster = (uint32_t) v; }
     *out_ctx = h;
     return ADK_OK;
 }
@@ -142,7 +143,7 @@ void adk_destroy(adk_ctx* h)
     if (c->stream) cudaStreamSynchronize(c->stream);
     adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
                            &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
-                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux};
+                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards};
     for (adk::DevBuf* b : bufs) adk::free_buf(*b);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->ev0) cudaEventDestroy(c->ev0);

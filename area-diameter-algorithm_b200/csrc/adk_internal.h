@@ -31,6 +31,7 @@ struct Ctx
     bool own_stream = true;
     bool debug = false;            // ADK_DEBUG, read once in adk_create
     uint32_t force_cell_warps = 0; // ADK_FORCE_CELL_WARPS (experiments only), read once in adk_create
+    uint32_t area_cluster = 0;     // ADK_AREA_CLUSTER=1|2|4|8: CTAs per anchor in the row sweep (0 = chosen per launch), read once in adk_create
     bool area_wavefront = false;   // ADK_AREA_WAVEFRONT=1 (A/B measurements of the old level wavefront), read once in adk_create
 
     // point set currently resident
@@ -50,6 +51,7 @@ struct Ctx
     DevBuf arena;                  // AD per-CTA slices (directories + layer vectors)
     DevBuf ad_order, ad_ovf, ad_cta;   // AD: processing order, overflow lists, per-CTA bests
     DevBuf ad_aux;                 // AD: per-CTA order / suffix-start tables and spill workspaces
+    DevBuf area_boards;            // A: per-cluster band progress boards of the row sweep
     uint64_t ad_V = 0, ad_Q = 0;   // per-slice capacities the arena was initialised for (grow-only)
     uint32_t ad_L = 0, ad_slices = 0;
     size_t ad_slice_bytes = 0;
