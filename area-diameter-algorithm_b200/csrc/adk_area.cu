@@ -998,7 +998,20 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
         const uint64_t resident = (uint64_t) std::max(per_sm, 1) * (uint64_t) c->sm_count;
         uint32_t CS = 1;
         if (c->area_cluster) CS = c->area_cluster;
-        else while (CS < 8 && (uint64_t) cnt * (CS * 2) <= resident) CS *= 2;
+        else
+        {   // Anchor times go like their source counts U.  One launch lasts max(all the work over the resident CTAs, the heaviest
+            // anchor alone); a cluster of CS CTAs divides the second term by `gain` (bands in flight) and multiplies the first by
+            // `waste` (bands started past the stopping point, the one-row lag) — both measured at n = 1000 (profiles/r2_area_*).
+            static const double waste[4] = {1.0, 1.25, 1.6, 2.2}, gain[4] = {1.0, 1.9, 3.4, 5.5};
+            double sumU = 0.0, maxU = 0.0;
+            for (uint32_t t = 0; t < cnt; ++t) { sumU += (double) P.info[t].U; maxU = std::max(maxU, (double) P.info[t].U); }
+            double best = 0.0;
+            for (int v = 0; v < 4; ++v)
+            {
+                const double t = std::max(sumU * waste[v] / (double) resident, maxU / gain[v]);
+                if (v == 0 || t < 0.95 * best) { best = v == 0 ? t : std::min(best, t); CS = 1u << v; }
+            }
+        }
         uint64_t slot_entries = 1;
         for (uint32_t t = 0; t < cnt; ++t)
         {
