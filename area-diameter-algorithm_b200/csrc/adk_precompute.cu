@@ -1,7 +1,7 @@
 // adk_precompute.cu — geometry precompute shared by both DP paths (sm_100a).
 //
 //  k_angles      : angle / squared distance of every point seen from every centre          (CustomMath.cpp:56-65, 15-20)
-//  k_order_rank  : per-centre neighbour orders by rank-counting with the reference's comparator
+//  k_order_sort  : per-centre neighbour orders: segmented radix sort + exact-comparator fix-up of the near-tie windows
 //                    mode 0: clockwise list                                                   (Utils.cpp:295-316)
 //                    mode 1: direction-mod-pi list = the one cyclic sequence every slope list of
 //                            Eppstein.cpp:62-114 is a rotation of
@@ -32,47 +32,122 @@ __global__ void k_angles(const double* __restrict__ x, const double* __restrict_
     }
 }
 
-// One CTA per centre.  rank(p) = #neighbours that the comparator puts before p; O(n^2) per centre but
-// exact for the reference's (angle, then "near-tie and collinear -> nearer first") order.  That comparator is not transitive
-// on eps-collinear triples (A before B before C before A is possible), so two points can count the same number of
-// predecessors: whenever that happens the final positions are taken from the total order (count, point index) instead, which
-// is a permutation whatever the comparator does (and equals the counts when they are distinct).
+// Angular order around every centre (north_star stage 2): a SEGMENTED RADIX SORT, one segment = one centre = one CTA.
+//   1. key = order-preserving 64-bit image of the angle (angles are >= 0, so the bit pattern is monotone), inverted because the
+//      reference sorts angle-DESCENDING (Utils.cpp:295-316); payload = the point index.  LSD radix sort, 8 passes of 8 bits, in shared
+//      memory: per pass a histogram per warp, one scan over (digit, warp), and a stable scatter in which the lanes of a warp rank
+//      themselves inside their digit with __match_any_sync.  Stable, so equal angles keep index order (the comparator's last rule).
+//   2. fix-up with the EXACT comparator: the reference orders two points whose angles differ by < 1e-6 AND that are eps-collinear with
+//      the centre by distance instead (nearer first).  In the sorted list the points within 1e-6 of p form a window around p, so
+//      the number of points the comparator puts before p is (window start) + (exact tests inside the window) — the same count the
+//      round-1 kernel formed by testing p against all n points.
+//   3. that comparator is not transitive on eps-collinear triples (A before B before C before A is possible), so two points can
+//      count the same number of predecessors: whenever that happens the final positions are taken from the total order
+//      (count, point index) instead, which is a permutation whatever the comparator does (and equals the counts when they are distinct).
+// O(n) work per point instead of O(n^2): n = 4096 sorts in well under 2 ms; the round-1 rank counting was ~70 G comparisons there.
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps = kSortThreads / 32;
+
 template <int MODE>
-__global__ void k_order_rank(const double* __restrict__ x, const double* __restrict__ y, uint32_t n,
-                             const double* __restrict__ ang, const double* __restrict__ d2c,
-                             int32_t* __restrict__ order, uint16_t* __restrict__ rank)
+__global__ void __launch_bounds__(kSortThreads)
+k_order_sort(const double* __restrict__ x, const double* __restrict__ y, uint32_t n,
+             const double* __restrict__ ang, const double* __restrict__ d2c,
+             int32_t* __restrict__ order, uint16_t* __restrict__ rank)
 {
-    extern __shared__ double sm[];
-    double* sk = sm;            // sort key (angle, or angle mod pi)
-    double* sd = sm + n;        // squared distance from the centre
-    double* sx = sm + 2 * n;
-    double* sy = sm + 3 * n;
-    uint32_t* scnt = reinterpret_cast<uint32_t*>(sm + 4 * n);     // predecessor count of every point
-    uint32_t* shist = scnt + n;                                   // points per count
+    extern __shared__ __align__(16) unsigned char sm_raw[];
+    const uint32_t m = n - 1;                                      // keys per segment
+    // [keyA m x u64][keyB m x u64][idxA m x u16][idxB m x u16][sx n][sy n][sd n] ; counts / histogram alias the spare sort buffer
+    unsigned long long* keyA = reinterpret_cast<unsigned long long*>(sm_raw);
+    unsigned long long* keyB = keyA + m;
+    double* sx = reinterpret_cast<double*>(keyB + m);
+    double* sy = sx + n;
+    double* sd = sy + n;
+    uint16_t* idxA = reinterpret_cast<uint16_t*>(sd + n);
+    uint16_t* idxB = idxA + m;
+    __shared__ uint32_t s_hist[kSortWarps][256];
+    __shared__ uint32_t s_digit_base[256];
+    __shared__ uint32_t s_warp_tot[kSortWarps];
     __shared__ int s_dup;
     const uint32_t c = blockIdx.x;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_dup = 0;
     for (uint32_t p = threadIdx.x; p < n; p += blockDim.x)
     {
+        sx[p] = x[p]; sy[p] = y[p]; sd[p] = d2c[(size_t) c * n + p];
+        if (p == c) continue;
         double a = ang[(size_t) c * n + p];
         if (MODE == 1 && a >= kPi) a = __dsub_rn(a, kPi);
-        sk[p] = a; sd[p] = d2c[(size_t) c * n + p]; sx[p] = x[p]; sy[p] = y[p];
-        scnt[p] = 0xffffffffu; shist[p] = 0;
+        const uint32_t t = p < c ? p : p - 1;
+        keyA[t] = ~(unsigned long long) __double_as_longlong(a);      // ascending in the inverted bits = descending in the angle
+        idxA[t] = (uint16_t) p;
     }
     __syncthreads();
-    const double cx = sx[c], cy = sy[c];
-    for (uint32_t p = threadIdx.x; p < n; p += blockDim.x)
+    // ---- 1. LSD radix sort of (key, index), 8 bits per pass; warp w owns the contiguous slice [w * per, (w + 1) * per) of the input
+    const uint32_t per = ((m + kSortWarps - 1) / kSortWarps + 31) & ~31u;
+    const uint32_t w0 = min(m, warp * per), w1 = min(m, w0 + per);
+    unsigned long long* kin = keyA; unsigned long long* kout = keyB;
+    uint16_t* iin = idxA; uint16_t* iout = idxB;
+    for (uint32_t shift = 0; shift < 64; shift += 8)
     {
-        if (p == c) continue;
-        const double kp = sk[p], dp = sd[p], px = sx[p], py = sy[p];
-        uint32_t cnt = 0;
-        for (uint32_t q = 0; q < n; ++q)
+        for (uint32_t t = threadIdx.x; t < kSortWarps * 256; t += blockDim.x) (&s_hist[0][0])[t] = 0;
+        __syncthreads();
+        for (uint32_t t = w0 + lane; t < w1; t += 32) atomicAdd(&s_hist[warp][(uint32_t) (kin[t] >> shift) & 255u], 1u);
+        __syncthreads();
+        {   // exclusive scan over (digit major, warp minor): thread d owns digit d
+            const uint32_t d = threadIdx.x;                       // kSortThreads == 256 digits
+            uint32_t col[kSortWarps], tot = 0;
+            for (int w = 0; w < kSortWarps; ++w) { col[w] = s_hist[w][d]; tot += col[w]; }
+            uint32_t incl = tot;
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if ((int) lane >= o) incl += v; }
+            if (lane == 31) s_warp_tot[warp] = incl;
+            __syncthreads();
+            uint32_t base = incl - tot;
+            for (uint32_t w = 0; w < warp; ++w) base += s_warp_tot[w];
+            for (int w = 0; w < kSortWarps; ++w) { s_hist[w][d] = base; base += col[w]; }
+        }
+        __syncthreads();
+        for (uint32_t t0 = w0; t0 < w1; t0 += 32)
         {
-            if (q == c || q == p) continue;
-            const double kq = sk[q];
+            const uint32_t t = t0 + lane;
+            const bool have = t < w1;
+            const unsigned long long k = have ? kin[t] : 0ull;
+            const uint32_t d = have ? (uint32_t) (k >> shift) & 255u : 256u + lane;      // idle lanes: distinct pseudo digits
+            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const uint32_t r = __popc(peers & ((1u << lane) - 1u));
+            uint32_t pos = 0;
+            if (have) pos = s_hist[warp][d] + r;
+            __syncwarp();
+            if (have && r == 0) s_hist[warp][d] += __popc(peers);                        // the group's first lane moves the cursor on
+            __syncwarp();
+            if (have) { kout[pos] = k; iout[pos] = iin[t]; }
+        }
+        __syncthreads();
+        unsigned long long* tk = kin; kin = kout; kout = tk;
+        uint16_t* ti = iin; iin = iout; iout = ti;
+    }
+    // after 8 passes the sorted data is back in (keyA, idxA); keyB is free: counts and their histogram live there
+    uint32_t* scnt = reinterpret_cast<uint32_t*>(keyB);          // predecessor count of the point at sorted position t
+    uint32_t* shist = scnt + m;                                   // points per count   (2 x 4 m bytes <= 8 m bytes)
+    for (uint32_t t = threadIdx.x; t < m; t += blockDim.x) shist[t] = 0;
+    __syncthreads();
+    // ---- 2. exact comparator inside the near-tie window (ArePointsClockwise(centre, q, p), Utils.cpp:295-309)
+    const double cx = sx[c], cy = sy[c];
+    for (uint32_t t = threadIdx.x; t < m; t += blockDim.x)
+    {
+        const uint32_t p = iin[t];
+        const double kp = __longlong_as_double((long long) ~kin[t]);
+        const double dp = sd[p], px = sx[p], py = sy[p];
+        uint32_t lo = t;                                          // window = sorted positions whose key is within the tolerance of kp
+        while (lo > 0 && fabs(__dsub_rn(__longlong_as_double((long long) ~kin[lo - 1]), kp)) < kAngleTol) --lo;
+        uint32_t cnt = lo;                                        // everything before the window has a clearly larger angle
+        for (uint32_t u = lo; u < m; ++u)
+        {
+            if (u == t) continue;
+            const double kq = __longlong_as_double((long long) ~kin[u]);
+            if (!(fabs(__dsub_rn(kq, kp)) < kAngleTol)) { if (u > t) break; else continue; }
+            const uint32_t q = iin[u];
             bool before;
-            // ArePointsClockwise(centre, q, p): Utils.cpp:295-309
-            if (fabs(__dsub_rn(kq, kp)) < kAngleTol && near_zero(signed_area(cx, cy, sx[q], sy[q], px, py)))
+            if (near_zero(signed_area(cx, cy, sx[q], sy[q], px, py)))
             {
                 const double dq = sd[q];
                 before = dq != dp ? dq < dp : q < p;
@@ -80,27 +155,27 @@ __global__ void k_order_rank(const double* __restrict__ x, const double* __restr
             else before = kq != kp ? kq > kp : q < p;
             cnt += before ? 1u : 0u;
         }
-        scnt[p] = cnt;
+        scnt[t] = cnt;
         if (atomicAdd(&shist[cnt], 1u) != 0u) s_dup = 1;
     }
     __syncthreads();
+    // ---- 3. placement
     const bool dup = s_dup != 0;
-    for (uint32_t p = threadIdx.x; p < n; p += blockDim.x)
+    for (uint32_t t = threadIdx.x; t < m; t += blockDim.x)
     {
-        if (p == c) continue;
-        uint32_t pos = scnt[p];
+        const uint32_t p = iin[t];
+        uint32_t pos = scnt[t];
         if (dup)
         {
             const uint32_t cp = pos;
             pos = 0;
-            for (uint32_t q = 0; q < n; ++q)
+            for (uint32_t u = 0; u < m; ++u)
             {
-                if (q == c) continue;
-                const uint32_t cq = scnt[q];
+                const uint32_t cq = scnt[u], q = iin[u];
                 pos += (cq < cp || (cq == cp && q < p)) ? 1u : 0u;
             }
         }
-        order[(size_t) c * (n - 1) + pos] = (int32_t) p;
+        order[(size_t) c * m + pos] = (int32_t) p;
         if (rank) rank[(size_t) c * n + p] = (uint16_t) pos;
     }
 }
@@ -254,12 +329,12 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi)
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
     }
-    const size_t smem = sizeof(double) * 4 * n + sizeof(uint32_t) * 2 * n;
+    const size_t smem = (sizeof(unsigned long long) * 2 + sizeof(uint16_t) * 2) * (size_t) (n - 1) + sizeof(double) * 3 * (size_t) n + 64;
     if (need_cw && !c->have_cw)
     {
         ADK_TRY(ensure(c, c->cw, sizeof(int32_t) * (size_t) n * (n - 1)));
-        ADK_CUDA(c, cudaFuncSetAttribute(k_order_rank<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        k_order_rank<0><<<n, 256, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(),
+        ADK_CUDA(c, cudaFuncSetAttribute(k_order_sort<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        k_order_sort<0><<<n, kSortThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(),
                                                      c->d2c.as<double>(), c->cw.as<int32_t>(), nullptr);
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
@@ -269,8 +344,8 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi)
     {
         ADK_TRY(ensure(c, c->modpi, sizeof(int32_t) * (size_t) n * (n - 1)));
         ADK_TRY(ensure(c, c->rank, sizeof(uint16_t) * (size_t) n * n));
-        ADK_CUDA(c, cudaFuncSetAttribute(k_order_rank<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        k_order_rank<1><<<n, 256, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(),
+        ADK_CUDA(c, cudaFuncSetAttribute(k_order_sort<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        k_order_sort<1><<<n, kSortThreads, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), n, c->ang.as<double>(),
                                                      c->d2c.as<double>(), c->modpi.as<int32_t>(), c->rank.as<uint16_t>());
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());

@@ -23,12 +23,31 @@ STAGE_SETS = ["tests/10/0", "tests/30/3", "tests/60/1", "tests/100/2", "uniform/
 def test_count_tables_and_orders(golden, solver, oracle, name):
     x, y = xy(golden["points"][name])
     assert solver.count_tables(x, y) == oracle.count_tables(x, y)          # Utils.cpp:74-143
-    if len(x) <= 400:
-        assert solver.cw_order(x, y) == oracle.cw_order(x, y)              # Utils.cpp:311-316
+    assert solver.cw_order(x, y) == oracle.cw_order(x, y)                  # Utils.cpp:311-316 (segmented radix sort + fix-up), up to real/0 (n = 699)
     rng = random.Random(5)
     n = len(x)
     tri = [tuple(rng.sample(range(n), 3)) for _ in range(300)]
     assert solver.points_in_triangle(x, y, tri) == oracle.points_in_triangle(x, y, tri)   # Utils.cpp:251-293
+
+
+def test_clockwise_orders_at_scale_and_on_near_ties(solver, oracle):
+    """Stage 2 beyond the fixture sizes: n = 1500 random points (every centre's list equal to the oracle's), and a set with many
+    exact and near ties in angle (points on common rays through a centre, points 1e-7 rad apart): the radix sort's fix-up must
+    reproduce the reference comparator's near-tie rule (|dAngle| < 1e-6 and eps-collinear -> nearer first)."""
+    rng = random.Random(99)
+    x = [rng.uniform(0, 20) for _ in range(1500)]
+    y = [rng.uniform(0, 20) for _ in range(1500)]
+    assert solver.cw_order(x, y) == oracle.cw_order(x, y)
+    # rays through (10, 10): several points per ray (eps-collinear with the centre) plus partners rotated by 1e-7 rad
+    x, y = [10.0], [10.0]
+    for k in range(40):
+        a = 2 * math.pi * k / 40 + 0.01
+        for r in (1.0, 2.5, 4.0):
+            x.append(10.0 + r * math.cos(a)); y.append(10.0 + r * math.sin(a))
+        x.append(10.0 + 3.0 * math.cos(a + 1e-7)); y.append(10.0 + 3.0 * math.sin(a + 1e-7))
+    got, want = solver.cw_order(x, y), oracle.cw_order(x, y)
+    assert got[0] == want[0]                                   # the centre of the rays
+    assert got == want
 
 
 @pytest.mark.parametrize("name", ["tests/20/0", "tests/50/4", "uniform/0/3", "real/9/0", "real/6/0"])
