@@ -60,6 +60,7 @@ EXPORTS = [
     "adk_merge", "adk_area_partial_dev", "adk_area_diameter_partial_dev",
     "adk_batch_assign", "adk_solve_batch",
     "adk_count_tables", "adk_points_in_triangle", "adk_cw_order", "adk_slope_order", "adk_lune_lists",
+    "adk_solve_area_tiled",
     "adk_multi_create", "adk_multi_destroy", "adk_multi_last_error", "adk_multi_device_count", "adk_multi_set_reuse",
     "adk_multi_solve_area", "adk_multi_solve_area_diameter", "adk_multi_last_stats",
 ]
@@ -281,6 +282,24 @@ class Solver:
     @staticmethod
     def _stats(s):
         return {k: (float(getattr(s, k)) if k.endswith("_ms") else int(getattr(s, k))) for k, _ in AdkStats._fields_}
+
+    def solve_area_tiled(self, points, patch_size=3.0, step_size=3 * 0.66, kmax=None, amax=4.0):
+        """run_area_only_tiled (Area-Selector) in one C call, windows generated on the device (adk_solve_area_tiled).
+        Returns {found, area, count, hull (indices into `points`), diam, patches, solved}."""
+        n = len(points)
+        ax, ay = _darr([p[0] for p in points]), _darr([p[1] for p in points])
+        res = AdkResult()
+        hull = (ctypes.c_uint32 * max(n, 1))()
+        st = (ctypes.c_uint64 * 2)()
+        self.lib.adk_solve_area_tiled.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_double,
+                                                  ctypes.c_double, ctypes.c_uint64, ctypes.c_double, ctypes.POINTER(AdkResult),
+                                                  ctypes.c_void_p, ctypes.c_void_p]
+        self._check(self.lib.adk_solve_area_tiled(self.ctx, ctypes.cast(ax, ctypes.c_void_p), ctypes.cast(ay, ctypes.c_void_p), n,
+                                                  float(patch_size), float(step_size), _k(kmax), float(amax), ctypes.byref(res),
+                                                  ctypes.cast(hull, ctypes.c_void_p), ctypes.cast(st, ctypes.c_void_p)), "adk_solve_area_tiled")
+        out = self._pack(res, hull)
+        out["patches"], out["solved"] = int(st[0]), int(st[1])
+        return out
 
     # ---- whole solves -------------------------------------------------------------------------------------------
     def solve_area(self, x, y, kmax=None, amax=float("inf"), reconstruct=True, counters=False):

@@ -143,7 +143,7 @@ void adk_destroy(adk_ctx* h)
     if (c->stream) cudaStreamSynchronize(c->stream);
     adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
                            &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
-                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards};
+                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards, &c->tile_buf};
     for (adk::DevBuf* b : bufs) adk::free_buf(*b);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->ev0) cudaEventDestroy(c->ev0);
@@ -376,6 +376,14 @@ int adk_solve_batch(adk_ctx* h, const adk_instance* inst, uint32_t ninst, uint32
         if (rc != ADK_OK) return rc;
     }
     return ADK_OK;
+}
+
+int adk_solve_area_tiled(adk_ctx* h, const double* x, const double* y, uint32_t n, double patch_size, double step_size,
+                         uint64_t kmax, double amax, adk_result* out, uint32_t* hull, adk_tiled_stats* stats)
+{
+    ADK_ENTER(h);
+    if (!out || !hull) return ADK_ERR_ARG;
+    return adk::area_tiled(c, x, y, n, patch_size, step_size, kmax, amax, out, hull, stats);
 }
 
 int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out)

@@ -52,6 +52,7 @@ struct Ctx
     DevBuf ad_order, ad_ovf, ad_cta;   // AD: processing order, overflow lists, per-CTA bests
     DevBuf ad_aux;                 // AD: per-CTA order / suffix-start tables and spill workspaces
     DevBuf area_boards;            // A: per-cluster band progress boards of the row sweep
+    DevBuf tile_buf;               // tiled workflow: the slide, the window grid, populations / order, one window instance
     uint64_t ad_V = 0, ad_Q = 0;   // per-slice capacities the arena was initialised for (grow-only)
     uint32_t ad_L = 0, ad_slices = 0;
     size_t ad_slice_bytes = 0;
@@ -98,6 +99,10 @@ int run_pit_query(Ctx* c, const uint32_t* h_triples, uint32_t m, int32_t* h_out)
 int area_partial(Ctx* c, uint64_t kmax, double amax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* st);
 int area_finish(Ctx* c, uint64_t kmax, double amax, const adk_partial* best, uint32_t flags, adk_result* out, uint32_t* hull);
 int area_slope_order(Ctx* c, uint32_t i, uint32_t j, int32_t* h_out, uint32_t* h_len);
+
+// ---- tiled area-only workflow (adk_tiled.cu) ----
+int area_tiled(Ctx* c, const double* hx, const double* hy, uint32_t n, double patch, double step, uint64_t kmax, double amax,
+               adk_result* out, uint32_t* hull, adk_tiled_stats* st);
 
 // ---- area+diameter path (adk_ad.cu) ----
 int ad_partial(Ctx* c, uint64_t kmax, double amax, double dmax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* st);

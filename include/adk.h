@@ -145,6 +145,21 @@ int adk_batch_assign(const adk_instance* inst, uint32_t ninst, uint32_t nshards,
  * exchange between ranks: the caller gathers the results it needs (a host gather of adk_result records). */
 int adk_solve_batch(adk_ctx* ctx, const adk_instance* inst, uint32_t ninst, uint32_t shard, uint32_t nshards, adk_result* out);
 
+/* ---- the tiled area-only workflow of the reference's Python driver in one call: replaces create_patch_dict
+ *      (external/Area-Selector/src/convex_area_selector/convex_polygon_finder.py:139-219) + the window loop of run_area_only_tiled
+ *      (run/quality_of_results_comparison.py:77-103).  The windows (patch_size x patch_size, np.arange grid from min - 0.01 with
+ *      step_size) are generated, counted and ordered on the device; they are visited by population, largest first, each one solved
+ *      with the area path from device-resident coordinates, until a window holds fewer points than the best polygon so far.
+ *      hull[] and diam[] index the caller's points (the first of equal points, as the reference maps them back). ----------------- */
+typedef struct adk_tiled_stats
+{
+    uint64_t patches;           /* non-empty windows */
+    uint64_t solved;            /* windows visited before the early stop */
+} adk_tiled_stats;
+
+int adk_solve_area_tiled(adk_ctx* ctx, const double* x, const double* y, uint32_t n, double patch_size, double step_size,
+                         uint64_t kmax, double amax, adk_result* out, uint32_t* hull /* capacity n */, adk_tiled_stats* stats);
+
 /* Lexicographic best of `count` partials: count desc, area asc, tie_key asc (host side, no device work). */
 int adk_merge(const adk_partial* parts, uint32_t count, adk_partial* out);
 

@@ -345,6 +345,12 @@ def test_tiled_area_workflow_equals_the_reference(solver):
         assert abs(got["area"] - c["area"]) <= 1e-9 * c["area"]
         assert same_cycle(got["hull"], c["hull"]), (c["name"], got["hull"], c["hull"])
         assert (got["patches"], got["solved"]) == (c["patches"], c["solved"])
+        # the same workflow in ONE C call with the windows generated, counted and ordered on the device (adk_solve_area_tiled)
+        dev = solver.solve_area_tiled(pts[c["name"]], c["patch_size"], c["step_size"], None, c["max_area"])
+        assert dev["found"] == int(c["found"]) and dev["count"] == c["count"], (c["name"], c["step_size"], dev)
+        assert abs(dev["area"] - c["area"]) <= 1e-9 * c["area"]
+        assert same_cycle(dev["hull"], c["hull"]), (c["name"], dev["hull"], c["hull"])
+        assert (dev["patches"], dev["solved"]) == (c["patches"], c["solved"])
 
 
 # ------------------------------------------------------------------------------------------------ full-size properties
