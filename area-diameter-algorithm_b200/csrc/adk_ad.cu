@@ -324,7 +324,8 @@ __device__ __forceinline__ int tri_count_ad(const Tables& T, bool layer0, int p,
 #define ADK_CELL_WARPS 4
 #endif
 constexpr int kCellWarps = ADK_CELL_WARPS;       // warps per CTA (one candidate per CTA) when candidates are plentiful
-constexpr int kMaxCellWarps = 16;                // ... and when few, heavy candidates set the critical path (chosen per launch)
+constexpr int kMidCellWarps = 10, kMaxCellWarps = 20;   // ... and when few, heavy candidates set the critical path (chosen per launch):
+                                                 // 2 x 10 or 1 x 20 warps per SM, the same 20 warps and 96 registers as 5 x 4
 constexpr int kCellThreads = kCellWarps * 32;
 #ifndef ADK_CELL_CTAS
 #define ADK_CELL_CTAS 5
@@ -1371,6 +1372,12 @@ struct AdSmall { PairStats stats; AdCounters counters; CtaBest best; AdHull hull
 constexpr uint64_t kMinPoolRecords = 1u << 16;        // smallest record pool a slice may have
 constexpr uint64_t kDefaultPoolRecords = 4u << 20;    // first-try pool per slice (overflowing candidates are re-run larger)
 
+// The three CTA widths of k_ad_cells (warps per candidate): 4 (5 CTAs per SM), 10 (2 per SM), 20 (1 per SM).
+#define ADK_CELLS_DISPATCH(nw, EXPR) \
+    do { if ((nw) == (uint32_t) kCellWarps) { auto kern = k_ad_cells<kCellThreads, kCellCtas>; EXPR; } \
+         else if ((nw) == (uint32_t) kMidCellWarps) { auto kern = k_ad_cells<kMidCellWarps * 32, 2>; EXPR; } \
+         else { auto kern = k_ad_cells<kMaxCellWarps * 32, 1>; EXPR; } } while (0)
+
 // Launches the cell kernel over `count` queue entries (order == nullptr: pairs[0..count)) with `slices` CTAs.
 int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uint32_t count, uint32_t slices, const CellLayout& Lo,
                     const AuxLayout& Ax, uint32_t capL, uint32_t capR, uint64_t kmax, uint32_t nlayers_ref, double amax, AdSmall* sm,
@@ -1378,19 +1385,13 @@ int ad_launch_cells(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order, uin
 {
     const size_t smem = cells_smem_bytes(capL, capR, nw);
     if (smem > 200 * 1024) { c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM; }
-    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, kCellCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    else ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kMaxCellWarps * 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    ADK_CELLS_DISPATCH(nw, ADK_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)));
     ADK_CUDA(c, cudaMemsetAsync(&sm->counters.queue, 0, sizeof(unsigned int), c->stream));
     ADK_CUDA(c, cudaMemsetAsync(d_ovf_count, 0, sizeof(unsigned int), c->stream));
     Tables T{c->below.as<int32_t>(), c->coll.as<int32_t>(), c->rb.as<int32_t>(), c->n};
-    if (nw == (uint32_t) kCellWarps)
-        k_ad_cells<kCellThreads, kCellCtas><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
+    ADK_CELLS_DISPATCH(nw, (kern<<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
                                                           &sm->counters, c->arena.as<unsigned char>(), Lo, c->ad_aux.as<unsigned char>(), Ax, capL, capR, kmax, nlayers_ref,
-                                                          amax, d_cta_best, d_ovf_list, d_ovf_count, round);
-    else
-        k_ad_cells<kMaxCellWarps * 32, 1><<<slices, nw * 32, smem, c->stream>>>(c->x.as<double>(), c->y.as<double>(), c->n, T, d_pairs, d_order, count,
-                                                          &sm->counters, c->arena.as<unsigned char>(), Lo, c->ad_aux.as<unsigned char>(), Ax, capL, capR, kmax, nlayers_ref,
-                                                          amax, d_cta_best, d_ovf_list, d_ovf_count, round);
+                                                          amax, d_cta_best, d_ovf_list, d_ovf_count, round)));
     ++c->launches;
     ADK_CUDA(c, cudaGetLastError());
     return ADK_OK;
@@ -1405,11 +1406,9 @@ int ad_cells_occupancy(Ctx* c, uint32_t capL, uint32_t capR, uint32_t nw, int* p
         if (nw > (uint32_t) kCellWarps) { *per_sm = 0; return ADK_OK; }        // this CTA width is not available for such lunes
         c->err = "area+diameter path: lune lists do not fit in shared memory"; return ADK_ERR_NOMEM;
     }
-    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kCellThreads, kCellCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-    else ADK_CUDA(c, cudaFuncSetAttribute(k_ad_cells<kMaxCellWarps * 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    ADK_CELLS_DISPATCH(nw, ADK_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)));
     int occ = 0;
-    if (nw == (uint32_t) kCellWarps) ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kCellThreads, kCellCtas>, (int) nw * 32, smem));
-    else ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ad_cells<kMaxCellWarps * 32, 1>, (int) nw * 32, smem));
+    ADK_CELLS_DISPATCH(nw, ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, (int) nw * 32, smem)));
     *per_sm = occ > 0 ? occ : (nw > (uint32_t) kCellWarps ? 0 : 1);
     return ADK_OK;
 }
@@ -1427,12 +1426,12 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
     int occ = 1;
     uint32_t nw = (uint32_t) kCellWarps;
     {
-        const double eff[3] = {1.0, 0.92, 0.72};                       // measured throughput of 4 / 8 / 16 warps per candidate
+        const uint32_t widths[3] = {(uint32_t) kCellWarps, (uint32_t) kMidCellWarps, (uint32_t) kMaxCellWarps};
+        const double eff[3] = {1.0, 0.88, 0.67};                       // measured throughput per warp of 4 / 10 / 20 warps per candidate (386 / 438 / 573 ms per sweep)
         double best_t = 0.0;
         for (int v = 0; v < 3; ++v)
         {
-            const uint32_t w = (uint32_t) kCellWarps << v;
-            if (w > (uint32_t) kMaxCellWarps) break;
+            const uint32_t w = widths[v];
             int o = 0;
             ADK_TRY(ad_cells_occupancy(c, ps.max_nl, ps.max_nr, w, &o));
             if (o <= 0) break;
