@@ -59,7 +59,7 @@ EXPORTS = [
     "adk_area_partial", "adk_area_finish", "adk_area_diameter_partial", "adk_area_diameter_finish",
     "adk_merge", "adk_area_partial_dev", "adk_area_diameter_partial_dev",
     "adk_batch_assign", "adk_solve_batch",
-    "adk_count_tables", "adk_points_in_triangle", "adk_cw_order", "adk_slope_order", "adk_lune_lists",
+    "adk_count_tables", "adk_points_in_triangle", "adk_cw_order", "adk_cw_order_noalloc", "adk_slope_order", "adk_lune_lists",
     "adk_solve_area_tiled",
     "adk_multi_create", "adk_multi_destroy", "adk_multi_last_error", "adk_multi_device_count", "adk_multi_set_reuse",
     "adk_multi_solve_area", "adk_multi_solve_area_diameter", "adk_multi_last_stats",

@@ -434,6 +434,12 @@ int adk_cw_order(adk_ctx* h, const double* x, const double* y, uint32_t n, int32
     return ADK_OK;
 }
 
+int adk_cw_order_noalloc(adk_ctx* h, const double* d_x, const double* d_y, uint32_t n, int32_t* d_order)
+{
+    ADK_ENTER(h);
+    return adk::cw_order_noalloc(c, d_x, d_y, n, d_order);
+}
+
 int adk_slope_order(adk_ctx* h, const double* x, const double* y, uint32_t n, uint32_t i, uint32_t j, int32_t* out, uint32_t* len)
 {
     ADK_ENTER(h);

@@ -94,6 +94,7 @@ int run_angles_and_orders(Ctx* c, bool need_cw, bool need_modpi);
 int run_count_tables(Ctx* c);
 int run_yorder(Ctx* c);
 int run_pit_query(Ctx* c, const uint32_t* h_triples, uint32_t m, int32_t* h_out);
+int cw_order_noalloc(Ctx* c, const double* d_x, const double* d_y, uint32_t n, int32_t* d_order);
 
 // ---- area path (adk_area.cu) ----
 int area_partial(Ctx* c, uint64_t kmax, double amax, uint32_t shard, uint32_t nshards, adk_partial* out, adk_stats* st);

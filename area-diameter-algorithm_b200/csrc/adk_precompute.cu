@@ -14,6 +14,7 @@
 #include "adk_device.cuh"
 
 #include <cstring>
+#include <string>
 
 namespace adk
 {
@@ -397,6 +398,50 @@ int run_pit_query(Ctx* c, const uint32_t* h_triples, uint32_t m, int32_t* h_out)
     ADK_CUDA(c, cudaGetLastError());
     ADK_CUDA(c, cudaMemcpyAsync(h_out, c->scratch1.p, sizeof(int32_t) * (size_t) m, cudaMemcpyDeviceToHost, c->stream));
     ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ADK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation variant
+//
+// adk_cw_order_noalloc (include/adk.h): the clockwise-order stage for callers that must not allocate (CUDA graph capture, tight
+// serving loops).  It has no counterpart in the reference.
+// The stage needs scratch: k_angles writes the n x n angle and squared-distance tables that k_order_sort reads.  Here that scratch
+// is this file-scope array instead of the context's grow-only buffers: 2 x kNoAllocMaxN^2 doubles = 4 MiB, held by every GPU that
+// loads the library until the process exits.  EVERY call shares it, so calls that overlap on the GPU (two streams, two contexts,
+// two threads) race; it keeps the previous call's contents, which is harmless: k_angles writes every entry of both tables for the
+// call's own n (row stride n) before k_order_sort reads any, so nothing has to start at zero.
+constexpr uint32_t kNoAllocMaxN = ADK_NOALLOC_MAX_POINTS;
+static __device__ __align__(256) double g_noalloc_scratch[2 * (size_t) kNoAllocMaxN * kNoAllocMaxN];
+
+// In host code the array's name is only a host-side stand-in for the symbol, not a device address: the address is asked for
+// once per device, with that device current, and cached.
+static double* g_noalloc_ptr[64] = {nullptr};
+
+int cw_order_noalloc(Ctx* c, const double* d_x, const double* d_y, uint32_t n, int32_t* d_order)
+{
+    if (!d_x || !d_y || !d_order) { c->err = "adk_cw_order_noalloc: null pointer"; return ADK_ERR_ARG; }
+    if (n < 2) { c->err = "adk_cw_order_noalloc: n < 2"; return ADK_ERR_ARG; }
+    if (n > kNoAllocMaxN)
+    {
+        c->err = "adk_cw_order_noalloc: n = " + std::to_string(n) + " exceeds the static scratch (ADK_NOALLOC_MAX_POINTS = " +
+                 std::to_string(kNoAllocMaxN) + "); use adk_cw_order";
+        return ADK_ERR_ARG;
+    }
+    if (c->device < 0 || c->device >= 64) { c->err = "adk_cw_order_noalloc: device ordinal out of range"; return ADK_ERR_ARG; }
+    double* scratch = g_noalloc_ptr[c->device];
+    if (!scratch)
+    {   // set-up, once per device; the caller (ADK_ENTER) has made the context's device current
+        ADK_CUDA(c, cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_noalloc_scratch));
+        g_noalloc_ptr[c->device] = scratch;
+    }
+    double* ang = scratch;
+    double* d2c = scratch + (size_t) n * n;
+    // 44 n + 64 bytes of dynamic shared memory: 22.6 KB at the maximum n, below the 48 KB that need no opt-in
+    const size_t smem = (sizeof(unsigned long long) * 2 + sizeof(uint16_t) * 2) * (size_t) (n - 1) + sizeof(double) * 3 * (size_t) n + 64;
+    k_angles<<<n, 256, 0, c->stream>>>(d_x, d_y, n, ang, d2c);
+    k_order_sort<0><<<n, kSortThreads, smem, c->stream>>>(d_x, d_y, n, ang, d2c, d_order, nullptr);
+    c->launches += 2;
+    ADK_CUDA(c, cudaGetLastError());
     return ADK_OK;
 }
 

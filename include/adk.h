@@ -208,6 +208,17 @@ int adk_count_tables(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
 int adk_points_in_triangle(adk_ctx* ctx, const double* x, const double* y, uint32_t n,
                            const uint32_t* triples /* 3*m */, uint32_t m, int32_t* out /* m */);
 int adk_cw_order(adk_ctx* ctx, const double* x, const double* y, uint32_t n, int32_t* order /* n*(n-1) */);
+/* The same clockwise lists as adk_cw_order for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * d_x, d_y (n doubles each) and d_order (n*(n-1) int32) are DEVICE pointers owned by the caller.  The call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine): the n x n angle and distance tables of the stage live in a static
+ * device array of 2 * ADK_NOALLOC_MAX_POINTS^2 doubles (4 MiB, held by every GPU that loads the library until exit).
+ * n > ADK_NOALLOC_MAX_POINTS is rejected with ADK_ERR_ARG and a text in adk_last_error.  The two kernels are queued on the
+ * context's stream (adk_set_stream) and the call returns WITHOUT synchronising; the first call on a device also resolves the
+ * array's address (cudaGetSymbolAddress), so make one call before starting a capture.  Every call shares the array: calls that
+ * overlap on the GPU (several streams, contexts or threads) race. */
+#define ADK_NOALLOC_MAX_POINTS 512u
+int adk_cw_order_noalloc(adk_ctx* ctx, const double* d_x, const double* d_y, uint32_t n, int32_t* d_order /* n*(n-1) */);
 /* slope order around centre j for anchor i (Eppstein.cpp:62-114); out capacity n; *len receives the length */
 int adk_slope_order(adk_ctx* ctx, const double* x, const double* y, uint32_t n, uint32_t i, uint32_t j,
                     int32_t* out, uint32_t* len);
