@@ -14,6 +14,7 @@
 #include "adk_device.cuh"
 
 #include <cooperative_groups.h>
+#include <cstddef>
 
 #include <algorithm>
 #include <cmath>
@@ -27,6 +28,7 @@ namespace adk
 
 struct SrcRec { double area; uint32_t gidx; uint16_t c; uint16_t c3; };   // 16 B, one per source cell; c3 bit 15: the source is the
                                                                            // first element of its row's slope list (for the counter)
+constexpr uint32_t kReachBuckets = 8;     // area buckets of an entry's readers (stop rule of the row sweep)
 constexpr uint32_t kNoPrev = 0xffffffffu;   // nothing before the read position: level 2 reads 0, deeper levels read +inf
 
 struct AnchorInfo
@@ -51,6 +53,7 @@ struct AnchorInfo
     unsigned long long lvl[3];   // best area (order-preserving bits) of the level in flight and its two neighbours
     int32_t best_row_any;
     uint32_t defer_overflow;   // a row met more than 32 eps-collinear points beyond its vertex: outside the contract, reported as an error
+    uint32_t pad2_[2];
     unsigned long long t0_ns, t1_ns;   // development: when the row pipeline started / finished this anchor (ADK_DEBUG)
 };
 
@@ -64,7 +67,7 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
             AnchorInfo* __restrict__ info, uint32_t first, uint32_t count,
             SrcRec* __restrict__ recs, uint16_t* __restrict__ srcl, int32_t* __restrict__ rowpt,
             uint32_t* __restrict__ nsrc, uint32_t* __restrict__ rowbase,
-            uint16_t* __restrict__ qscratch, uint32_t qstride, uint64_t K, double amax)
+            uint16_t* __restrict__ qscratch, uint32_t qstride, uint64_t K, double amax, uint32_t* __restrict__ mcr)
 {
     extern __shared__ uint16_t slot_of[];    // n entries: point -> row slot, 0xffff = not above the anchor
     __shared__ uint32_t s_start, s_rows, s_cmax, s_total;
@@ -221,7 +224,20 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
             if (lane == 31) s_total = incl;
         }
         __syncthreads();
-        // Phase 2b: the read T[m-c][l][j] as an index into row l's compact prefix-minimum array
+        // Phase 2b: the read T[m-c][l][j] as an index into row l's compact prefix-minimum array.
+        // Every table entry also learns WHO READS IT: a record r that reads entry e turns a finite value g of e at level m into a
+        // finite value at level m + c_r only if g + area_r <= A.  Readers are bucketed by floor(8 area_r / A); amcr[e][b] becomes the
+        // largest c among the readers of e in buckets <= b, so that the row sweep can bound the highest level a finite entry can
+        // still feed by m + amcr[e][floor(8 (A - g) / A)] and stop long before "top level + largest c of the anchor".
+        // Storage: 8 x 32-bit words per entry while the maxima are scattered (native atomicMax, nobody waits for it), packed to
+        // 8 x 16 bits at the start of the same 32 bytes by the prefix pass below.
+        uint32_t* amcr = mcr + A.meta_off * kReachBuckets;
+        {
+            uint4* z = reinterpret_cast<uint4*>(amcr);
+            for (uint32_t t = threadIdx.x; t < 2u * s_total; t += blockDim.x) z[t] = make_uint4(0u, 0u, 0u, 0u);
+        }
+        __syncthreads();
+        const double inv_bucket = (double) kReachBuckets / amax;
         uint32_t cm = 0;
         for (uint32_t jj = warp; jj < rows; jj += nwarps)
         {
@@ -232,9 +248,26 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
             {
                 const uint32_t lp = rsrc[k];
                 const uint32_t q = Q[(size_t) lp * rows + jj];
-                rrec[k].gidx = (q == 0xffff || q == 0) ? kNoPrev : abase[lp] + q - 1;
-                cm = max(cm, (uint32_t) rrec[k].c);
+                const uint32_t g = (q == 0xffff || q == 0) ? kNoPrev : abase[lp] + q - 1;
+                rrec[k].gidx = g;
+                const uint32_t c = rrec[k].c;
+                if (g != kNoPrev)
+                {
+                    const int br = min((int) kReachBuckets - 1, max(0, (int) (rrec[k].area * inv_bucket)));
+                    atomicMax(amcr + (size_t) g * kReachBuckets + br, c);
+                }
+                cm = max(cm, c);
             }
+        }
+        __syncthreads();
+        for (uint32_t t = threadIdx.x; t < s_total; t += blockDim.x)
+        {   // prefix maximum over the buckets, packed to 16 bits in place (c <= ADK_MAX_POINTS)
+            uint4* e = reinterpret_cast<uint4*>(amcr + (size_t) t * kReachBuckets);
+            const uint4 lo = e[0], hi = e[1];
+            uint32_t v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+            for (int b = 1; b < 8; ++b) v[b] = max(v[b], v[b - 1]);
+            e[0] = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
         }
         atomicMax(&s_cmax, cm);
         __syncthreads();
@@ -429,20 +462,29 @@ __device__ __forceinline__ void row_segment(uint32_t ns, uint32_t rd, uint32_t w
 // n = 1000) is cut by the number of bands in flight, which is what anchors-over-8-GPUs needs.  The ring holds
 // ceil(cmax / 32) + CS bands: the oldest band in flight still reads ceil(cmax / 32) bands back while the newest one writes.
 // Bands past the last finite level may be started before the stop rule can know (at most CS - 1 of them): they produce +inf only.
+__device__ void hull_diameter_dev(const double* x, const double* y, const int32_t* hull, uint32_t cnt, uint32_t* out);
+
+// The best anchor a cluster has met so far, with its polygon already walked back (see the end of k_area_rows).
+struct KeepRec { uint32_t found, m; double area; uint32_t order, len, ok, diam[2]; int32_t pt, row, pad; };
+
 constexpr uint32_t kMaxRing = 256;           // bands on the board: covers any cmax < 32 * (kMaxRing - 8) = 7 936 > ADK_MAX_POINTS
 struct BandBoard
 {
     unsigned long long prog[kMaxRing];      // (band + 1) << 32 | rows finished, per ring slot
     unsigned int top[kMaxRing];             // highest finite level of the band in that slot (0 = none)
     double area[kMaxRing];                  // its best area
-    unsigned int q, levels, pad[2];         // the anchor the cluster works on; levels executed (all bands)
+    unsigned int q, levels, reach, pad;     // the anchor the cluster works on; levels executed (all bands); highest level a finite entry can feed
+    KeepRec keep;                           // this cluster's best anchor so far; its hull is at keep_hull[cluster * hull_stride ..]
 };
 
 __global__ void __launch_bounds__(kRowThreads, kRowThreads >= 512 ? 1 : 2)
 k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
             const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc,
             const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, uint64_t slot_entries, uint64_t K, double amax,
-            uint32_t cap_rows, BandBoard* __restrict__ boards)
+            uint32_t cap_rows, BandBoard* __restrict__ boards,
+            const double* __restrict__ x, const double* __restrict__ y, const uint16_t* __restrict__ srcl,
+            const int32_t* __restrict__ rowpt, int32_t* __restrict__ keep_hull, uint32_t hull_stride,
+            const uint32_t* __restrict__ mcr)
 {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
@@ -453,17 +495,20 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
     __shared__ unsigned long long s_best[kBand];
     __shared__ long long s_req;
     __shared__ int s_row, s_go;
+    __shared__ __align__(16) uint16_t s_mc[kRowWarps][32][kReachBuckets];
+    __shared__ unsigned int s_reach;
     extern __shared__ uint32_t s_rowtab[];     // [cap_rows] source counts, [cap_rows] row bases (anchors with more rows read them from global memory)
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     SrcRec* st_rec = s_rec[warp];
     BandBoard& B = boards[cid];
     volatile unsigned long long* vprog = B.prog;
+    if (crank == 0 && threadIdx.x == 0) { B.keep.found = 0; B.keep.m = 0; B.keep.area = 0.0; B.keep.ok = 0; B.keep.len = 0; }
     for (;;)
     {
         __syncthreads();
         if (crank == 0 && threadIdx.x == 0)
         {
-            B.q = atomicAdd(queue, 1u); B.levels = 0;
+            B.q = atomicAdd(queue, 1u); B.levels = 0; B.reach = 0;
             for (uint32_t t = 0; t < kMaxRing; ++t) { B.prog[t] = 0ull; B.top[t] = 0u; }
             __threadfence();
         }
@@ -473,11 +518,13 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
         AnchorInfo& A = info[first + q];
         const uint32_t rows = A.rows, U = A.U, W = A.W, acap = (uint32_t) A.a, cmax = A.cmax;
         const uint32_t Wb = W / kBand, W8 = W * 8u;     // W8: bytes per table row
+        const double inv_bucket = (double) kReachBuckets / amax;
         // bands this anchor can fill at all: a polygon above it has at most a + 2 points (the host sizes the ring with the same
         // bound, so a band beyond it would wrap onto a band that is still being written)
         const uint64_t top_level = K < (uint64_t) acap + 2 ? K : (uint64_t) acap + 2;
         const uint32_t nb_cap = (uint32_t) (top_level >= 3 ? (top_level - 2 + kBand - 1) / kBand : 1);
         const SrcRec* arec = recs + A.meta_off;
+        const uint4* amcr = reinterpret_cast<const uint4*>(mcr + A.meta_off * kReachBuckets);      // 32 bytes per entry, the first 16 hold 8 x uint16
         const uint32_t* ansrc = nsrc + A.row_off;
         const uint32_t* abase = rowbase + A.row_off;
         if (rows <= cap_rows)
@@ -488,7 +535,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
         double* T = Tbuf + (size_t) cid * slot_entries;      // the cluster's own table slot, reused for every anchor it takes
         if (threadIdx.x == 0)
         {
-            s_req = 0; s_row = 0x7fffffff;
+            s_req = 0; s_row = 0x7fffffff; s_reach = 0;
             if (crank == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t0_ns));
         }
         __syncthreads();
@@ -518,7 +565,12 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         }
                         const uint64_t lo_done = 3u + kBand * (b - CS);
                         const uint64_t hi_done = K < lo_done + kBand - 1 ? K : lo_done + kBand - 1;
-                        s_go = (hi_done >= K || hi_done >= (uint64_t) ktop + cmax) ? 0 : 1;
+                        // Nothing beyond hi_done can be finite once hi_done has passed every level a finite entry can feed (its level
+                        // + the largest c among its readers) and every level the constant level 2 can feed (2 + c).  ktop + cmax, the
+                        // rule of round 1, is the same bound with the anchor-wide cmax in place of the per-entry one.
+                        (void) ktop;
+                        const uint64_t reach = max((uint64_t) *reinterpret_cast<volatile unsigned int*>(&B.reach), (uint64_t) cmax + 2u);
+                        s_go = (hi_done >= K || hi_done >= reach) ? 0 : 1;
                     }
                     __syncthreads();
                     const int go = s_go;
@@ -537,10 +589,12 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                 uint32_t nj = 0, nr = 0;
                 while (nj < rows && ansrc[nj] == 0) ++nj;
                 SrcRec nxt = SrcRec{0.0, kNoPrev, 0, 0};
+                uint4 nxt_mc = make_uint4(0u, 0u, 0u, 0u);   // the reader summary of the entry this lane's record produces (see k_area_prep)
+                uint32_t reach_l = 0;           // highest level a finite entry written by this lane (level m) can feed
                 {
                     uint32_t nb = 0, nc = 0;
                     if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
-                    if (lane < nc) nxt = arec[(size_t) nj * acap + nb + lane];
+                    if (lane < nc) { nxt = arec[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
                 }
                 for (uint32_t jj = 0; jj < rows; ++jj)
                 {
@@ -571,13 +625,13 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         uint32_t base, cnt;
                         row_segment(ns, rd, warp, base, cnt);
                         __syncwarp();
-                        if (lane < cnt) st_rec[lane] = nxt;
+                        if (lane < cnt) { st_rec[lane] = nxt; *reinterpret_cast<uint4*>(s_mc[warp][lane]) = nxt_mc; }
                         __syncwarp();
                         if (++nr >= rounds) { nr = 0; ++nj; while (nj < rows && ansrc[nj] == 0) ++nj; }
                         {
                             uint32_t nb = 0, nc = 0;
                             if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
-                            if (lane < nc) nxt = arec[(size_t) nj * acap + nb + lane];
+                            if (lane < nc) { nxt = arec[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
                         }
                         // every predecessor vector of the segment is requested before any of them is used
                         double pv[32];
@@ -642,6 +696,11 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                             changes += g < before ? 1u : 0u;                             // Eppstein.cpp:228-232
                             before = g;
                             if (active) __stcg(reinterpret_cast<double*>(outp), g);      // Eppstein.cpp:234
+                            if (active && g < INFINITY)
+                            {   // readers of this entry that can still fit under the area bound: area <= A - g (inflated: never stop early)
+                                const int bs = min((int) kReachBuckets - 1, max(0, (int) (__dadd_rn(__dmul_rn(__dsub_rn(amax, g), 1.000001), 1e-12) * inv_bucket)));
+                                reach_l = max(reach_l, m + (uint32_t) s_mc[warp][u][bs]);
+                            }
                             outp += W8;
                         }
                         req += changes;
@@ -652,9 +711,12 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                     if (CS > 1 && threadIdx.x == 0) { __threadfence(); vprog[bslot] = ((unsigned long long) (b + 1) << 32) | (jj + 1); }
                 }
                 if (warp == 0) s_best[lane] = area_bits(band_best);
+                reach_l = __reduce_max_sync(0xffffffffu, reach_l);
+                if (lane == 0 && reach_l) atomicMax(&s_reach, reach_l);
                 __syncthreads();
                 if (threadIdx.x == 0)
                 {
+                    if (s_reach) atomicMax(&B.reach, s_reach);
                     unsigned int tp = 0; double ar = 0.0;
                     for (uint32_t l = 0; l < kBand; ++l)
                         if (s_best[l] != kInfBits) { tp = lo + l; ar = bits_area(s_best[l]); }
@@ -676,12 +738,14 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
         // started beyond its stopping point hold +inf only), and the first row (in j order) that attains the best area there
         // (Eppstein.cpp:219-224).  The board keeps the last kMaxRing bands; a finite level is never more than cmax levels from the end.
         uint32_t top = 2; double best_area = 0.0;
+        uint32_t bands_ran = 0;                 // bands started for this anchor: no more than the ring holds = nothing was overwritten
         if (U > 0)
         {
             for (uint32_t b = 0; (uint64_t) (3u + kBand * b) <= K && b < nb_cap; ++b)
             {
                 const unsigned long long tag = vprog[b % kMaxRing] >> 32;
                 if (tag < (unsigned long long) (b + 1)) break;                 // this band was never started: the sweep had stopped
+                bands_ran = b + 1;
                 if (tag > (unsigned long long) (b + 1)) continue;              // its slot belongs to a later band by now
                 const unsigned int tp = *reinterpret_cast<volatile unsigned int*>(&B.top[b % kMaxRing]);
                 if (tp) { top = tp; best_area = *reinterpret_cast<volatile double*>(&B.area[b % kMaxRing]); }
@@ -704,6 +768,72 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
             A.levels_run = *reinterpret_cast<volatile unsigned int*>(&B.levels);
             if (top > 2) { A.best_m = top; A.best_area = best_area; A.best_row = *reinterpret_cast<volatile int*>(&A.best_row_any); }
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(A.t1_ns));
+        }
+        // The anchor's table is still complete in the cluster's slot (when the ring did not wrap): if this anchor is the cluster's
+        // best so far, walk its polygon back NOW (Eppstein.cpp:240-270) instead of re-running the winner after the solve.  A cluster
+        // takes its anchors in the reference's order, so "strictly better" keeps the first of equals, as the reference does; the
+        // solve's winner beats every anchor its cluster met before it and is beaten by none after it, so its polygon is the one
+        // its cluster holds at the end.  One warp; the other CTAs wait at the next cluster barrier, nothing overwrites the table.
+        if (crank == 0 && warp == 0 && top > 2 && bands_ran <= Wb &&
+            (!B.keep.found || top > B.keep.m || (top == B.keep.m && best_area < B.keep.area)))
+        {
+            const uint16_t* asrc = srcl + A.meta_off;
+            const int32_t* arowpt = rowpt + A.row_off;
+            int32_t* hull = keep_hull + (size_t) cid * hull_stride;
+            uint32_t m = top, h = 0, ok = 1;
+            int row = *reinterpret_cast<volatile int*>(&A.best_row_any);
+            const int row0 = row;
+            if (lane == 0) hull[0] = A.pt;
+            h = 1;
+            int last = A.pt;
+            const uint32_t hcap = rows + 2;          // a polygon has at most rows + 1 vertices (exactly degenerate inputs must not run away)
+            while (m > 2)
+            {
+                if (h >= hcap || row < 0 || (uint32_t) row >= rows) { ok = 0; break; }
+                const int j = arowpt[row];
+                const uint32_t ns = ansrc[row], ob = abase[row];
+                const uint32_t tp = level_pos(m, Wb);
+                const double lx = x[last], ly = y[last], jx = x[j], jy = y[j];
+                int pick = -1;
+                for (int hi = (int) ns - 1; hi >= 0 && pick < 0; hi -= 32)
+                {   // the last position where the running minimum changes and the turn at j stays convex
+                    const int k = hi - (int) lane;
+                    bool cond = false;
+                    if (k >= 0)
+                    {
+                        const double v = __ldcg(&T[(size_t) (ob + k) * W + tp]);
+                        const double vp = k ? __ldcg(&T[(size_t) (ob + k - 1) * W + tp]) : INFINITY;
+                        if (v != vp)
+                        {
+                            const int l = arowpt[asrc[(size_t) row * acap + k]];
+                            cond = orientation(lx, ly, jx, jy, x[l], y[l]) >= 0;
+                        }
+                    }
+                    const uint32_t bm = __ballot_sync(0xffffffffu, cond);
+                    if (bm) pick = hi - (__ffs((int) bm) - 1);
+                }
+                if (pick < 0) { ok = 0; break; }
+                const SrcRec r = arec[(size_t) row * acap + pick];
+                const uint32_t c = m == 3 ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
+                if (c > m) { ok = 0; break; }
+                m -= c;
+                if (lane == 0) hull[h] = j;
+                ++h;
+                last = j;
+                row = (int) asrc[(size_t) row * acap + pick];
+            }
+            if (ok && (row < 0 || (uint32_t) row >= rows)) ok = 0;
+            if (ok) { if (lane == 0) hull[h] = arowpt[row]; ++h; }
+            __syncwarp();
+            if (lane == 0)
+            {
+                KeepRec kr;
+                kr.found = 1; kr.m = top; kr.area = best_area; kr.order = A.order; kr.len = h; kr.ok = ok; kr.pt = A.pt; kr.row = row0; kr.pad = 0;
+                kr.diam[0] = kr.diam[1] = 0;
+                if (ok) { __threadfence(); hull_diameter_dev(x, y, hull, h, kr.diam); }
+                B.keep = kr;
+            }
+            __syncwarp();
         }
     }
 }
@@ -946,6 +1076,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     ADK_TRY(ensure(c, c->scratch0, sizeof(AnchorInfo) * cnt));
     ADK_TRY(ensure(c, c->scratch1, sizeof(SrcRec) * std::max<uint64_t>(P.meta_total, 1)));
     ADK_TRY(ensure(c, c->scratch2, sizeof(uint16_t) * std::max<uint64_t>(P.meta_total, 1)));
+    ADK_TRY(ensure(c, c->area_mcr, sizeof(uint32_t) * kReachBuckets * std::max<uint64_t>(P.meta_total, 1)));
     ADK_TRY(ensure(c, c->scratch3, sizeof(int32_t) * 3 * std::max<uint64_t>(P.row_total, 1)));
     const uint32_t prep_grid = std::min<uint32_t>(cnt, (uint32_t) c->sm_count);   // 1024-thread CTAs, one per SM
     const uint32_t qstride = P.amax_rows * P.amax_rows;
@@ -964,7 +1095,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
     {
         k_area_prep<<<prep_grid, kPrepThreads, sizeof(uint16_t) * n, c->stream>>>(
             c->x.as<double>(), c->y.as<double>(), n, T, c->cw.as<int32_t>(), c->modpi.as<int32_t>(), c->rank.as<uint16_t>(),
-            d_info, 0, cnt, d_recs, d_srcl, d_rowpt, d_nsrc, d_rowbase, c->scratch4.as<uint16_t>(), qstride, K, amax);
+            d_info, 0, cnt, d_recs, d_srcl, d_rowpt, d_nsrc, d_rowbase, c->scratch4.as<uint16_t>(), qstride, K, amax, c->area_mcr.as<uint32_t>());
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
     }
@@ -1025,10 +1156,39 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             slot_entries = std::max<uint64_t>(slot_entries, W * (uint64_t) A.U);
         }
         slot_entries = (slot_entries + 31) & ~(uint64_t) 31;
+        // A ring that never wraps leaves the anchor's table complete when the anchor ends, and the cluster can then walk its polygon
+        // back on the spot (end of k_area_rows) instead of the winner being re-run after the solve.  The slots are sized for the
+        // largest anchor, so smaller ones lengthen their rings for free; beyond that the slots may grow into the memory budget
+        // (HBM is idle otherwise), never past what complete tables would take.
+        {
+            uint64_t full = 1;
+            for (uint32_t t = 0; t < cnt; ++t)
+            {
+                const AnchorInfo& A = P.info[t];
+                const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
+                const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
+                full = std::max<uint64_t>(full, nb_max * kBand * (uint64_t) A.U);
+            }
+            const uint64_t want_slots = std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1));
+            const uint64_t roomy = std::min<uint64_t>(full, budget_entries / want_slots) & ~(uint64_t) 31;
+            if (roomy > slot_entries) slot_entries = roomy;
+        }
+        for (uint32_t t = 0; t < cnt; ++t)
+        {
+            AnchorInfo& A = P.info[t];
+            if (A.U == 0) continue;
+            const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
+            const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
+            const uint64_t fit = std::min<uint64_t>(nb_max, slot_entries / ((uint64_t) A.U * kBand));
+            if (fit * kBand > A.W) A.W = (uint32_t) (fit * kBand);
+        }
         const uint64_t slots = std::min<uint64_t>(std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1)), budget_entries / slot_entries);
         if (slots == 0) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
         ADK_TRY(ensure(c, c->scratch5, sizeof(double) * slots * slot_entries));
         ADK_TRY(ensure(c, c->area_boards, sizeof(BandBoard) * slots));
+        const uint32_t hull_stride = (n + 8) & ~3u;
+        ADK_TRY(ensure(c, c->area_keep_hull, sizeof(int32_t) * (size_t) hull_stride * slots));
+        c->area_keep_valid = false;
         ADK_CUDA(c, cudaMemcpyAsync(d_info, P.info.data(), sizeof(AnchorInfo) * cnt, cudaMemcpyHostToDevice, c->stream));
         ADK_CUDA(c, cudaMemsetAsync(c->small.p, 0, sizeof(unsigned int) * 2, c->stream));
         ADK_CUDA(c, cudaEventRecord(c->ev2, c->stream));
@@ -1042,8 +1202,12 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             cfg.attrs = attr; cfg.numAttrs = 1;
             ADK_CUDA(c, cudaLaunchKernelEx(&cfg, k_area_rows, d_info, 0u, cnt, &so_->queue, (const SrcRec*) d_recs, (const uint32_t*) d_nsrc,
                                            (const uint32_t*) d_rowbase, c->scratch5.as<double>(), (uint64_t) slot_entries, K, amax, cap_rows,
-                                           c->area_boards.as<BandBoard>()));
+                                           c->area_boards.as<BandBoard>(), (const double*) c->x.as<double>(), (const double*) c->y.as<double>(),
+                                           (const uint16_t*) d_srcl, (const int32_t*) d_rowpt, c->area_keep_hull.as<int32_t>(), hull_stride,
+                                           (const uint32_t*) c->area_mcr.as<uint32_t>()));
         }
+        c->area_keep_valid = true; c->area_keep_slots = (uint32_t) slots; c->area_keep_stride = hull_stride;
+        c->area_keep_K = K; c->area_keep_amax = amax;
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
         ADK_CUDA(c, cudaEventRecord(c->ev3, c->stream));
@@ -1059,6 +1223,12 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             ADK_CUDA(c, cudaStreamSynchronize(c->stream));
             unsigned long long tmin = ~0ull, tmax = 0; double sum = 0.0, longest = 0.0;
             for (auto& a : h) { tmin = std::min(tmin, a.t0_ns); tmax = std::max(tmax, a.t1_ns); sum += (double) (a.t1_ns - a.t0_ns); longest = std::max(longest, (double) (a.t1_ns - a.t0_ns)); }
+            { const AnchorInfo* w = nullptr; for (auto& a : h) if (!w || a.best_m > w->best_m) w = &a;
+              if (w) std::fprintf(stderr, "[adk] best anchor: pt %d order %u m %u U %u cmax %u W %u (bands %u) levels_run %u rows %u a %d; slot_entries %llu CS %u\n", w->pt, w->order,
+                                  w->best_m, w->U, w->cmax, w->W, w->W / 32, w->levels_run, w->rows, w->a, (unsigned long long) slot_entries, CS); }
+            { double run = 0.0, useful = 0.0;
+              for (auto& a : h) { run += (double) a.levels_run * a.U; const uint32_t tb = a.best_m > 2 ? (a.best_m - 2 + 31) / 32 : 1; useful += (double) tb * 32 * a.U; }
+              std::fprintf(stderr, "[adk] executed level x source cells %.4g, of which up to each anchor's top band %.4g (%.1f %%)\n", run, useful, 100.0 * useful / run); }
             std::fprintf(stderr, "[adk] rows kernel: %u anchors on %llu CTAs, span %.2f ms, sum of anchor times %.2f ms, longest anchor %.2f ms\n",
                          cnt, (unsigned long long) slots * CS, (tmax - tmin) * 1e-6, sum * 1e-6, longest * 1e-6);
         }
@@ -1179,11 +1349,47 @@ int area_finish(Ctx* c, uint64_t kmax, double amax, const adk_partial* best, uin
     out->count = best->count; out->area = best->area;
     if (!(flags & ADK_FLAG_RECONSTRUCT)) return ADK_OK;
     const uint64_t K = std::min<uint64_t>(kmax, n);
+    if (best->w0 >= n) { c->err = "area_finish: bad witness"; return ADK_ERR_ARG; }
+    if (c->debug) std::fprintf(stderr, "[adk] area_finish: keep valid %d K %llu/%llu amax %g/%g slots %u\n", (int) c->area_keep_valid,
+                               (unsigned long long) K, (unsigned long long) c->area_keep_K, amax, c->area_keep_amax, c->area_keep_slots);
+    if (c->area_keep_valid && c->area_keep_K == K && c->area_keep_amax == amax && c->area_keep_slots > 0)
+    {   // the partial solve on this context walked the polygon of every cluster's best anchor back while its table was still
+        // there: if the winner is one of them (it is, when it was found on this GPU) there is nothing to re-run
+        const uint32_t slots = c->area_keep_slots;
+        std::vector<KeepRec> recs(slots);
+        ADK_CUDA(c, cudaMemcpy2DAsync(recs.data(), sizeof(KeepRec), reinterpret_cast<const char*>(c->area_boards.p) + offsetof(BandBoard, keep),
+                                      sizeof(BandBoard), sizeof(KeepRec), slots, cudaMemcpyDeviceToHost, c->stream));
+        ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->debug)
+        {
+            uint32_t nf = 0; for (uint32_t t = 0; t < slots; ++t) nf += recs[t].found ? 1u : 0u;
+            std::fprintf(stderr, "[adk] area_finish: %u kept records over %u clusters\n", nf, slots);
+        }
+        if (c->debug)
+            for (uint32_t t = 0; t < slots; ++t)
+                if (recs[t].found && (recs[t].m + 2 >= best->count || t < 3))
+                    std::fprintf(stderr, "[adk] keep[%u]: m %u area %.17g order %u pt %d len %u ok %u   (winner: m %u area %.17g order %u pt %u)\n", t, recs[t].m,
+                                 recs[t].area, recs[t].order, recs[t].pt, recs[t].len, recs[t].ok, best->count, best->area, (uint32_t) (best->tie_key >> 32), best->w0);
+        for (uint32_t t = 0; t < slots; ++t)
+        {
+            const KeepRec& kr = recs[t];
+            if (!kr.found || !kr.ok || kr.m != best->count || kr.order != (uint32_t) (best->tie_key >> 32) || (uint32_t) kr.pt != best->w0 ||
+                kr.area != best->area || kr.len == 0 || kr.len > n) continue;
+            ADK_TRY(ensure_pinned(c, sizeof(int32_t) * ((size_t) n + 8)));
+            ADK_CUDA(c, cudaMemcpyAsync(c->h_pinned, c->area_keep_hull.as<int32_t>() + (size_t) t * c->area_keep_stride, sizeof(int32_t) * kr.len,
+                                        cudaMemcpyDeviceToHost, c->stream));
+            ADK_CUDA(c, cudaStreamSynchronize(c->stream));
+            const int32_t* hp = static_cast<const int32_t*>(c->h_pinned);
+            out->hull_len = kr.len;
+            for (uint32_t q = 0; q < kr.len; ++q) hull[q] = (uint32_t) hp[q];
+            out->diam_valid = 1; out->diam[0] = kr.diam[0]; out->diam[1] = kr.diam[1];      // Eppstein.cpp:271-273
+            return ADK_OK;
+        }
+    }
     ADK_TRY(run_angles_and_orders(c, true, true));
     ADK_TRY(run_count_tables(c));
     std::vector<int32_t> yorder, above;
     ADK_TRY(area_fetch_yorder(c, yorder, above));
-    if (best->w0 >= n) { c->err = "area_finish: bad witness"; return ADK_ERR_ARG; }
     AreaPlan P;
     area_plan_add(P, (int32_t) best->w0, above[best->w0], (uint32_t) (best->tie_key >> 32));
     // re-run the winning anchor keeping every level up to m*, then walk back (Eppstein.cpp:240-274)

@@ -24,7 +24,7 @@ int set_cuda_error(Ctx* c, cudaError_t e, const char* what)
 void release_idle(Ctx* c, const DevBuf* keep)
 {
     auto drop = [&](DevBuf& b) { if (&b != keep && b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; } };
-    if (keep == &c->arena) { drop(c->scratch5); drop(c->scratch4); drop(c->scratch2); drop(c->scratch1); }
+    if (keep == &c->arena) { drop(c->scratch5); drop(c->scratch4); drop(c->scratch2); drop(c->scratch1); drop(c->area_mcr); c->area_keep_valid = false; }
     else if (c->arena.p)
     {
         drop(c->arena); drop(c->ad_aux);
@@ -143,7 +143,7 @@ void adk_destroy(adk_ctx* h)
     if (c->stream) cudaStreamSynchronize(c->stream);
     adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
                            &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
-                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards, &c->tile_buf};
+                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards, &c->area_keep_hull, &c->area_mcr, &c->tile_buf};
     for (adk::DevBuf* b : bufs) adk::free_buf(*b);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->ev0) cudaEventDestroy(c->ev0);

@@ -52,6 +52,12 @@ struct Ctx
     DevBuf ad_order, ad_ovf, ad_cta;   // AD: processing order, overflow lists, per-CTA bests
     DevBuf ad_aux;                 // AD: per-CTA order / suffix-start tables and spill workspaces
     DevBuf area_boards;            // A: per-cluster band progress boards of the row sweep
+    DevBuf area_mcr;               // A: per table entry, the largest c among the records that read it (stop rule of the row sweep)
+    DevBuf area_keep_hull;         // A: per-cluster polygon of the cluster's best anchor (walked back inside the row sweep)
+    bool area_keep_valid = false;  // ... valid for the resident point set and these bounds (see area_finish)
+    uint32_t area_keep_slots = 0, area_keep_stride = 0;
+    uint64_t area_keep_K = 0;
+    double area_keep_amax = 0.0;
     DevBuf tile_buf;               // tiled workflow: the slide, the window grid, populations / order, one window instance
     uint64_t ad_V = 0, ad_Q = 0;   // per-slice capacities the arena was initialised for (grow-only)
     uint32_t ad_L = 0, ad_slices = 0;

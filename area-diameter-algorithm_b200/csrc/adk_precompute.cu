@@ -298,6 +298,7 @@ int upload_points(Ctx* c, const double* x, const double* y, uint32_t n, bool dev
     c->n = n;
     c->have_cw = c->have_modpi = c->have_tables = c->have_yorder = false;
     c->ad_keep_valid = false;
+    c->area_keep_valid = false;
     c->points_valid = true;
     if (!device_ptrs)
     {
