@@ -1182,20 +1182,34 @@ k_ad_cells(const double* __restrict__ x, const double* __restrict__ y, uint32_t 
     if (threadIdx.x == 0) cta_best[blockIdx.x] = s_best;
 }
 
-__global__ void k_ad_reduce(const CtaBest* __restrict__ in, uint32_t count, CtaBest* __restrict__ out, int merge_existing)
+__device__ __forceinline__ bool cta_best_better(const CtaBest& c, const CtaBest& b)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (!c.found) return false;
+    return !b.found || c.count > b.count || (c.count == b.count && (c.area < b.area || (c.area == b.area && c.key < b.key)));
+}
+
+// Best candidate over the per-CTA records (count desc, area asc, pair key asc: AntipodalOptimized.cpp:512-517).  One CTA: every
+// thread folds a strided share, then a tree over shared memory (the order is total, so any association gives the same winner).
+__global__ void __launch_bounds__(256)
+k_ad_reduce(const CtaBest* __restrict__ in, uint32_t count, CtaBest* __restrict__ out, int merge_existing)
+{
+    __shared__ CtaBest s_b[256];
     CtaBest b;
-    if (merge_existing) b = *out;
-    else { b.found = 0; b.count = 0; b.area = 0.0; b.key = ~0ull; b.s = b.t = 0; }
-    for (uint32_t i = 0; i < count; ++i)
+    b.found = 0; b.count = 0; b.area = 0.0; b.key = ~0ull; b.s = b.t = 0; b.nl = b.nr = 0; b.slice = 0; b.round = 0; b.states = 0; b.pad = 0;
+    if (merge_existing && threadIdx.x == 0) b = *out;
+    for (uint32_t i = threadIdx.x; i < count; i += blockDim.x)
     {
         const CtaBest c = in[i];
-        if (!c.found) continue;
-        const bool better = !b.found || c.count > b.count || (c.count == b.count && (c.area < b.area || (c.area == b.area && c.key < b.key)));
-        if (better) b = c;
+        if (cta_best_better(c, b)) b = c;
     }
-    *out = b;
+    s_b[threadIdx.x] = b;
+    __syncthreads();
+    for (uint32_t o = blockDim.x >> 1; o; o >>= 1)
+    {
+        if (threadIdx.x < o && cta_best_better(s_b[threadIdx.x + o], s_b[threadIdx.x])) s_b[threadIdx.x] = s_b[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = s_b[0];
 }
 
 // --------------------------------------------------------------------------------------------- witness recovery
@@ -1244,7 +1258,8 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
         s_v[threadIdx.x] = bvv; s_i[threadIdx.x] = bi;
     }
     __syncthreads();
-    if (threadIdx.x != 0) return;
+    if (threadIdx.x >= 32) return;            // one warp walks: lanes test 32 predecessor candidates at a time
+    const uint32_t lane = threadIdx.x;
     const double Sx = S.Lx[0], Sy = S.Ly[0], Ex = S.Lx[nl - 1], Ey = S.Ly[nl - 1];
     const int Sp = S.Lidx[0], Ep = S.Lidx[nl - 1];
     const double seg2 = dist2(Sx, Sy, Ex, Ey);
@@ -1276,46 +1291,71 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
         int32_t* oth_out = rt ? left : right; uint32_t& oth_cnt = rt ? a : b;
         const uint32_t o = eo, s = es, ss = ess;
         bool found = false, via_switch = false; uint32_t prev = 0, cused = 0; unsigned long long pv = kInfBits;
-        // (a) the state was produced by staying on its own chain: source (o, p, s) on the same side
+        // (a) the state was produced by staying on its own chain: source (o, p, s) on the same side; the first p (then z) that
+        //     reproduces the stored value, as a sequential scan would find it
         if (dist2(othx[o], othy[o], ownx[s], owny[s]) <= seg2)
-            for (uint32_t p = 0; p < s && !found; ++p)
+            for (uint32_t p0 = 0; p0 < s && !found; p0 += 32)
             {
-                if (!(orientation(ownx[ss], owny[ss], ownx[s], owny[s], ownx[p], owny[p]) >= 0 &&
-                      orientation(ownx[ss], owny[ss], ownx[s], owny[s], ax, ay) >= 0)) continue;
-                const double tri = fabs(signed_area(ax, ay, ownx[p], owny[p], ownx[s], owny[s]));
-                for (int z = 0; z < 2 && !found; ++z)
+                const uint32_t p = p0 + lane;
+                bool hit = false; uint32_t hc = 0; unsigned long long hv = kInfBits;
+                if (p < s && orientation(ownx[ss], owny[ss], ownx[s], owny[s], ownx[p], owny[p]) >= 0 &&
+                    orientation(ownx[ss], owny[ss], ownx[s], owny[s], ax, ay) >= 0)
                 {
-                    const uint32_t c = 1u + (uint32_t) tri_count_ad(T, z == 1, owni[p], ownx[p], owny[p], owni[s], ownx[s], owny[s], ap, ax, ay);
-                    if (c > k) continue;
-                    const uint32_t ks = k - c;
-                    if ((z == 1) != (ks == 0)) continue;
-                    const unsigned long long sv = state_value(sl, nl, nr, rt, o, p, s, ks);
-                    if (sv == kInfBits) continue;
-                    if (area_bits(__dadd_rn(bits_area(sv), tri)) != ev) continue;
-                    found = true; via_switch = false; prev = p; cused = c; pv = sv;
+                    const double tri = fabs(signed_area(ax, ay, ownx[p], owny[p], ownx[s], owny[s]));
+                    for (int z = 0; z < 2 && !hit; ++z)
+                    {
+                        const uint32_t c = 1u + (uint32_t) tri_count_ad(T, z == 1, owni[p], ownx[p], owny[p], owni[s], ownx[s], owny[s], ap, ax, ay);
+                        if (c > k) continue;
+                        const uint32_t ks = k - c;
+                        if ((z == 1) != (ks == 0)) continue;
+                        const unsigned long long sv = state_value(sl, nl, nr, rt, o, p, s, ks);
+                        if (sv == kInfBits) continue;
+                        if (area_bits(__dadd_rn(bits_area(sv), tri)) != ev) continue;
+                        hit = true; hc = c; hv = sv;
+                    }
+                }
+                const uint32_t hm = __ballot_sync(0xffffffffu, hit);
+                if (hm)
+                {
+                    const int w = __ffs((int) hm) - 1;
+                    found = true; via_switch = false; prev = p0 + (uint32_t) w;
+                    cused = __shfl_sync(0xffffffffu, hc, w); pv = __shfl_sync(0xffffffffu, hv, w);
                 }
             }
         // (b) it was produced by a switch from the other chain: source (o' = s, s' = p, ss' = o) on the other side
         if (!found && dist2(ownx[s], owny[s], othx[o], othy[o]) <= seg2)
-            for (uint32_t p = 0; p < o && !found; ++p)
+            for (uint32_t p0 = 0; p0 < o && !found; p0 += 32)
             {
-                const double rx = othx[p], ry = othy[p], px = othx[o], py = othy[o];
-                const double refd = pseudo_dist(rx, ry, px, py, ownx[s], owny[s]);
-                const double d = pseudo_dist(rx, ry, px, py, ownx[ss], owny[ss]);
-                if (!(d <= refd)) continue;
-                if (!(s == 0 || (orientation(ownx[s], owny[s], ax, ay, ownx[ss], owny[ss]) >= 0 &&
-                                 orientation(ownx[ss], owny[ss], ownx[s], owny[s], bx, by) >= 0))) continue;
-                const double tri = fabs(signed_area(bx, by, rx, ry, px, py));
-                for (int z = 0; z < 2 && !found; ++z)
+                const uint32_t p = p0 + lane;
+                bool hit = false; uint32_t hc = 0; unsigned long long hv = kInfBits;
+                if (p < o)
                 {
-                    const uint32_t c = 1u + (uint32_t) tri_count_ad(T, z == 1, othi[p], rx, ry, othi[o], px, py, bp, bx, by);
-                    if (c > k) continue;
-                    const uint32_t ks = k - c;
-                    if ((z == 1) != (ks == 0)) continue;
-                    const unsigned long long sv = state_value(sl, nl, nr, !rt, s, p, o, ks);
-                    if (sv == kInfBits) continue;
-                    if (area_bits(__dadd_rn(bits_area(sv), tri)) != ev) continue;
-                    found = true; via_switch = true; prev = p; cused = c; pv = sv;
+                    const double rx = othx[p], ry = othy[p], px = othx[o], py = othy[o];
+                    const double refd = pseudo_dist(rx, ry, px, py, ownx[s], owny[s]);
+                    const double d = pseudo_dist(rx, ry, px, py, ownx[ss], owny[ss]);
+                    if (d <= refd && (s == 0 || (orientation(ownx[s], owny[s], ax, ay, ownx[ss], owny[ss]) >= 0 &&
+                                                 orientation(ownx[ss], owny[ss], ownx[s], owny[s], bx, by) >= 0)))
+                    {
+                        const double tri = fabs(signed_area(bx, by, rx, ry, px, py));
+                        for (int z = 0; z < 2 && !hit; ++z)
+                        {
+                            const uint32_t c = 1u + (uint32_t) tri_count_ad(T, z == 1, othi[p], rx, ry, othi[o], px, py, bp, bx, by);
+                            if (c > k) continue;
+                            const uint32_t ks = k - c;
+                            if ((z == 1) != (ks == 0)) continue;
+                            const unsigned long long sv = state_value(sl, nl, nr, !rt, s, p, o, ks);
+                            if (sv == kInfBits) continue;
+                            if (area_bits(__dadd_rn(bits_area(sv), tri)) != ev) continue;
+                            hit = true; hc = c; hv = sv;
+                        }
+                    }
+                }
+                const uint32_t hm = __ballot_sync(0xffffffffu, hit);
+                if (hm)
+                {
+                    const int w = __ffs((int) hm) - 1;
+                    found = true; via_switch = true; prev = p0 + (uint32_t) w;
+                    cused = __shfl_sync(0xffffffffu, hc, w); pv = __shfl_sync(0xffffffffu, hv, w);
                 }
             }
         if (!found) { ok = 0; break; }
@@ -1331,6 +1371,8 @@ k_ad_backtrack(const double* __restrict__ x, const double* __restrict__ y, uint3
         else { e_right = !rt; eo = s; es = prev; ess = o; }
         ev = pv;
     }
+    __syncwarp();
+    if (lane != 0) return;
     for (uint32_t t = 0; t < a; ++t) hull[t] = left[t];
     for (uint32_t t = 0; t < b; ++t) hull[a + t] = right[t];
     out->len = a + b; out->ok = ok; out->nl = nl; out->nr = nr;
@@ -1470,7 +1512,7 @@ int ad_run_queue(Ctx* c, const PairRec* d_pairs, const uint32_t* d_order0, uint3
         ADK_TRY(ensure(c, c->ad_cta, sizeof(CtaBest) * slices));
         ADK_TRY(ad_launch_cells(c, d_pairs, d_order, count, (uint32_t) slices, Lo, Ax, ps.max_nl, ps.max_nr, kmax, nlayers_ref, amax, sm,
                                 c->ad_cta.as<CtaBest>(), d_ovf[round & 1], &sm->ovf_count[round & 1], (uint32_t) round, nw));
-        k_ad_reduce<<<1, 32, 0, c->stream>>>(c->ad_cta.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
+        k_ad_reduce<<<1, 256, 0, c->stream>>>(c->ad_cta.as<CtaBest>(), (uint32_t) slices, &sm->best, merge);
         ++c->launches;
         ADK_CUDA(c, cudaGetLastError());
         merge = 1;
