@@ -433,9 +433,36 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
 #ifndef ADK_ROW_THREADS
 #define ADK_ROW_THREADS 256
 #endif
+#ifndef ADK_ROW_SEG
+#define ADK_ROW_SEG 32
+#endif
+#ifndef ADK_ROW_CTAS
+#define ADK_ROW_CTAS 2
+#endif
 constexpr int kRowThreads = ADK_ROW_THREADS;
 constexpr uint32_t kRowWarps = kRowThreads / 32;
 constexpr uint32_t kBand = 32;
+constexpr uint32_t kSeg = ADK_ROW_SEG;                 // sources per warp and round
+constexpr uint32_t kRound = kRowWarps * kSeg;          // sources per CTA and round
+// Staging of the predecessor vectors (round 2): the 32 levels a warp needs from one predecessor entry are 256 contiguous bytes of
+// its table row, starting at any 8-byte boundary and possibly wrapping at the end of the ring.  They are brought into shared
+// memory with 16-byte asynchronous copies (cp.async.cg: L2 -> shared memory, no register in between), 17 per source, so that a
+// vector in flight costs 272 bytes of shared memory instead of two registers in every lane: the kernel drops from 124 to under
+// 64 registers and the resident warps per SM double.
+constexpr uint32_t kStageDoubles = 34;                 // per source: 32 levels + one element of slack at either end (16-byte pieces)
+// Per source of a round: address of the first 16-byte piece, byte correction for the pieces that lie past the end of the ring,
+// number of pieces (0 = nothing to fetch) and the first piece that is past the first band slot.
+struct __align__(16) SrcPlan { unsigned long long first; int32_t wrap; uint16_t pieces, turn; };
+
+__device__ __forceinline__ void async_copy16(void* smem_dst, const void* gmem_src)
+{
+    const uint32_t d = (uint32_t) __cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void async_copy_wait()
+{
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
 
 __device__ __forceinline__ uint32_t level_pos(uint32_t lvl, uint32_t Wb)      // lvl >= 3
 {
@@ -443,11 +470,11 @@ __device__ __forceinline__ uint32_t level_pos(uint32_t lvl, uint32_t Wb)      //
     return ((z >> 5) % Wb) * kBand + (z & 31u);
 }
 
-// Segment of round `rd` of a row with ns sources that warp `warp` handles: the row is cut into ceil(ns / kRowThreads) rounds
-// of equal size, a round into kRowWarps equal segments of at most 32 sources.
+// Segment of round `rd` of a row with ns sources that warp `warp` handles: the row is cut into ceil(ns / kRound) rounds
+// of equal size, a round into kRowWarps equal segments of at most kSeg sources.
 __device__ __forceinline__ void row_segment(uint32_t ns, uint32_t rd, uint32_t warp, uint32_t& base, uint32_t& cnt)
 {
-    const uint32_t rounds = (ns + kRowThreads - 1) / kRowThreads;
+    const uint32_t rounds = (ns + kRound - 1) / kRound;
     const uint32_t per_round = rounds == 1 ? ns : (ns + rounds - 1) / rounds;
     const uint32_t seg = (per_round + kRowWarps - 1) / kRowWarps;
     const uint32_t end = min(ns, (rd + 1) * per_round);
@@ -477,10 +504,10 @@ struct BandBoard
     KeepRec keep;                           // this cluster's best anchor so far; its hull is at keep_hull[cluster * hull_stride ..]
 };
 
-__global__ void __launch_bounds__(kRowThreads, kRowThreads >= 512 ? 1 : 2)
+__global__ void __launch_bounds__(kRowThreads, ADK_ROW_CTAS)
 k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigned int* __restrict__ queue,
             const SrcRec* __restrict__ recs, const uint32_t* __restrict__ nsrc,
-            const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, uint64_t slot_entries, uint64_t K, double amax,
+            const uint32_t* __restrict__ rowbase, double* __restrict__ Tbuf, const uint64_t* __restrict__ slot_off, uint64_t K, double amax,
             uint32_t cap_rows, BandBoard* __restrict__ boards,
             const double* __restrict__ x, const double* __restrict__ y, const uint16_t* __restrict__ srcl,
             const int32_t* __restrict__ rowpt, int32_t* __restrict__ keep_hull, uint32_t hull_stride,
@@ -490,25 +517,31 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
     cg::cluster_group cluster = cg::this_cluster();
     const uint32_t crank = cluster.block_rank(), CS = cluster.num_blocks();
     const uint32_t cid = blockIdx.x / CS;
-    __shared__ __align__(16) SrcRec s_rec[kRowWarps][32];
+    __shared__ __align__(16) SrcRec s_rec[kRowWarps][kSeg];
+    __shared__ __align__(16) SrcPlan s_plan[kRowWarps][kSeg];
     __shared__ double s_tot[2][kRowWarps][32];
     __shared__ unsigned long long s_best[kBand];
     __shared__ long long s_req;
     __shared__ int s_row, s_go;
-    __shared__ __align__(16) uint16_t s_mc[kRowWarps][32][kReachBuckets];
+    __shared__ __align__(16) uint16_t s_mc[kRowWarps][kSeg][kReachBuckets];
     __shared__ unsigned int s_reach;
-    extern __shared__ uint32_t s_rowtab[];     // [cap_rows] source counts, [cap_rows] row bases (anchors with more rows read them from global memory)
+    // [cap_rows] source counts, [cap_rows] row bases (anchors with more rows read them from global memory), then the staging
+    // area: kStageDoubles doubles per source of the round, kSeg sources per warp
+    extern __shared__ __align__(16) uint32_t s_rowtab[];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     SrcRec* st_rec = s_rec[warp];
+    SrcPlan* st_plan = s_plan[warp];
+    double* stage = reinterpret_cast<double*>(s_rowtab + 2u * cap_rows) + (size_t) warp * kSeg * kStageDoubles;
     BandBoard& B = boards[cid];
     volatile unsigned long long* vprog = B.prog;
     if (crank == 0 && threadIdx.x == 0) { B.keep.found = 0; B.keep.m = 0; B.keep.area = 0.0; B.keep.ok = 0; B.keep.len = 0; }
-    for (;;)
+    for (bool first_round = true;; first_round = false)
     {
         __syncthreads();
         if (crank == 0 && threadIdx.x == 0)
         {
-            B.q = atomicAdd(queue, 1u); B.levels = 0; B.reach = 0;
+            // the first anchor of cluster k is anchor k (its slot is sized for it, see area_run); then the queue behind the first ones
+            B.q = first_round ? cid : gridDim.x / CS + atomicAdd(queue, 1u); B.levels = 0; B.reach = 0;
             for (uint32_t t = 0; t < kMaxRing; ++t) { B.prog[t] = 0ull; B.top[t] = 0u; }
             __threadfence();
         }
@@ -532,7 +565,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
             for (uint32_t t = threadIdx.x; t < rows; t += blockDim.x) { s_rowtab[t] = ansrc[t]; s_rowtab[cap_rows + t] = abase[t]; }
             ansrc = s_rowtab; abase = s_rowtab + cap_rows;
         }
-        double* T = Tbuf + (size_t) cid * slot_entries;      // the cluster's own table slot, reused for every anchor it takes
+        double* T = Tbuf + slot_off[cid];                    // the cluster's own table slot, reused for every anchor it takes
         if (threadIdx.x == 0)
         {
             s_req = 0; s_row = 0x7fffffff; s_reach = 0;
@@ -584,7 +617,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                 const uint32_t bslot = b % kMaxRing, pslot = (b + kMaxRing - 1) % kMaxRing;
                 const unsigned long long ptag = (unsigned long long) b << 32;        // band b - 1 carries tag (b - 1) + 1
                 double band_best = INFINITY;    // warp 0: best final value of level m over the rows
-                // A row's sources are cut into rounds of at most kRowThreads, and a round evenly into one segment per warp.
+                // A row's sources are cut into rounds of at most kRound, and a round evenly into one segment per warp.
                 // The source records of a round are requested one round ahead (they depend on nothing).
                 uint32_t nj = 0, nr = 0;
                 while (nj < rows && ansrc[nj] == 0) ++nj;
@@ -618,14 +651,40 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         __syncwarp();
                     }
                     const uint32_t obase = abase[jj];
-                    const uint32_t rounds = (ns + kRowThreads - 1) / kRowThreads;
+                    const uint32_t rounds = (ns + kRound - 1) / kRound;
                     double carry = INFINITY;
                     for (uint32_t rd = 0; rd < rounds; ++rd)
                     {
                         uint32_t base, cnt;
                         row_segment(ns, rd, warp, base, cnt);
                         __syncwarp();
-                        if (lane < cnt) { st_rec[lane] = nxt; *reinterpret_cast<uint4*>(s_mc[warp][lane]) = nxt_mc; }
+                        if (lane < cnt)
+                        {
+                            st_rec[lane] = nxt; *reinterpret_cast<uint4*>(s_mc[warp][lane]) = nxt_mc;
+                            // Where the 32 levels m - c (m = lo .. lo + 31) of this source's predecessor entry lie: level lo - c sits at
+                            // position p of band slot s0 = bm + floor(-c / 32), the window runs on into slot s0 + 1 (both modulo the
+                            // ring).  Lane L of the band reads window element p + L; the window is fetched as 16-byte pieces
+                            // starting at element p & ~1, so lane L finds its element at index (p & 1) + L of the staged copy.  A
+                            // source none of whose levels exists yet (c + 3 > lo + 31, or past K) is not fetched at all.
+                            const uint32_t c = nxt.c, p = (0u - c) & 31u, p2 = p & ~1u;
+                            const uint64_t mtop = K < (uint64_t) lo + 31u ? K : (uint64_t) lo + 31u;
+                            const bool fetch = nxt.gidx != kNoPrev && (uint64_t) c + 3u <= mtop;
+                            int s0 = (int) bm + ((-(int) c) >> 5);
+                            if (s0 < 0) s0 += (int) Wb;
+                            const int s1 = s0 + 1 == (int) Wb ? 0 : s0 + 1;
+                            SrcPlan pl;
+                            pl.first = (unsigned long long) __cvta_generic_to_global(T) + (uint64_t) nxt.gidx * W8 + (uint64_t) s0 * (kBand * 8u) + p2 * 8u;
+                            pl.wrap = (s1 - s0 - 1) * (int) (kBand * 8u);
+                            pl.pieces = (uint16_t) (fetch ? 16u + (p & 1u) : 0u);
+                            pl.turn = (uint16_t) ((kBand - p2) >> 1);
+                            st_plan[lane] = pl;
+                            s_mc[warp][lane][kReachBuckets - 1] |= (uint16_t) ((c & 1u) << 15);     // the parity travels with the reader summary
+                        }
+                        else if (lane < kSeg)
+                        {   // the loops below run in groups of four sources: the padding fetches nothing and adds +inf
+                            st_rec[lane] = SrcRec{INFINITY, kNoPrev, 0, 0};
+                            st_plan[lane] = SrcPlan{0ull, 0, 0, 0};
+                        }
                         __syncwarp();
                         if (++nr >= rounds) { nr = 0; ++nj; while (nj < rows && ansrc[nj] == 0) ++nj; }
                         {
@@ -633,46 +692,64 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                             if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
                             if (lane < nc) { nxt = arec[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
                         }
-                        // every predecessor vector of the segment is requested before any of them is used
-                        double pv[32];
+                        // every predecessor vector of the segment is on its way before any of them is used
+                        {
+                            char* dst = reinterpret_cast<char*>(stage) + lane * 16u;
+                            const uint4* plan = reinterpret_cast<const uint4*>(st_plan);
+#pragma unroll 1
+                            for (uint32_t u0 = 0; u0 < cnt; u0 += 4)
+                            {
+                                uint4 pw[4];
+#pragma unroll
+                                for (uint32_t t = 0; t < 4; ++t) pw[t] = plan[u0 + t];             // first (x, y) | wrap (z) | pieces, turn (w)
+#pragma unroll
+                                for (uint32_t t = 0; t < 4; ++t)
+                                {
+                                    const long long off = (long long) (int) (lane * 16u) + (lane >= (pw[t].w >> 16) ? (int) pw[t].z : 0);
+                                    const unsigned long long first = ((unsigned long long) pw[t].y << 32) | pw[t].x;
+                                    if (lane < (pw[t].w & 0xffffu)) async_copy16(dst + t * (kStageDoubles * 8u), reinterpret_cast<const char*>(first + off));
+                                }
+                                dst += 4u * kStageDoubles * 8u;
+                            }
+                        }
+                        async_copy_wait();
+                        __syncwarp();
+                        // local prefix minima: the staged element of this lane becomes the running minimum of the segment up to u.
+                        // Branch-free: level m - c is a real table entry (>= 3), the constant level 2 (T[2] = 0) or nothing (+inf),
+                        // Eppstein.cpp:210-216; lanes past K behave like level 0.
                         double run = INFINITY;
+                        {
+                            const int mk = active ? (int) m : 0;
+                            const bool is3 = m == 3u;
+                            double* cell = stage + lane;
+                            const uint4* rec4 = reinterpret_cast<const uint4*>(st_rec);          // area (x, y) | gidx (z) | c, c3 (w)
+#pragma unroll 1
+                            for (uint32_t u0 = 0; u0 < cnt; u0 += 4)
+                            {
+                                uint4 rw[4]; double v[4]; double* mine[4];
+#pragma unroll
+                                for (uint32_t t = 0; t < 4; ++t) rw[t] = rec4[u0 + t];
+#pragma unroll
+                                for (uint32_t t = 0; t < 4; ++t) { mine[t] = cell + t * kStageDoubles + (rw[t].w & 1u); v[t] = *mine[t]; }
+#pragma unroll
+                                for (uint32_t t = 0; t < 4; ++t)
+                                {
+                                    const uint32_t c = is3 ? ((rw[t].w >> 16) & 0x7fffu) : (rw[t].w & 0xffffu);
+                                    const int k = mk - (int) c;
+                                    const bool real = k >= 3 && rw[t].z != kNoPrev;
+                                    const int hi = real ? __double2hiint(v[t]) : (k == 2 ? 0 : 0x7ff00000);
+                                    const int lw = real ? __double2loint(v[t]) : 0;
+                                    const double cur = __dadd_rn(__hiloint2double(hi, lw), __hiloint2double((int) rw[t].y, (int) rw[t].x));
+                                    v[t] = cur <= amax ? cur : INFINITY;
+                                }
+#pragma unroll
+                                for (uint32_t t = 0; t < 4; ++t) { run = v[t] < run ? v[t] : run; *mine[t] = run; }
+                                cell += 4u * kStageDoubles;
+                            }
+                        }
+                        // the first element of the whole list is no change point if it is finite (its running minimum is its own value)
                         bool head_finite = false;
-#pragma unroll
-                        for (uint32_t u = 0; u < 32; ++u)
-                        {
-                            if (u >= cnt) break;
-                            pv[u] = INFINITY;
-                            const SrcRec r = st_rec[u];
-                            const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
-                            if (r.gidx != kNoPrev && active && c + 3u <= m)
-                            {   // level m - c = 3 + 32 b + (lane - c): its band is b + floor((lane - c) / 32), at most ceil(cmax / 32) bands back
-                                const int d = (int) lane - (int) c;
-                                int slot = (int) bm + (d >> 5);
-                                if (slot < 0) slot += (int) Wb;
-                                // row address and offset inside the row as two 32 x 32 + 64 bit multiply-adds
-                                const char* rowp = reinterpret_cast<const char*>(T) + (uint64_t) r.gidx * W8;
-                                const uint32_t off = (uint32_t) slot * kBand + ((uint32_t) d & 31u);
-                                pv[u] = __ldcg(reinterpret_cast<const double*>(rowp + (uint64_t) off * 8u));
-                            }
-                        }
-                        // local prefix minima (pv[u] becomes the running minimum of the segment up to u)
-#pragma unroll
-                        for (uint32_t u = 0; u < 32; ++u)
-                        {
-                            if (u >= cnt) break;
-                            const SrcRec r = st_rec[u];
-                            const uint32_t c = m == 3u ? (uint32_t) (r.c3 & 0x7fffu) : (uint32_t) r.c;
-                            double val = INFINITY;
-                            if (active && c + 2u <= m)
-                            {   // Eppstein.cpp:210-216 with T[0], T[1] = +inf and T[2] = 0
-                                const double prev = m - c == 2u ? 0.0 : pv[u];
-                                const double cur = __dadd_rn(prev, r.area);
-                                if (cur <= amax) val = cur;
-                            }
-                            if (u == 0 && base == 0) head_finite = (r.c3 & 0x8000u) && val < INFINITY;
-                            run = val < run ? val : run;
-                            pv[u] = run;
-                        }
+                        if (base == 0 && cnt) head_finite = (st_rec[0].c3 & 0x8000u) && stage[lane + ((uint32_t) st_rec[0].c & 1u)] < INFINITY;
                         s_tot[par][warp][lane] = run;
                         __syncthreads();
                         double cin = carry, all = carry;
@@ -688,20 +765,28 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         if (head_finite) --req;                                          // the list's first element is no change point
                         char* outp = reinterpret_cast<char*>(T + mypos) + (uint64_t) (obase + base) * W8;
                         uint32_t changes = 0;
-#pragma unroll
-                        for (uint32_t u = 0; u < 32; ++u)
                         {
-                            if (u >= cnt) break;
-                            const double g = pv[u] < cin ? pv[u] : cin;
-                            changes += g < before ? 1u : 0u;                             // Eppstein.cpp:228-232
-                            before = g;
-                            if (active) __stcg(reinterpret_cast<double*>(outp), g);      // Eppstein.cpp:234
-                            if (active && g < INFINITY)
-                            {   // readers of this entry that can still fit under the area bound: area <= A - g (inflated: never stop early)
-                                const int bs = min((int) kReachBuckets - 1, max(0, (int) (__dadd_rn(__dmul_rn(__dsub_rn(amax, g), 1.000001), 1e-12) * inv_bucket)));
-                                reach_l = max(reach_l, m + (uint32_t) s_mc[warp][u][bs]);
+                            const double* cell = stage + lane;
+                            const uint16_t* mc = s_mc[warp][0];
+#pragma unroll 4
+                            for (uint32_t u = 0; u < cnt; ++u)
+                            {
+                                const uint32_t w7 = mc[kReachBuckets - 1];                   // largest c among the entry's readers | parity << 15
+                                const double mine = cell[w7 >> 15];
+                                const double g = mine < cin ? mine : cin;
+                                changes += g < before ? 1u : 0u;                             // Eppstein.cpp:228-232
+                                before = g;
+                                if (active) __stcg(reinterpret_cast<double*>(outp), g);      // Eppstein.cpp:234
+                                if (g < INFINITY && m + (w7 & 0x7fffu) > reach_l)
+                                {   // readers of this entry that can still fit under the area bound: area <= A - g (inflated: never stop early);
+                                    // skipped when even the entry's largest reader cannot raise the bound this lane already holds
+                                    const int bs = min((int) kReachBuckets - 1, max(0, (int) (__dadd_rn(__dmul_rn(__dsub_rn(amax, g), 1.000001), 1e-12) * inv_bucket)));
+                                    reach_l = max(reach_l, m + ((uint32_t) mc[bs] & 0x7fffu));
+                                }
+                                outp += W8;
+                                cell += kStageDoubles;
+                                mc += kReachBuckets;
                             }
-                            outp += W8;
                         }
                         req += changes;
                         carry = all;
@@ -1122,8 +1207,9 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
         // heaviest anchor's critical path.
         uint32_t max_rows = 1;
         for (uint32_t t = 0; t < cnt; ++t) max_rows = std::max<uint32_t>(max_rows, (uint32_t) P.info[t].a);
-        const uint32_t cap_rows = std::min<uint32_t>(max_rows, 4096);
-        const size_t smem = sizeof(uint32_t) * 2 * cap_rows;
+        const uint32_t cap_rows = (std::min<uint32_t>(max_rows, 4096) + 1u) & ~1u;      // even: the staging area behind the row table stays 16-byte aligned
+        const size_t smem = sizeof(uint32_t) * 2 * cap_rows + sizeof(double) * kRowWarps * kSeg * kStageDoubles;
+        ADK_CUDA(c, cudaFuncSetAttribute(k_area_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         int per_sm = 0;
         ADK_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_area_rows, kRowThreads, smem));
         const uint64_t resident = (uint64_t) std::max(per_sm, 1) * (uint64_t) c->sm_count;
@@ -1143,48 +1229,63 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
                 if (v == 0 || t < 0.95 * best) { best = v == 0 ? t : std::min(best, t); CS = 1u << v; }
             }
         }
-        uint64_t slot_entries = 1;
+        // Table slots.  Cluster k starts with anchor k (the anchors arrive heaviest first) and then pulls from the queue behind the
+        // first `slots` anchors, so its slot must hold anchor k and whatever the queue may still hand out: slot k = max(need of
+        // anchor k, largest need in the tail).  Sizing every slot for the single largest anchor (round 1) took 86-120 GB at
+        // n = 1000 for two CTAs per SM and left no room for more resident CTAs.
+        //   need  = the shortest ring the sweep can run with: ceil(cmax / 32) + CS bands (reach back cmax levels from the oldest band
+        //           in flight), never more than the levels an anchor with this many rows can fill;
+        //   full  = every level the anchor can fill: a ring that never wraps leaves the table complete when the anchor ends, and
+        //           the cluster can then walk its polygon back on the spot (end of k_area_rows) instead of the winner being re-run
+        //           after the solve.  Slots grow from need towards full as far as the memory budget allows (HBM is idle otherwise).
+        std::vector<uint64_t> need(cnt), full(cnt), nbmax(cnt);
         for (uint32_t t = 0; t < cnt; ++t)
         {
-            AnchorInfo& A = P.info[t];
-            // bands: enough to reach back cmax levels from the oldest band in flight, never more than the levels an anchor with this
-            // many rows can fill
+            const AnchorInfo& A = P.info[t];
             const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
-            const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
-            const uint64_t W = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + CS, nb_max) * kBand;
-            A.W = (uint32_t) W; A.t_off = 0;
-            slot_entries = std::max<uint64_t>(slot_entries, W * (uint64_t) A.U);
+            nbmax[t] = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
+            const uint64_t wb = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + CS, nbmax[t]);
+            need[t] = wb * kBand * (uint64_t) A.U;
+            full[t] = nbmax[t] * kBand * (uint64_t) A.U;
         }
-        slot_entries = (slot_entries + 31) & ~(uint64_t) 31;
-        // A ring that never wraps leaves the anchor's table complete when the anchor ends, and the cluster can then walk its polygon
-        // back on the spot (end of k_area_rows) instead of the winner being re-run after the solve.  The slots are sized for the
-        // largest anchor, so smaller ones lengthen their rings for free; beyond that the slots may grow into the memory budget
-        // (HBM is idle otherwise), never past what complete tables would take.
+        uint64_t slots = std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1));
+        std::vector<uint64_t> slot_size;
+        uint64_t total_need = 0;
+        for (;; --slots)
         {
-            uint64_t full = 1;
-            for (uint32_t t = 0; t < cnt; ++t)
-            {
-                const AnchorInfo& A = P.info[t];
-                const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
-                const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
-                full = std::max<uint64_t>(full, nb_max * kBand * (uint64_t) A.U);
-            }
-            const uint64_t want_slots = std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1));
-            const uint64_t roomy = std::min<uint64_t>(full, budget_entries / want_slots) & ~(uint64_t) 31;
-            if (roomy > slot_entries) slot_entries = roomy;
+            uint64_t tail_need = 1;
+            for (uint32_t t = (uint32_t) slots; t < cnt; ++t) tail_need = std::max(tail_need, need[t]);
+            slot_size.assign(slots, 0);
+            total_need = 0;
+            for (uint32_t k = 0; k < slots; ++k) { slot_size[k] = (std::max(need[k], tail_need) + 31) & ~(uint64_t) 31; total_need += slot_size[k]; }
+            if (total_need <= budget_entries || slots == 1) break;
         }
+        if (total_need > budget_entries) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
+        {
+            uint64_t tail_full = 1;
+            for (uint32_t t = (uint32_t) slots; t < cnt; ++t) tail_full = std::max(tail_full, full[t]);
+            uint64_t total_want = 0;
+            std::vector<uint64_t> want(slots);
+            for (uint32_t k = 0; k < slots; ++k) { want[k] = std::max(slot_size[k], (std::max(full[k], tail_full) + 31) & ~(uint64_t) 31); total_want += want[k]; }
+            const double f = total_want <= budget_entries ? 1.0 : (double) (budget_entries - total_need) / (double) (total_want - total_need);
+            for (uint32_t k = 0; k < slots; ++k)
+                slot_size[k] = std::min<uint64_t>(want[k], slot_size[k] + ((uint64_t) ((double) (want[k] - slot_size[k]) * f) & ~(uint64_t) 31));
+        }
+        std::vector<uint64_t> slot_off(slots + 1, 0);
+        uint64_t min_slot = ~0ull;
+        for (uint32_t k = 0; k < slots; ++k) { slot_off[k + 1] = slot_off[k] + slot_size[k]; min_slot = std::min(min_slot, slot_size[k]); }
         for (uint32_t t = 0; t < cnt; ++t)
-        {
+        {   // an anchor lengthens its ring to fill the slot it will run in: its own for the first `slots`, any slot for the others
             AnchorInfo& A = P.info[t];
-            if (A.U == 0) continue;
-            const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
-            const uint64_t nb_max = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
-            const uint64_t fit = std::min<uint64_t>(nb_max, slot_entries / ((uint64_t) A.U * kBand));
-            if (fit * kBand > A.W) A.W = (uint32_t) (fit * kBand);
+            A.t_off = 0;
+            const uint64_t room = t < slots ? slot_size[t] : min_slot;
+            const uint64_t wb = A.U ? std::min<uint64_t>(nbmax[t], room / ((uint64_t) A.U * kBand)) : 1;
+            A.W = (uint32_t) (std::max<uint64_t>(wb, 1) * kBand);
         }
-        const uint64_t slots = std::min<uint64_t>(std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1)), budget_entries / slot_entries);
-        if (slots == 0) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
-        ADK_TRY(ensure(c, c->scratch5, sizeof(double) * slots * slot_entries));
+        ADK_TRY(ensure(c, c->scratch5, sizeof(double) * std::max<uint64_t>(slot_off[slots], 32)));
+        ADK_TRY(ensure(c, c->area_slot_off, sizeof(uint64_t) * (slots + 1)));
+        ADK_CUDA(c, cudaMemcpyAsync(c->area_slot_off.p, slot_off.data(), sizeof(uint64_t) * (slots + 1), cudaMemcpyHostToDevice, c->stream));
+        const uint64_t slot_entries = slot_off[slots] / slots;        // mean, for the debug line
         ADK_TRY(ensure(c, c->area_boards, sizeof(BandBoard) * slots));
         const uint32_t hull_stride = (n + 8) & ~3u;
         ADK_TRY(ensure(c, c->area_keep_hull, sizeof(int32_t) * (size_t) hull_stride * slots));
@@ -1201,7 +1302,7 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
             attr[0].val.clusterDim.x = CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
             cfg.attrs = attr; cfg.numAttrs = 1;
             ADK_CUDA(c, cudaLaunchKernelEx(&cfg, k_area_rows, d_info, 0u, cnt, &so_->queue, (const SrcRec*) d_recs, (const uint32_t*) d_nsrc,
-                                           (const uint32_t*) d_rowbase, c->scratch5.as<double>(), (uint64_t) slot_entries, K, amax, cap_rows,
+                                           (const uint32_t*) d_rowbase, c->scratch5.as<double>(), (const uint64_t*) c->area_slot_off.as<uint64_t>(), K, amax, cap_rows,
                                            c->area_boards.as<BandBoard>(), (const double*) c->x.as<double>(), (const double*) c->y.as<double>(),
                                            (const uint16_t*) d_srcl, (const int32_t*) d_rowpt, c->area_keep_hull.as<int32_t>(), hull_stride,
                                            (const uint32_t*) c->area_mcr.as<uint32_t>()));

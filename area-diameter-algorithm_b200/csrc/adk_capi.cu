@@ -143,7 +143,7 @@ void adk_destroy(adk_ctx* h)
     if (c->stream) cudaStreamSynchronize(c->stream);
     adk::DevBuf* bufs[] = {&c->x, &c->y, &c->ang, &c->d2c, &c->cw, &c->modpi, &c->rank, &c->below, &c->coll, &c->rb, &c->yorder,
                            &c->above, &c->scratch0, &c->scratch1, &c->scratch2, &c->scratch3, &c->scratch4, &c->scratch5,
-                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards, &c->area_keep_hull, &c->area_mcr, &c->tile_buf};
+                           &c->scratch6, &c->arena, &c->small, &c->ad_order, &c->ad_ovf, &c->ad_cta, &c->ad_aux, &c->area_boards, &c->area_keep_hull, &c->area_mcr, &c->area_slot_off, &c->tile_buf};
     for (adk::DevBuf* b : bufs) adk::free_buf(*b);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
     if (c->ev0) cudaEventDestroy(c->ev0);

@@ -52,6 +52,7 @@ struct Ctx
     DevBuf ad_order, ad_ovf, ad_cta;   // AD: processing order, overflow lists, per-CTA bests
     DevBuf ad_aux;                 // AD: per-CTA order / suffix-start tables and spill workspaces
     DevBuf area_boards;            // A: per-cluster band progress boards of the row sweep
+    DevBuf area_slot_off;          // A: start of every resident cluster's table slot in scratch5 (entries)
     DevBuf area_mcr;               // A: per table entry, the largest c among the records that read it (stop rule of the row sweep)
     DevBuf area_keep_hull;         // A: per-cluster polygon of the cluster's best anchor (walked back inside the row sweep)
     bool area_keep_valid = false;  // ... valid for the resident point set and these bounds (see area_finish)

@@ -16,6 +16,7 @@ Usage: python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|referenc
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -69,6 +70,28 @@ def frozen_answers(sigma):
     except Exception:
         pass
     return out
+
+
+def witness_is_valid(x, y, sol, amax, dmax):
+    """Size-independent check of one answer: the hull is a simple convex cycle, encloses exactly `count` points (boundary
+    included), its area is the reported one and within A, and no two of its vertices are farther apart than D."""
+    hull = sol["hull"]
+    h = len(hull)
+    if not sol.get("found", h > 0):
+        return sol["count"] == 0
+    if h < 3 or len(set(hull)) != h:
+        return False
+    cr = lambda a, b, px, py: (x[b] - x[a]) * (py - y[a]) - (px - x[a]) * (y[b] - y[a])
+    edges = list(zip(hull, hull[1:] + hull[:1]))
+    area2 = sum(x[a] * y[b] - x[b] * y[a] for a, b in edges)
+    sign = 1.0 if area2 > 0 else -1.0
+    if abs(abs(area2) / 2 - sol["area"]) > 1e-7 * max(1.0, sol["area"]) or sol["area"] > amax * (1 + 1e-12):
+        return False
+    if any(sign * cr(a, b, x[c], y[c]) < -2e-10 for (a, b), c in zip(edges, hull[2:] + hull[:2])):
+        return False
+    inside = sum(all(sign * cr(a, b, x[p], y[p]) >= -2e-10 for a, b in edges) for p in range(len(x)))
+    far = max(math.dist((x[a], y[a]), (x[b], y[b])) for a in hull for b in hull)
+    return inside == sol["count"] and far <= dmax * (1 + 1e-12)
 
 
 def load_workload(sigma):
@@ -502,6 +525,12 @@ def run_b200_arm(args):
                 if ref is not None:
                     assert got["count"] == ref["count"] and got["hull"] == ref["hull"] and sorted(got["diam"]) == sorted(ref["diam"]), ("multi", d, got, ref)
         line["answers_checked_against_frozen_reference"] = checked
+        # the diameters with no frozen answer (sigma != 1.5 beyond the D = 2 sample): the witness itself is checked — simple convex
+        # cycle, enclosed-point count = the reported count, area <= A, farthest pair <= D — and the counts must not fall as D grows
+        line["witness_valid"] = [d for d, got in zip(diams, res["last"]) if witness_is_valid(w["x"], w["y"], got, w["amax"], d)]
+        assert len(line["witness_valid"]) == len(diams), ("invalid witness", line["witness_valid"])
+        counts = [r["count"] for r in res["last"]]
+        assert all(a <= b for a, b in zip(counts, counts[1:])) or diams != sorted(diams), counts
         if world == 1 and not args.no_cpu:
             cb = cpu_reference_run(w, steps=2, warmup=0)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "states_per_sec", "cells_per_sec_per_core",

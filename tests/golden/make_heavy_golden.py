@@ -4,6 +4,7 @@
 
   bench.sigma1.5.D{3,4,5,6} : the headline sweep beyond the D = 2 sample (tests/golden/bench_n200.json holds D = 2)
   real.{1..5}.D4            : the cell samples at the real call shape (quality_of_results_comparison.py:194-197)
+  bench.sigma{1.0,0.5}.D2   : the D = 2 solve of the denser sets of the bench fixture
   area.n1000.K16            : BASELINE config 3's point set (synth.gaussian_points(1000, 2.0, 1000)), area path, K = 16
 
 Each job writes tests/golden/heavy/<tag>.json when it ends; `--merge` folds whatever is there into
@@ -46,6 +47,11 @@ def job_list():
     for d in (6.0, 5.0, 4.0, 3.0):
         jobs.append({"tag": f"bench.sigma1.5.D{int(d)}", "name": "bench_n200/1.5", "algo": 2, "kmax": KINF, "amax": fx["amax"],
                      "dmax": d, "x": [float(q[0]) for q in pts], "y": [float(q[1]) for q in pts]})
+    # the D = 2 solve of the two denser sets SURVEY 8d names (sigma = 1.0, 0.5): the only solves of those sweeps a CPU can afford
+    for sigma in ("1.0", "0.5"):
+        pts = fx["sets"][sigma]["points"]
+        jobs.append({"tag": f"bench.sigma{sigma}.D2", "name": f"bench_n200/{sigma}", "algo": 2, "kmax": KINF, "amax": fx["amax"],
+                     "dmax": 2.0, "x": [float(q[0]) for q in pts], "y": [float(q[1]) for q in pts]})
     return jobs
 
 
@@ -67,12 +73,18 @@ def run(job):
 
 
 def merge():
-    runs = []
+    dest = os.path.join(HERE, "heavy_outputs.json")
+    by_tag = {}
+    if os.path.exists(dest):                         # runs already merged stay (the per-job files are scratch)
+        with open(dest) as f:
+            by_tag = {r["tag"]: r for r in json.load(f)["runs"]}
     for fn in sorted(os.listdir(OUT)):
         if fn.endswith(".json"):
             with open(os.path.join(OUT, fn)) as f:
-                runs.append(json.load(f))
-    with open(os.path.join(HERE, "heavy_outputs.json"), "w") as f:
+                r = json.load(f)
+            by_tag[r["tag"]] = r
+    runs = [by_tag[t] for t in sorted(by_tag)]
+    with open(dest, "w") as f:
         json.dump({"generated_by": "tests/golden/make_heavy_golden.py",
                    "reference_build": "oracle/_ref/libadkref.so: unmodified reference, g++ -O3, long double = x87 80-bit",
                    "runs": runs}, f, separators=(",", ":"))

@@ -1,0 +1,25 @@
+#!/usr/bin/env bash
+# development: config-3 bench for every k_area_rows build variant under build/variants/rows_*.so (+ area parity for two of them)
+# usage: tools/gpu_rows_variants.sh <tag>
+TAG=${1:-rv}
+mkdir -p gpurun_out
+one() { # name lib extra-env
+  n=$1; so=$2; shift 2
+  env "$@" ADK_LIB_PATH=$PWD/$so timeout 200 python bench.py --workload area_n1000 --steps 3 --warmup 2 --no-cpu > gpurun_out/${TAG}_$n.json 2> gpurun_out/${TAG}_$n.err
+  python - "$n" gpurun_out/${TAG}_$n.json <<'PY'
+import json,sys,hashlib
+try:
+    d=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1]); a=d["answers"][0]
+    print(sys.argv[1], "ms/solve %.1f" % d["ms_per_step"], "rows kernel %.1f ms" % d["roofline"]["avg_launch_ms"], "frac %.3f" % d["roofline"]["frac"], "count", a["count"], "area %.12g" % a["area"], hashlib.md5(str(a["hull"]).encode()).hexdigest()[:8])
+except Exception as e: print(sys.argv[1], "FAILED", e)
+PY
+}
+for so in build/variants/rows_*.so; do one $(basename $so .so) $so X=1; done
+one rows_s16c4_cs2 build/variants/rows_s16c4.so ADK_AREA_CLUSTER=2
+one rows_s32c2_cs2 build/variants/rows_s32c2.so ADK_AREA_CLUSTER=2
+for v in s16c4 s32c2; do
+  (ADK_LIB_PATH=$PWD/build/variants/rows_$v.so timeout 600 python -m pytest tests -m gpu -q -x -k "area_path or config3 or edge_cases or oracle_differential or shards_merge or batch_area or tiled or slope" > gpurun_out/${TAG}_pytest_$v.log 2>&1; echo "pytest exit $?" >> gpurun_out/${TAG}_pytest_$v.log)
+  tail -2 gpurun_out/${TAG}_pytest_$v.log
+done
+timeout 300 python bench.py --sigma 1.0 --steps 3 --warmup 3 --no-cpu > gpurun_out/${TAG}_sigma1.0.json 2> gpurun_out/${TAG}_sigma1.0.err; echo "sigma1.0 exit $?"; cut -c1-400 gpurun_out/${TAG}_sigma1.0.json
+timeout 400 python bench.py --sigma 0.5 --steps 1 --warmup 1 --no-cpu > gpurun_out/${TAG}_sigma0.5.json 2> gpurun_out/${TAG}_sigma0.5.err; echo "sigma0.5 exit $?"; cut -c1-400 gpurun_out/${TAG}_sigma0.5.json; tail -3 gpurun_out/${TAG}_sigma0.5.err
