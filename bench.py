@@ -331,6 +331,8 @@ def run_b200_arm(args):
     w = load_workload(args.sigma)
     n, amax, diams = w["n"], w["amax"], w["diameters"]
     solver = pkg.Solver(local)
+    if args.memory_budget_gb > 0:
+        solver.set_memory_budget(int(args.memory_budget_gb * 2**30))
     stream = torch.cuda.Stream(device=dev)
     solver.set_stream(stream.cuda_stream)
     solver.set_reuse(False)      # every solve recomputes the count tables and orders, as the reference does on every call
@@ -575,6 +577,8 @@ def run_aux_workload(args):
     adist = importlib.import_module("area_diameter_algorithm_b200.dist")
     capi = importlib.import_module("area_diameter_algorithm_b200.capi")
     solver = pkg.Solver(local)
+    if args.memory_budget_gb > 0:
+        solver.set_memory_budget(int(args.memory_budget_gb * 2**30))
     stream = torch.cuda.Stream(device=dev)
     solver.set_stream(stream.cuda_stream)
     solver.set_reuse(False)      # every solve recomputes the count tables and orders, as the reference does on every call
@@ -729,6 +733,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sigma", type=float, default=1.5, help="cluster width of the synthetic n=200 set (fixture: 3.0, 2.0, 1.5, 1.0, 0.5)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--memory-budget-gb", type=float, default=0.0, help="development: cap the DP workspace (adk_set_memory_budget); 0 = the library's default")
     ap.add_argument("--ref-solves", type=int, default=1, help="--impl reference: solves of the sweep per step (1 = D=2, 2 = D=2 and D=3; "
                     "D=3 alone is ~10 core-minutes per replica)")
     ap.add_argument("--instance-sharding", action="store_true", help="cells_batch on N > 1 GPUs: whole instances per rank (adk_solve_batch) "

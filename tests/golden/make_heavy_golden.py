@@ -82,7 +82,7 @@ def merge():
         if fn.endswith(".json"):
             with open(os.path.join(OUT, fn)) as f:
                 r = json.load(f)
-            by_tag[r["tag"]] = r
+            by_tag[r["tag"]] = {**by_tag.get(r["tag"], {}), **r}     # keys added later (tests/golden/add_f64_entries.py) stay
     runs = [by_tag[t] for t in sorted(by_tag)]
     with open(dest, "w") as f:
         json.dump({"generated_by": "tests/golden/make_heavy_golden.py",

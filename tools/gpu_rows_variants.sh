@@ -15,11 +15,5 @@ except Exception as e: print(sys.argv[1], "FAILED", e)
 PY
 }
 for so in build/variants/rows_*.so; do one $(basename $so .so) $so X=1; done
-one rows_s16c4_cs2 build/variants/rows_s16c4.so ADK_AREA_CLUSTER=2
-one rows_s32c2_cs2 build/variants/rows_s32c2.so ADK_AREA_CLUSTER=2
-for v in s16c4 s32c2; do
-  (ADK_LIB_PATH=$PWD/build/variants/rows_$v.so timeout 600 python -m pytest tests -m gpu -q -x -k "area_path or config3 or edge_cases or oracle_differential or shards_merge or batch_area or tiled or slope" > gpurun_out/${TAG}_pytest_$v.log 2>&1; echo "pytest exit $?" >> gpurun_out/${TAG}_pytest_$v.log)
-  tail -2 gpurun_out/${TAG}_pytest_$v.log
-done
-timeout 300 python bench.py --sigma 1.0 --steps 3 --warmup 3 --no-cpu > gpurun_out/${TAG}_sigma1.0.json 2> gpurun_out/${TAG}_sigma1.0.err; echo "sigma1.0 exit $?"; cut -c1-400 gpurun_out/${TAG}_sigma1.0.json
-timeout 400 python bench.py --sigma 0.5 --steps 1 --warmup 1 --no-cpu > gpurun_out/${TAG}_sigma0.5.json 2> gpurun_out/${TAG}_sigma0.5.err; echo "sigma0.5 exit $?"; cut -c1-400 gpurun_out/${TAG}_sigma0.5.json; tail -3 gpurun_out/${TAG}_sigma0.5.err
+(timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/${TAG}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/${TAG}_pytest_gpu.log)
+tail -3 gpurun_out/${TAG}_pytest_gpu.log
