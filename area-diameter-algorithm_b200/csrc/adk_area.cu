@@ -491,6 +491,42 @@ __device__ __forceinline__ void row_segment(uint32_t ns, uint32_t rd, uint32_t w
 // Bands past the last finite level may be started before the stop rule can know (at most CS - 1 of them): they produce +inf only.
 __device__ void hull_diameter_dev(const double* x, const double* y, const int32_t* hull, uint32_t cnt, uint32_t* out);
 
+// Local prefix minima of one warp's segment (see k_area_rows).  BAND0: the band that holds level 3, whose lane 0 uses the m == 3
+// variant of c (Eppstein.cpp:25-28); the other bands do not pay for the choice.
+template <bool BAND0>
+__device__ __forceinline__ double prefix_pass(const SrcRec* st_rec, double* cell, uint32_t cnt, uint32_t m, bool active, double amax)
+{
+    const int mk = active ? (int) m : 0;
+    const bool is3 = BAND0 && m == 3u;
+    const uint4* rec4 = reinterpret_cast<const uint4*>(st_rec);          // area (x, y) | gidx (z) | c, c3 (w)
+    double run = INFINITY;
+#pragma unroll 1
+    for (uint32_t u0 = 0; u0 < cnt; u0 += 4)
+    {
+        uint4 rw[4]; double v[4];
+#pragma unroll
+        for (uint32_t t = 0; t < 4; ++t) rw[t] = rec4[u0 + t];
+#pragma unroll
+        for (uint32_t t = 0; t < 4; ++t) v[t] = cell[t * kStageDoubles + (rw[t].w & 1u)];
+        __syncwarp();                       // every lane has its elements before a neighbour overwrites them
+#pragma unroll
+        for (uint32_t t = 0; t < 4; ++t)
+        {
+            const uint32_t c = (BAND0 && is3) ? ((rw[t].w >> 16) & 0x7fffu) : (rw[t].w & 0xffffu);
+            const int k = mk - (int) c;
+            const bool real = k >= 3 && rw[t].z != kNoPrev;
+            const int hi = real ? __double2hiint(v[t]) : (k == 2 ? 0 : 0x7ff00000);
+            const int lw = real ? __double2loint(v[t]) : 0;
+            const double cur = __dadd_rn(__hiloint2double(hi, lw), __hiloint2double((int) rw[t].y, (int) rw[t].x));
+            v[t] = cur <= amax ? cur : INFINITY;
+        }
+#pragma unroll
+        for (uint32_t t = 0; t < 4; ++t) { run = v[t] < run ? v[t] : run; cell[t * kStageDoubles + 1u] = run; }
+        cell += 4u * kStageDoubles;
+    }
+    return run;
+}
+
 // The best anchor a cluster has met so far, with its polygon already walked back (see the end of k_area_rows).
 struct KeepRec { uint32_t found, m; double area; uint32_t order, len, ok, diam[2]; int32_t pt, row, pad; };
 
@@ -523,7 +559,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
     __shared__ unsigned long long s_best[kBand];
     __shared__ long long s_req;
     __shared__ int s_row, s_go;
-    __shared__ __align__(16) uint16_t s_mc[kRowWarps][kSeg][kReachBuckets];
+    __shared__ __align__(16) uint16_t s_mc[kRowWarps][kReachBuckets];    // per warp and round: largest reader c per area bucket
     __shared__ unsigned int s_reach;
     // [cap_rows] source counts, [cap_rows] row bases (anchors with more rows read them from global memory), then the staging
     // area: kStageDoubles doubles per source of the round, kSeg sources per warp
@@ -621,13 +657,15 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                 // The source records of a round are requested one round ahead (they depend on nothing).
                 uint32_t nj = 0, nr = 0;
                 while (nj < rows && ansrc[nj] == 0) ++nj;
-                SrcRec nxt = SrcRec{0.0, kNoPrev, 0, 0};
+                // kept as raw words until the round that uses them: unpacking right behind the loads would wait for them
+                const uint4* arec4 = reinterpret_cast<const uint4*>(arec);                 // area (x, y) | gidx (z) | c, c3 (w)
+                uint4 nxt = make_uint4(0u, 0u, kNoPrev, 0u);
                 uint4 nxt_mc = make_uint4(0u, 0u, 0u, 0u);   // the reader summary of the entry this lane's record produces (see k_area_prep)
                 uint32_t reach_l = 0;           // highest level a finite entry written by this lane (level m) can feed
                 {
                     uint32_t nb = 0, nc = 0;
                     if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
-                    if (lane < nc) { nxt = arec[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
+                    if (lane < nc) { nxt = arec4[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
                 }
                 for (uint32_t jj = 0; jj < rows; ++jj)
                 {
@@ -658,27 +696,35 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         uint32_t base, cnt;
                         row_segment(ns, rd, warp, base, cnt);
                         __syncwarp();
+                        {   // the largest reader c per area bucket over the entries this warp produces in this round (see the stop rule below)
+                            const bool mine_ = lane < cnt;
+                            const uint32_t q[4] = {mine_ ? nxt_mc.x : 0u, mine_ ? nxt_mc.y : 0u, mine_ ? nxt_mc.z : 0u, mine_ ? nxt_mc.w : 0u};
+                            uint32_t packed[4];
+#pragma unroll
+                            for (uint32_t h = 0; h < 4; ++h)
+                                packed[h] = __reduce_max_sync(0xffffffffu, q[h] & 0xffffu) | (__reduce_max_sync(0xffffffffu, q[h] >> 16) << 16);
+                            if (lane == 0) *reinterpret_cast<uint4*>(s_mc[warp]) = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+                        }
                         if (lane < cnt)
                         {
-                            st_rec[lane] = nxt; *reinterpret_cast<uint4*>(s_mc[warp][lane]) = nxt_mc;
+                            *reinterpret_cast<uint4*>(&st_rec[lane]) = nxt;
                             // Where the 32 levels m - c (m = lo .. lo + 31) of this source's predecessor entry lie: level lo - c sits at
                             // position p of band slot s0 = bm + floor(-c / 32), the window runs on into slot s0 + 1 (both modulo the
                             // ring).  Lane L of the band reads window element p + L; the window is fetched as 16-byte pieces
                             // starting at element p & ~1, so lane L finds its element at index (p & 1) + L of the staged copy.  A
                             // source none of whose levels exists yet (c + 3 > lo + 31, or past K) is not fetched at all.
-                            const uint32_t c = nxt.c, p = (0u - c) & 31u, p2 = p & ~1u;
+                            const uint32_t c = nxt.w & 0xffffu, p = (0u - c) & 31u, p2 = p & ~1u;
                             const uint64_t mtop = K < (uint64_t) lo + 31u ? K : (uint64_t) lo + 31u;
-                            const bool fetch = nxt.gidx != kNoPrev && (uint64_t) c + 3u <= mtop;
+                            const bool fetch = nxt.z != kNoPrev && (uint64_t) c + 3u <= mtop;
                             int s0 = (int) bm + ((-(int) c) >> 5);
                             if (s0 < 0) s0 += (int) Wb;
                             const int s1 = s0 + 1 == (int) Wb ? 0 : s0 + 1;
                             SrcPlan pl;
-                            pl.first = (unsigned long long) __cvta_generic_to_global(T) + (uint64_t) nxt.gidx * W8 + (uint64_t) s0 * (kBand * 8u) + p2 * 8u;
+                            pl.first = (unsigned long long) __cvta_generic_to_global(T) + (uint64_t) nxt.z * W8 + (uint64_t) s0 * (kBand * 8u) + p2 * 8u;
                             pl.wrap = (s1 - s0 - 1) * (int) (kBand * 8u);
                             pl.pieces = (uint16_t) (fetch ? 16u + (p & 1u) : 0u);
                             pl.turn = (uint16_t) ((kBand - p2) >> 1);
                             st_plan[lane] = pl;
-                            s_mc[warp][lane][kReachBuckets - 1] |= (uint16_t) ((c & 1u) << 15);     // the parity travels with the reader summary
                         }
                         else if (lane < kSeg)
                         {   // the loops below run in groups of four sources: the padding fetches nothing and adds +inf
@@ -690,7 +736,7 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         {
                             uint32_t nb = 0, nc = 0;
                             if (nj < rows) row_segment(ansrc[nj], nr, warp, nb, nc);
-                            if (lane < nc) { nxt = arec[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
+                            if (lane < nc) { nxt = arec4[(size_t) nj * acap + nb + lane]; nxt_mc = amcr[2u * (abase[nj] + nb + lane)]; }
                         }
                         // every predecessor vector of the segment is on its way before any of them is used
                         {
@@ -714,42 +760,15 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         }
                         async_copy_wait();
                         __syncwarp();
-                        // local prefix minima: the staged element of this lane becomes the running minimum of the segment up to u.
-                        // Branch-free: level m - c is a real table entry (>= 3), the constant level 2 (T[2] = 0) or nothing (+inf),
-                        // Eppstein.cpp:210-216; lanes past K behave like level 0.
-                        double run = INFINITY;
-                        {
-                            const int mk = active ? (int) m : 0;
-                            const bool is3 = m == 3u;
-                            double* cell = stage + lane;
-                            const uint4* rec4 = reinterpret_cast<const uint4*>(st_rec);          // area (x, y) | gidx (z) | c, c3 (w)
-#pragma unroll 1
-                            for (uint32_t u0 = 0; u0 < cnt; u0 += 4)
-                            {
-                                uint4 rw[4]; double v[4]; double* mine[4];
-#pragma unroll
-                                for (uint32_t t = 0; t < 4; ++t) rw[t] = rec4[u0 + t];
-#pragma unroll
-                                for (uint32_t t = 0; t < 4; ++t) { mine[t] = cell + t * kStageDoubles + (rw[t].w & 1u); v[t] = *mine[t]; }
-#pragma unroll
-                                for (uint32_t t = 0; t < 4; ++t)
-                                {
-                                    const uint32_t c = is3 ? ((rw[t].w >> 16) & 0x7fffu) : (rw[t].w & 0xffffu);
-                                    const int k = mk - (int) c;
-                                    const bool real = k >= 3 && rw[t].z != kNoPrev;
-                                    const int hi = real ? __double2hiint(v[t]) : (k == 2 ? 0 : 0x7ff00000);
-                                    const int lw = real ? __double2loint(v[t]) : 0;
-                                    const double cur = __dadd_rn(__hiloint2double(hi, lw), __hiloint2double((int) rw[t].y, (int) rw[t].x));
-                                    v[t] = cur <= amax ? cur : INFINITY;
-                                }
-#pragma unroll
-                                for (uint32_t t = 0; t < 4; ++t) { run = v[t] < run ? v[t] : run; *mine[t] = run; }
-                                cell += 4u * kStageDoubles;
-                            }
-                        }
+                        // local prefix minima: lane L takes its element (index parity + L of the staged copy) and leaves the running
+                        // minimum of the segment up to u at index L + 1, whatever the parity (the loads of a group of four all come
+                        // before its stores).  Branch-free: level m - c is a real table entry (>= 3), the constant level 2 (T[2] = 0)
+                        // or nothing (+inf), Eppstein.cpp:210-216; lanes past K behave like level 0.
+                        const double run = b == 0 ? prefix_pass<true>(st_rec, stage + lane, cnt, m, active, amax)
+                                                  : prefix_pass<false>(st_rec, stage + lane, cnt, m, active, amax);
                         // the first element of the whole list is no change point if it is finite (its running minimum is its own value)
                         bool head_finite = false;
-                        if (base == 0 && cnt) head_finite = (st_rec[0].c3 & 0x8000u) && stage[lane + ((uint32_t) st_rec[0].c & 1u)] < INFINITY;
+                        if (base == 0 && cnt) head_finite = (st_rec[0].c3 & 0x8000u) && stage[lane + 1u] < INFINITY;
                         s_tot[par][warp][lane] = run;
                         __syncthreads();
                         double cin = carry, all = carry;
@@ -766,27 +785,26 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                         char* outp = reinterpret_cast<char*>(T + mypos) + (uint64_t) (obase + base) * W8;
                         uint32_t changes = 0;
                         {
-                            const double* cell = stage + lane;
-                            const uint16_t* mc = s_mc[warp][0];
+                            const double* cell = stage + lane + 1u;
 #pragma unroll 4
                             for (uint32_t u = 0; u < cnt; ++u)
                             {
-                                const uint32_t w7 = mc[kReachBuckets - 1];                   // largest c among the entry's readers | parity << 15
-                                const double mine = cell[w7 >> 15];
+                                const double mine = *cell;
                                 const double g = mine < cin ? mine : cin;
                                 changes += g < before ? 1u : 0u;                             // Eppstein.cpp:228-232
                                 before = g;
                                 if (active) __stcg(reinterpret_cast<double*>(outp), g);      // Eppstein.cpp:234
-                                if (g < INFINITY && m + (w7 & 0x7fffu) > reach_l)
-                                {   // readers of this entry that can still fit under the area bound: area <= A - g (inflated: never stop early);
-                                    // skipped when even the entry's largest reader cannot raise the bound this lane already holds
-                                    const int bs = min((int) kReachBuckets - 1, max(0, (int) (__dadd_rn(__dmul_rn(__dsub_rn(amax, g), 1.000001), 1e-12) * inv_bucket)));
-                                    reach_l = max(reach_l, m + ((uint32_t) mc[bs] & 0x7fffu));
-                                }
                                 outp += W8;
                                 cell += kStageDoubles;
-                                mc += kReachBuckets;
                             }
+                        }
+                        if (cnt && before < INFINITY)
+                        {   // Stop rule: the highest level a finite entry of level m can feed.  `before` is the smallest value this lane
+                            // wrote in the round; readers that still fit under the area bound have area <= A - g (inflated: never stop
+                            // early), and s_mc holds, per area bucket, the largest c among the readers of the round's entries.  One bound per
+                            // lane and round instead of one per entry: never below the per-entry bound, and a few instructions per round.
+                            const int bs = min((int) kReachBuckets - 1, max(0, (int) (__dadd_rn(__dmul_rn(__dsub_rn(amax, before), 1.000001), 1e-12) * inv_bucket)));
+                            reach_l = max(reach_l, m + (uint32_t) s_mc[warp][bs]);
                         }
                         req += changes;
                         carry = all;

@@ -10,7 +10,7 @@ one() { # name lib extra-env
 import json,sys,hashlib
 try:
     d=json.loads(open(sys.argv[2]).read().strip().splitlines()[-1]); a=d["answers"][0]
-    print(sys.argv[1], "ms/solve %.1f" % d["ms_per_step"], "rows kernel %.1f ms" % d["roofline"]["avg_launch_ms"], "frac %.3f" % d["roofline"]["frac"], "count", a["count"], "area %.12g" % a["area"], hashlib.md5(str(a["hull"]).encode()).hexdigest()[:8])
+    print(sys.argv[1], "cells/step %.4g" % (d["value"]*d["ms_per_step"]/1e3), "ms/solve %.1f" % d["ms_per_step"], "rows kernel %.1f ms" % d["roofline"]["avg_launch_ms"], "frac %.3f" % d["roofline"]["frac"], "count", a["count"], "area %.12g" % a["area"], hashlib.md5(str(a["hull"]).encode()).hexdigest()[:8])
 except Exception as e: print(sys.argv[1], "FAILED", e)
 PY
 }
