@@ -127,53 +127,64 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
             uint32_t ns = 0, kept = 0, ndef = 0;
             SrcRec* rrec = arec + (size_t) jj * acap;
             uint16_t* rsrc = asrc + (size_t) jj * acap;
-            for (uint32_t base = 1; base < len; base += 32)
+            // two chunks of 32 ring positions per step: the loads of both (ring -> slot -> coordinates -> count tables, four
+            // dependent round trips) are in flight together, the lists are then extended in order
+            struct Cand { bool keep, src, defer; int p; uint32_t sl; double area; uint32_t cfull, c3; };
+            auto eval = [&](uint32_t t) -> Cand
             {
-                const uint32_t t = base + lane;
-                bool keep = false, src = false, defer = false;
-                int p = -1; uint32_t sl = 0xffff;
-                double area = 0.0; uint32_t cfull = 0, c3 = 0;
+                Cand e{false, false, false, -1, 0xffffu, 0.0, 0u, 0u};
                 if (t < len)
                 {
-                    p = ring_j[(r0 + t) % len];
-                    sl = slot_of[p];
-                    if (sl != 0xffff)
+                    e.p = ring_j[(r0 + t) % len];
+                    e.sl = slot_of[e.p];
+                    if (e.sl != 0xffff)
                     {
-                        const double px = x[p], py = y[p];
+                        const double px = x[e.p], py = y[e.p];
                         const double s = signed_area(ix, iy, jx, jy, px, py);
-                        if (near_zero(s)) defer = py > jy;              // Eppstein.cpp:76-82
+                        if (near_zero(s)) e.defer = py > jy;              // Eppstein.cpp:76-82
                         else
                         {
-                            keep = true;
+                            e.keep = true;
                             if (s > 0.0)
                             {   // left of pi->pj: a candidate predecessor (Eppstein.cpp:209-214)
-                                area = fabs(s);
-                                const int cnt = cij + T.C(j, p) + points_in_triangle(T, i, ix, iy, j, jx, jy, p, px, py);
-                                cfull = 1u + (uint32_t) cnt;
-                                c3 = cfull + (uint32_t) T.C(p, i);      // the m == 3 extra term (Eppstein.cpp:25-28)
-                                src = area <= amax && (uint64_t) cfull <= K;
+                                e.area = fabs(s);
+                                const int cnt = cij + T.C(j, e.p) + points_in_triangle(T, i, ix, iy, j, jx, jy, e.p, px, py);
+                                e.cfull = 1u + (uint32_t) cnt;
+                                e.c3 = e.cfull + (uint32_t) T.C(e.p, i);  // the m == 3 extra term (Eppstein.cpp:25-28)
+                                e.src = e.area <= amax && (uint64_t) e.cfull <= K;
                             }
                         }
                     }
                 }
-                const uint32_t km = __ballot_sync(0xffffffffu, keep), sm = __ballot_sync(0xffffffffu, src);
-                const uint32_t dm = __ballot_sync(0xffffffffu, defer);
+                return e;
+            };
+            auto commit = [&](const Cand& e)
+            {
+                const uint32_t km = __ballot_sync(0xffffffffu, e.keep), sm = __ballot_sync(0xffffffffu, e.src);
+                const uint32_t dm = __ballot_sync(0xffffffffu, e.defer);
                 const uint32_t lt = (1u << lane) - 1u;
-                if (keep) Q[(size_t) jj * rows + sl] = (uint16_t) (ns + __popc(sm & lt));
-                if (src)
+                if (e.keep) Q[(size_t) jj * rows + e.sl] = (uint16_t) (ns + __popc(sm & lt));
+                if (e.src)
                 {
                     const uint32_t k = ns + __popc(sm & lt);
                     const uint32_t head = (k == 0 && kept == 0 && (km & lt) == 0u) ? 0x8000u : 0u;
-                    rsrc[k] = (uint16_t) sl;
-                    rrec[k] = SrcRec{area, kNoPrev, (uint16_t) cfull, (uint16_t) (c3 | head)};
+                    rsrc[k] = (uint16_t) e.sl;
+                    rrec[k] = SrcRec{e.area, kNoPrev, (uint16_t) e.cfull, (uint16_t) (e.c3 | head)};
                 }
-                if (defer)
+                if (e.defer)
                 {
                     const uint32_t d = ndef + __popc(dm & lt);
-                    if (d < 32) s_def[warp][d] = p;
+                    if (d < 32) s_def[warp][d] = e.p;
                 }
                 if (ndef + __popc(dm) > 32u && lane == 0) A.defer_overflow = 1u;     // never truncate silently
                 ns += __popc(sm); kept += __popc(km); ndef = min(32u, ndef + __popc(dm));
+            };
+#pragma unroll 1
+            for (uint32_t base = 1; base < len; base += 64)
+            {
+                const Cand e0 = eval(base + lane), e1 = eval(base + 32u + lane);
+                commit(e0);
+                commit(e1);
             }
             __syncwarp();
             if (ndef && lane == 0)
@@ -244,19 +255,36 @@ k_area_prep(const double* __restrict__ x, const double* __restrict__ y, uint32_t
             const uint32_t ns = ansrc[jj];
             SrcRec* rrec = arec + (size_t) jj * acap;
             const uint16_t* rsrc = asrc + (size_t) jj * acap;
-            for (uint32_t k = lane; k < ns; k += 32)
+            // four records per lane at a time: the chain record -> Q column -> row base is three dependent memory round trips
+#pragma unroll 1
+            for (uint32_t k0 = lane; k0 < ns; k0 += 128)
             {
-                const uint32_t lp = rsrc[k];
-                const uint32_t q = Q[(size_t) lp * rows + jj];
-                const uint32_t g = (q == 0xffff || q == 0) ? kNoPrev : abase[lp] + q - 1;
-                rrec[k].gidx = g;
-                const uint32_t c = rrec[k].c;
-                if (g != kNoPrev)
+                uint32_t lp[4], q[4], ab[4], cc[4]; double ar[4];
+#pragma unroll
+                for (uint32_t t = 0; t < 4; ++t) { const uint32_t k = k0 + 32u * t; lp[t] = k < ns ? rsrc[k] : 0u; }
+#pragma unroll
+                for (uint32_t t = 0; t < 4; ++t)
                 {
-                    const int br = min((int) kReachBuckets - 1, max(0, (int) (rrec[k].area * inv_bucket)));
-                    atomicMax(amcr + (size_t) g * kReachBuckets + br, c);
+                    const uint32_t k = k0 + 32u * t;
+                    q[t] = k < ns ? Q[(size_t) lp[t] * rows + jj] : 0xffffu;
+                    ab[t] = abase[lp[t]];
+                    cc[t] = k < ns ? rrec[k].c : 0u;
+                    ar[t] = k < ns ? rrec[k].area : 0.0;
                 }
-                cm = max(cm, c);
+#pragma unroll
+                for (uint32_t t = 0; t < 4; ++t)
+                {
+                    const uint32_t k = k0 + 32u * t;
+                    if (k >= ns) continue;
+                    const uint32_t g = (q[t] == 0xffff || q[t] == 0) ? kNoPrev : ab[t] + q[t] - 1;
+                    rrec[k].gidx = g;
+                    if (g != kNoPrev)
+                    {
+                        const int br = min((int) kReachBuckets - 1, max(0, (int) (ar[t] * inv_bucket)));
+                        atomicMax(amcr + (size_t) g * kReachBuckets + br, cc[t]);
+                    }
+                    cm = max(cm, cc[t]);
+                }
             }
         }
         __syncthreads();
