@@ -604,8 +604,12 @@ def run_aux_workload(args):
             if resident or world > 1:
                 part, st = (solver.area_partial_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, rank, world) if resident else
                             solver.area_partial(x, y, None, amax, rank, world))
-                best = adist.merge_partials(adist.gather_partials(part, device=dev))
-                r = solver.area_finish_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, best, True) if rank == 0 else None
+                parts = adist.gather_partials(part, device=dev)
+                best = adist.merge_partials(parts)
+                # the rank whose anchor won finishes: its cluster still holds the polygon it walked back during the sweep (no re-run)
+                owner = adist.owner_of(best, parts)
+                r = solver.area_finish_dev(d_x.data_ptr(), d_y.data_ptr(), n, None, amax, best, True) if rank == owner else None
+                r = adist.share_result(r, owner, n, device=dev)
                 return st["cells_executed"], st["dp_ms"], r
             r = solver.solve_area_host(h_x.data_ptr(), h_y.data_ptr(), n, None, amax, True)
             return r["cells_executed"], r["dp_ms"], r
