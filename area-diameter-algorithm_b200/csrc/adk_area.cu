@@ -454,10 +454,10 @@ k_area_dp(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsigne
 // 256-byte vector.  Traffic per cell = 8 B read + 8 B written (the algorithmic 16 B); the level wavefront above re-reads
 // the 16-byte source record at every level and pulls a 64-byte DRAM burst for every 8-byte gather (80 B per cell measured).
 // Table layout: T[compact source index][ring of Wb bands][32 levels].
-// One CTA per anchor, one row at a time: the warps take 32 sources each, request all their predecessor vectors at once
-// (one memory round trip per 32 x warps sources), form local prefix minima in registers, exchange the segment minima
-// through shared memory and write the final vectors.  Rows are strictly ordered inside the CTA, so no flags are needed;
-// bands are swept one after the other, and after each band the stop rule of the wavefront applies.
+// One CTA per anchor, one row at a time: the warps take up to kSeg sources each, request all their predecessor vectors at once
+// (one memory round trip per kSeg x warps sources; asynchronous copies into shared memory, see SrcPlan), form local prefix minima
+// in place, exchange the segment minima through shared memory and write the final vectors.  Rows are strictly ordered inside the
+// CTA, so no flags are needed; bands are swept one after the other, and after each band the stop rule applies.
 #ifndef ADK_ROW_THREADS
 #define ADK_ROW_THREADS 256
 #endif
@@ -650,22 +650,18 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                     // band is not needed.
                     if (threadIdx.x == 0)
                     {
-                        uint32_t ktop = 2;
                         const uint32_t t0 = b + CS > kMaxRing ? b + CS - kMaxRing : 0u;      // bands whose board slot is still theirs
                         for (uint32_t t = t0; t + CS <= b; ++t)
-                        {
+                        {   // every band up to b - CS has published its share of `reach`
                             const uint32_t sl = t % kMaxRing;
                             while (vprog[sl] != (((unsigned long long) (t + 1) << 32) | 0xffffffffull)) __nanosleep(64);
                             __threadfence();
-                            const unsigned int tp = *reinterpret_cast<volatile unsigned int*>(&B.top[sl]);
-                            if (tp) ktop = tp;
                         }
                         const uint64_t lo_done = 3u + kBand * (b - CS);
                         const uint64_t hi_done = K < lo_done + kBand - 1 ? K : lo_done + kBand - 1;
                         // Nothing beyond hi_done can be finite once hi_done has passed every level a finite entry can feed (its level
-                        // + the largest c among its readers) and every level the constant level 2 can feed (2 + c).  ktop + cmax, the
+                        // + the largest c among its readers) and every level the constant level 2 can feed (2 + c).  "top finite level + cmax", the
                         // rule of round 1, is the same bound with the anchor-wide cmax in place of the per-entry one.
-                        (void) ktop;
                         const uint64_t reach = max((uint64_t) *reinterpret_cast<volatile unsigned int*>(&B.reach), (uint64_t) cmax + 2u);
                         s_go = (hi_done >= K || hi_done >= reach) ? 0 : 1;
                     }
@@ -679,7 +675,6 @@ k_area_rows(AnchorInfo* __restrict__ info, uint32_t first, uint32_t count, unsig
                 const uint32_t bm = b % Wb;
                 const uint32_t mypos = bm * kBand + lane;
                 const uint32_t bslot = b % kMaxRing, pslot = (b + kMaxRing - 1) % kMaxRing;
-                const unsigned long long ptag = (unsigned long long) b << 32;        // band b - 1 carries tag (b - 1) + 1
                 double band_best = INFINITY;    // warp 0: best final value of level m over the rows
                 // A row's sources are cut into rounds of at most kRound, and a round evenly into one segment per warp.
                 // The source records of a round are requested one round ahead (they depend on nothing).

@@ -229,3 +229,28 @@ def test_tiled_workflow_window_grid_equals_the_reference(built):
         pops = [len(member(w)) for w in order]
         assert pops == sorted(pops, reverse=True) and pops[-1] >= 1
         assert len(xy) == len(set(map(tuple, pts[c["name"]])))
+
+
+def test_bench_witness_check_accepts_the_frozen_answers_and_rejects_tampered_ones():
+    """bench.py checks every answer of a sweep that has no frozen reference output by its witness alone (sigma = 1.0 / 0.5 beyond D = 2):
+    the check must accept the unmodified reference's own answers and notice a wrong count, a dropped vertex or a diameter bound
+    that the polygon does not meet."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("adk_bench", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    checked = 0
+    for sigma in (1.5, 1.0):
+        w = bench.load_workload(sigma)
+        frozen = {float(r["dmax"]): r for r in w["sample"]}
+        frozen.update(bench.frozen_answers(sigma))
+        assert frozen, sigma
+        for d, r in frozen.items():
+            sol = {"found": True, "count": r["count"], "area": float(r["area"]), "hull": list(r["hull"])}
+            assert bench.witness_is_valid(w["x"], w["y"], sol, w["amax"], d), (sigma, d)
+            assert not bench.witness_is_valid(w["x"], w["y"], dict(sol, count=sol["count"] + 1), w["amax"], d)
+            assert not bench.witness_is_valid(w["x"], w["y"], dict(sol, hull=sol["hull"][:-1]), w["amax"], d)
+            assert not bench.witness_is_valid(w["x"], w["y"], sol, w["amax"], 0.5 * d)
+            assert not bench.witness_is_valid(w["x"], w["y"], sol, 0.5 * float(r["area"]), d)
+            checked += 1
+    assert checked >= 6          # sigma 1.5: D = 2..6, sigma 1.0: D = 2
