@@ -254,3 +254,15 @@ def test_bench_witness_check_accepts_the_frozen_answers_and_rejects_tampered_one
             assert not bench.witness_is_valid(w["x"], w["y"], sol, 0.5 * float(r["area"]), d)
             checked += 1
     assert checked >= 6          # sigma 1.5: D = 2..6, sigma 1.0: D = 2
+
+
+def test_header_is_plain_c(tmp_path):
+    """The drop-in boundary is a C ABI: include/adk.h must compile as C99 (no C++ in the signatures) and adk_partial, the record
+    the ranks exchange, must stay 32 bytes."""
+    src = tmp_path / "t.c"
+    src.write_text('#include "adk.h"\n'
+                   'int main(void) { adk_result r; adk_stats s; (void) r; (void) s; return sizeof(adk_partial) == 32 ? 0 : 1; }\n')
+    exe = tmp_path / "t"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
+                   check=True, capture_output=True)
+    assert subprocess.run([str(exe)]).returncode == 0
