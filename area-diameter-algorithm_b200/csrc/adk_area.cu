@@ -12,6 +12,7 @@
 //     stops as soon as no deeper level can be finite.
 #include "adk_internal.h"
 #include "adk_device.cuh"
+#include "adk_area_plan.h"
 
 #include <cooperative_groups.h>
 #include <cstddef>
@@ -1270,59 +1271,19 @@ int area_run(Ctx* c, AreaPlan& P, uint64_t K, double amax, uint32_t full_m, floa
                 if (v == 0 || t < 0.95 * best) { best = v == 0 ? t : std::min(best, t); CS = 1u << v; }
             }
         }
-        // Table slots.  Cluster k starts with anchor k (the anchors arrive heaviest first) and then pulls from the queue behind the
-        // first `slots` anchors, so its slot must hold anchor k and whatever the queue may still hand out: slot k = max(need of
-        // anchor k, largest need in the tail).  Sizing every slot for the single largest anchor (round 1) took 86-120 GB at
-        // n = 1000 for two CTAs per SM and left no room for more resident CTAs.
-        //   need  = the shortest ring the sweep can run with: ceil(cmax / 32) + CS bands (reach back cmax levels from the oldest band
-        //           in flight), never more than the levels an anchor with this many rows can fill;
-        //   full  = every level the anchor can fill: a ring that never wraps leaves the table complete when the anchor ends, and
-        //           the cluster can then walk its polygon back on the spot (end of k_area_rows) instead of the winner being re-run
-        //           after the solve.  Slots grow from need towards full as far as the memory budget allows (HBM is idle otherwise).
-        std::vector<uint64_t> need(cnt), full(cnt), nbmax(cnt);
-        for (uint32_t t = 0; t < cnt; ++t)
+        // Table slots: one per resident cluster, sized for the anchors that cluster can meet; every anchor's ring fills its slot
+        // (adk_area_plan.h, checked on the CPU by tests/dropin/slot_plan_check.cpp).
+        std::vector<AnchorShape> shapes(cnt);
+        for (uint32_t t = 0; t < cnt; ++t) shapes[t] = AnchorShape{(uint32_t) P.info[t].a, P.info[t].U, P.info[t].cmax};
+        SlotPlan plan;
+        if (!plan_area_slots(shapes, K, CS, resident, budget_entries, kBand, plan))
         {
-            const AnchorInfo& A = P.info[t];
-            const uint64_t top_level = std::min<uint64_t>(K, (uint64_t) A.a + 2);
-            nbmax[t] = std::max<uint64_t>(1, (top_level >= 3 ? top_level - 2 + kBand - 1 : 1) / kBand);
-            const uint64_t wb = std::min<uint64_t>(((uint64_t) A.cmax + kBand - 1) / kBand + CS, nbmax[t]);
-            need[t] = wb * kBand * (uint64_t) A.U;
-            full[t] = nbmax[t] * kBand * (uint64_t) A.U;
+            c->err = "area path: one anchor's level tables exceed the memory budget";
+            return ADK_ERR_NOMEM;
         }
-        uint64_t slots = std::min<uint64_t>(cnt, std::max<uint64_t>(resident / CS, 1));
-        std::vector<uint64_t> slot_size;
-        uint64_t total_need = 0;
-        for (;; --slots)
-        {
-            uint64_t tail_need = 1;
-            for (uint32_t t = (uint32_t) slots; t < cnt; ++t) tail_need = std::max(tail_need, need[t]);
-            slot_size.assign(slots, 0);
-            total_need = 0;
-            for (uint32_t k = 0; k < slots; ++k) { slot_size[k] = (std::max(need[k], tail_need) + 31) & ~(uint64_t) 31; total_need += slot_size[k]; }
-            if (total_need <= budget_entries || slots == 1) break;
-        }
-        if (total_need > budget_entries) { c->err = "area path: one anchor's level tables exceed the memory budget"; return ADK_ERR_NOMEM; }
-        {
-            uint64_t tail_full = 1;
-            for (uint32_t t = (uint32_t) slots; t < cnt; ++t) tail_full = std::max(tail_full, full[t]);
-            uint64_t total_want = 0;
-            std::vector<uint64_t> want(slots);
-            for (uint32_t k = 0; k < slots; ++k) { want[k] = std::max(slot_size[k], (std::max(full[k], tail_full) + 31) & ~(uint64_t) 31); total_want += want[k]; }
-            const double f = total_want <= budget_entries ? 1.0 : (double) (budget_entries - total_need) / (double) (total_want - total_need);
-            for (uint32_t k = 0; k < slots; ++k)
-                slot_size[k] = std::min<uint64_t>(want[k], slot_size[k] + ((uint64_t) ((double) (want[k] - slot_size[k]) * f) & ~(uint64_t) 31));
-        }
-        std::vector<uint64_t> slot_off(slots + 1, 0);
-        uint64_t min_slot = ~0ull;
-        for (uint32_t k = 0; k < slots; ++k) { slot_off[k + 1] = slot_off[k] + slot_size[k]; min_slot = std::min(min_slot, slot_size[k]); }
-        for (uint32_t t = 0; t < cnt; ++t)
-        {   // an anchor lengthens its ring to fill the slot it will run in: its own for the first `slots`, any slot for the others
-            AnchorInfo& A = P.info[t];
-            A.t_off = 0;
-            const uint64_t room = t < slots ? slot_size[t] : min_slot;
-            const uint64_t wb = A.U ? std::min<uint64_t>(nbmax[t], room / ((uint64_t) A.U * kBand)) : 1;
-            A.W = (uint32_t) (std::max<uint64_t>(wb, 1) * kBand);
-        }
+        const uint64_t slots = plan.slots;
+        const std::vector<uint64_t>& slot_off = plan.off;
+        for (uint32_t t = 0; t < cnt; ++t) { P.info[t].W = plan.W[t]; P.info[t].t_off = 0; }
         ADK_TRY(ensure(c, c->scratch5, sizeof(double) * std::max<uint64_t>(slot_off[slots], 32)));
         ADK_TRY(ensure(c, c->area_slot_off, sizeof(uint64_t) * (slots + 1)));
         ADK_CUDA(c, cudaMemcpyAsync(c->area_slot_off.p, slot_off.data(), sizeof(uint64_t) * (slots + 1), cudaMemcpyHostToDevice, c->stream));

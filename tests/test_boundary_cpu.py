@@ -266,3 +266,15 @@ def test_header_is_plain_c(tmp_path):
     subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
                    check=True, capture_output=True)
     assert subprocess.run([str(exe)]).returncode == 0
+
+
+def test_area_slot_plan_invariants(tmp_path):
+    """The table-slot planner of the area path (csrc/adk_area_plan.h, host code without CUDA): on 4 000 random anchor populations
+    every slot holds its own anchor and anything the queue can hand out later, every ring lies inside its slot and is at least the
+    shortest ring the sweep can run with, the total stays inside the budget, and a refusal only happens when one anchor alone
+    does not fit."""
+    exe = tmp_path / "slot_plan_check"
+    subprocess.run(["g++", "-O1", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "area-diameter-algorithm_b200", "csrc"),
+                    os.path.join(ROOT, "tests", "dropin", "slot_plan_check.cpp"), "-o", str(exe)], check=True, capture_output=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
