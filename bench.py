@@ -12,7 +12,11 @@ rank that owns the winning pair, which reconstructs it from its resident records
   e2e   : the same metric through the reference-facing C-ABI call with HOST buffers (pinned), H2D/D2H inside the timed region.
   --impl reference : the UNMODIFIED reference (oracle/_ref/libadkref.so) on the host cores, on a bounded sample of the workload.
 
+  checks: every answer of the sweep is compared with the unmodified reference's frozen output where one exists (tests/golden: all five
+          diameters at sigma = 1.5, D = 2 at sigma = 1.0) and its witness is validated in any case (witness_is_valid).
+
 Usage: python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--sigma S]
+                       [--workload ad_n200|area_n1000|cells_batch] [--no-cpu] [--memory-budget-gb G]
 """
 import argparse
 import json
