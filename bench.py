@@ -98,6 +98,16 @@ def witness_is_valid(x, y, sol, amax, dmax):
     return inside == sol["count"] and far <= dmax * (1 + 1e-12)
 
 
+def oracle_answers(sigma):
+    """Answers of the binary64 ORACLE (not the reference) for solves no frozen reference output exists for, computed with the candidate
+    pairs sharded over processes (tests/golden/make_oracle_sharded.py): {dmax: record}.  Only count, area and diameter pair are held."""
+    path = os.path.join(ROOT, "tests", "golden", "oracle_sharded.json")
+    if not os.path.exists(path):
+        return {}
+    with open(path) as f:
+        return {float(r["dmax"]): r for r in json.load(f)["runs"] if float(r["sigma"]) == float(sigma)}
+
+
 def load_workload(sigma):
     with open(os.path.join(ROOT, "tests", "golden", "bench_n200.json")) as f:
         fx = json.load(f)
@@ -531,6 +541,16 @@ def run_b200_arm(args):
                 if ref is not None:
                     assert got["count"] == ref["count"] and got["hull"] == ref["hull"] and sorted(got["diam"]) == sorted(ref["diam"]), ("multi", d, got, ref)
         line["answers_checked_against_frozen_reference"] = checked
+        # where the reference is out of a CPU's reach, the binary64 oracle (pinned to the reference elsewhere) is the second opinion
+        by_oracle = []
+        for d, got in zip(diams, res["last"]):
+            o = oracle_answers(w["sigma"]).get(float(d))
+            if o is None or d in checked:
+                continue
+            assert got["count"] == o["count"] and sorted(got["diam"]) == sorted(o["diam"]), ("oracle", d, got, o)
+            assert abs(got["area"] - float(o["area"])) <= 1e-9 * float(o["area"]), ("oracle", d, got["area"], o["area"])
+            by_oracle.append(d)
+        line["answers_checked_against_oracle"] = by_oracle
         # the diameters with no frozen answer (sigma != 1.5 beyond the D = 2 sample): the witness itself is checked — simple convex
         # cycle, enclosed-point count = the reported count, area <= A, farthest pair <= D — and the counts must not fall as D grows
         line["witness_valid"] = [d for d, got in zip(diams, res["last"]) if witness_is_valid(w["x"], w["y"], got, w["amax"], d)]

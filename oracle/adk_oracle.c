@@ -880,8 +880,28 @@ static uint32_t reconstruct_AD(const pts_t* P, const tables_t* T, const int32_t*
     return a + b;
 }
 
+/* The candidate pairs of one solve are independent (AntipodalOptimized.cpp:495-527 is a loop over them with a running best), so a
+ * long solve can be cut into shards: shard s of nshards takes every nshards-th pair of the enumeration order.  The shards' bests
+ * merge by (count desc, area asc, enumeration order asc) — the strict comparisons of :512-517 keep the first of equals.  Used by
+ * tests/golden/make_oracle_sharded.py to afford instances one core cannot (the sigma = 0.5 bench set); shard 0 of 1 is the solve. */
+static int ad_solve_impl(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
+                         int reconstruct, uint32_t shard, uint32_t nshards, adko_result* out, uint32_t* hull);
+
 int adko_solve_area_diameter(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
                              int reconstruct, adko_result* out, uint32_t* hull)
+{
+    return ad_solve_impl(x, y, n, kmax, amax, dmax, reconstruct, 0, 1, out, hull);
+}
+
+int adko_solve_area_diameter_shard(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
+                                   uint32_t shard, uint32_t nshards, adko_result* out)
+{
+    if (nshards == 0 || shard >= nshards) return 1;
+    return ad_solve_impl(x, y, n, kmax, amax, dmax, 0, shard, nshards, out, NULL);
+}
+
+static int ad_solve_impl(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
+                         int reconstruct, uint32_t shard, uint32_t nshards, adko_result* out, uint32_t* hull)
 {
     memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
@@ -906,7 +926,7 @@ int adko_solve_area_diameter(const double* x, const double* y, uint32_t n, uint6
         for (uint32_t j = i + 1; j < n; ++j)
         {   /* :495-527 */
             if (!(dist2(&P, (int) i, (int) j) <= dmax2)) continue;
-            ++out->pairs;
+            if ((out->pairs++ % nshards) != shard) continue;
             uint32_t nl, nr;
             lune_lists(&P, (int) i, (int) j, L, &nl, R, &nr);
             uint64_t pk = 0; double pa = INFINITY;

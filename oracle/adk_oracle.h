@@ -40,6 +40,12 @@ int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax,
 int adko_solve_area_diameter(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
                              int reconstruct, adko_result* out, uint32_t* hull);
 
+/* The same solve restricted to every nshards-th candidate pair of the enumeration order (no reconstruction): out->count, area and
+ * diam are this shard's best, cells / states this shard's share, pairs the number of ALL candidate pairs.  Merge the shards by
+ * (count desc, area asc, (diam[0], diam[1]) asc).  tests/golden/make_oracle_sharded.py. */
+int adko_solve_area_diameter_shard(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
+                                   uint32_t shard, uint32_t nshards, adko_result* out);
+
 /* SortPointsClockWiseAroundPoint for every centre (Utils.cpp:295-316): order[i*(n-1)+p]. */
 int adko_cw_order(const double* x, const double* y, uint32_t n, int32_t* order);
 

@@ -71,6 +71,29 @@ class Oracle:
         assert rc == 0, rc
         return self._pack(res, hull)
 
+    def solve_area_diameter_shard(self, x, y, kmax, amax, dmax, shard, nshards):
+        """Every nshards-th candidate pair only (no reconstruction); merge with merge_shards."""
+        res = _Res()
+        hull = (ctypes.c_uint32 * 1)()
+        rc = self.lib.adko_solve_area_diameter_shard(_arr(x), _arr(y), ctypes.c_uint32(len(x)), ctypes.c_uint64(self._k(kmax)),
+                                                     ctypes.c_double(amax), ctypes.c_double(dmax), ctypes.c_uint32(shard),
+                                                     ctypes.c_uint32(nshards), ctypes.byref(res))
+        assert rc == 0, rc
+        return self._pack(res, hull)
+
+    @staticmethod
+    def merge_shards(parts):
+        """Best of the shards: count desc, area asc, pair in enumeration order asc (the strict comparisons of
+        AntipodalOptimized.cpp:512-517 keep the first of equals); cells and states add up."""
+        best = None
+        for p in parts:
+            if p["found"] and (best is None or (-p["count"], p["area"], p["diam"]) < (-best["count"], best["area"], best["diam"])):
+                best = p
+        out = dict(best) if best else {"found": 0, "count": 0, "area": 0.0, "diam": None}
+        out["cells"] = sum(p["cells"] for p in parts); out["states"] = sum(p["states"] for p in parts)
+        out["pairs"] = parts[0]["pairs"] if parts else 0
+        return out
+
     def cw_order(self, x, y):
         n = len(x)
         out = (ctypes.c_int32 * (n * (n - 1)))()

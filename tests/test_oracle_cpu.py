@@ -108,3 +108,21 @@ def test_edge_cases(oracle):
     r = oracle.solve_area_diameter([0, 1, 0], [0, 0, 1], 3, 10.0, 10.0)
     assert r["found"] and r["count"] == 3
     assert oracle.solve_area_diameter([0, 1, 0], [0, 0, 1], 3, 10.0, 1.2)["found"] == 0
+
+
+def test_sharded_oracle_solves_merge_to_the_whole_solve(golden, oracle):
+    """adko_solve_area_diameter_shard (every nshards-th candidate pair) + merge_shards == the whole solve: answer, diameter pair, and
+    the cell / state / pair counters.  This is what lets tests/golden/make_oracle_sharded.py afford the dense bench sets."""
+    from oracle.oraclepy import Oracle
+    done = 0
+    for r in golden["runs"]["bind.ADopt.75"][:12] + golden["runs"]["test.ADopt"][:6]:
+        x, y = xy(golden["points"][r["name"]])
+        whole = oracle.solve_area_diameter(x, y, r["kmax"], r["amax"], r["dmax"], False)
+        for nshards in (1, 3, 7):
+            parts = [oracle.solve_area_diameter_shard(x, y, r["kmax"], r["amax"], r["dmax"], s, nshards) for s in range(nshards)]
+            m = Oracle.merge_shards(parts)
+            assert (m["found"], m["count"], m["diam"]) == (whole["found"], whole["count"], whole["diam"]), (r["name"], nshards)
+            assert not whole["found"] or m["area"] == whole["area"], (r["name"], nshards)
+            assert (m["cells"], m["states"], m["pairs"]) == (whole["cells"], whole["states"], whole["pairs"]), (r["name"], nshards)
+        done += 1
+    assert done >= 12
