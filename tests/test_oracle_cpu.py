@@ -1,10 +1,11 @@
 """The oracle (oracle/adk_oracle.c) pinned against the reference's golden vectors and live reference outputs.
 CPU only; this is what makes the oracle trustworthy as the checker of the CUDA path."""
+import os
 import random
 
 import pytest
 
-from util import xy, assert_same_solution, float32_equal, same_cycle
+from util import ROOT, xy, assert_same_solution, float32_equal, same_cycle
 
 
 def test_oracle_reproduces_reference_known_answers_path_A(golden, oracle):
@@ -126,3 +127,35 @@ def test_sharded_oracle_solves_merge_to_the_whole_solve(golden, oracle):
             assert (m["cells"], m["states"], m["pairs"]) == (whole["cells"], whole["states"], whole["pairs"]), (r["name"], nshards)
         done += 1
     assert done >= 12
+
+
+def test_recorded_gpu_answers_of_the_dense_sweeps_equal_the_sharded_oracle():
+    """The bench lines the B200 printed for the dense sets SURVEY 8d names (profiles/r2_bench_sigma1.0_n1.json, _sigma0.5_) against
+    the binary64 oracle's answers for the same solves (tests/golden/oracle_sharded.json, computed in the build container with the
+    candidate pairs sharded over processes): count, diameter pair, area to 1e-9; and, once all five diameters of a sweep are held,
+    the sweep's cell and state totals.  A check of RECORDED device output — the live one is the -m gpu test of the same name."""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "oracle_sharded.json")) as f:
+        runs = json.load(f)["runs"]
+    by_sigma = {}
+    for r in runs:
+        by_sigma.setdefault(float(r["sigma"]), {})[float(r["dmax"])] = r
+    compared = 0
+    for sigma, held in by_sigma.items():
+        path = os.path.join(ROOT, "profiles", f"r2_bench_sigma{sigma}_n1.json")
+        if not os.path.exists(path):
+            continue
+        with open(path) as f:
+            line = [json.loads(l) for l in f if l.lstrip().startswith("{")][-1]
+        assert line["config"]["sigma"] == sigma and line["config"]["amax"] == next(iter(held.values()))["amax"]
+        for a in line["answers"]:
+            o = held.get(float(a["D"]))
+            if o is None:
+                continue
+            assert a["count"] == o["count"] and sorted(a["diam"]) == sorted(o["diam"]), (sigma, a, o)
+            assert abs(a["area"] - o["area"]) <= 1e-9 * o["area"], (sigma, a["area"], o["area"])
+            compared += 1
+        if all(float(d) in held for d in line["config"]["diameters"]):
+            assert sum(held[float(d)]["cells"] for d in line["config"]["diameters"]) == line["config"]["cells_per_step"], sigma
+            assert sum(held[float(d)]["states"] for d in line["config"]["diameters"]) == line["config"]["states_per_step"], sigma
+    assert compared >= 1

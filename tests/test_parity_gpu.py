@@ -9,7 +9,7 @@ import sys
 
 import pytest
 
-from util import (ROOT, xy, assert_same_solution, float32_equal, same_cycle, check_witness, write_reference_layout,
+from util import (ROOT, REL_TOL, xy, assert_same_solution, float32_equal, same_cycle, check_witness, write_reference_layout,
                   write_experiments_layout, polygon_area)
 
 pytestmark = pytest.mark.gpu
@@ -410,6 +410,30 @@ def test_headline_sweep_equals_the_frozen_reference(golden, solver, d):
     check_witness(x, y, g, fx["amax"], float(d))
     if want.get("entries_required"):
         assert g["entries_required"] == want["entries_required"], (d, g["entries_required"], want["entries_required"])
+
+
+def _oracle_sharded_runs():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "oracle_sharded.json")) as f:
+        return json.load(f)["runs"]
+
+
+@pytest.mark.parametrize("tag", [r["tag"] for r in _oracle_sharded_runs()])
+def test_dense_sweeps_equal_the_sharded_oracle(golden, solver, tag):
+    """The dense sets SURVEY 8d names (Gaussian n = 200, sigma = 1.0 and 0.5, `bench.py --sigma`): the unmodified reference cannot
+    afford them on a CPU, so the binary64 oracle — pinned to the reference in tests/test_oracle_cpu.py — solved them in the build
+    container with the candidate pairs sharded over processes (tests/golden/make_oracle_sharded.py).  Count and diameter pair exact,
+    area to 1e-9, the in-kernel cell and state counters equal to the oracle's, and the witness valid."""
+    o = next(r for r in _oracle_sharded_runs() if r["tag"] == tag)
+    fx = golden["bench_n200"]
+    pts = fx["sets"][str(float(o["sigma"]))]["points"]
+    x = [float(p[0]) for p in pts]
+    y = [float(p[1]) for p in pts]
+    g = solver.solve_area_diameter(x, y, None, o["amax"], float(o["dmax"]), True, counters=True)
+    assert g["found"] == o["found"] and g["count"] == o["count"] and sorted(g["diam"]) == sorted(o["diam"]), (tag, g["count"], g["diam"])
+    assert abs(g["area"] - o["area"]) <= REL_TOL * o["area"], (tag, g["area"], o["area"])
+    assert g["cells_executed"] == o["cells"] and g["states"] == o["states"] and g["pairs"] == o["pairs"], (tag, g["cells_executed"], g["states"], g["pairs"])
+    check_witness(x, y, g, o["amax"], float(o["dmax"]))
 
 
 @pytest.mark.parametrize("slide", [1, 2, 3, 4, 5])
