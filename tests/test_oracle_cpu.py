@@ -159,3 +159,25 @@ def test_recorded_gpu_answers_of_the_dense_sweeps_equal_the_sharded_oracle():
             assert sum(held[float(d)]["cells"] for d in line["config"]["diameters"]) == line["config"]["cells_per_step"], sigma
             assert sum(held[float(d)]["states"] for d in line["config"]["diameters"]) == line["config"]["states_per_step"], sigma
     assert compared >= 1
+
+
+def test_reference_optimisation_flag_changes_counters_only(golden):
+    """aShouldEnableOptimizations (Eppstein.cpp:186-189, AntipodalOptimized.cpp:505-508) prunes anchors / candidate pairs that cannot
+    beat the best count so far: with the flag on the unmodified reference returns the same answer and never larger BenchmarkInfo
+    counters.  This is why the GPU library may ignore the flag and why the frozen runs, generated with the
+    flag off as the reference's bench does (src/CMakeLists.txt:88), pin the counters."""
+    from oracle.refpy import RefLib, ref_available
+    if not ref_available("x87"):
+        pytest.skip("oracle/_ref is built only where /root/reference exists")
+    ref = RefLib("x87")
+    smaller = 0
+    for algo, tag in ((0, "test.A"), (2, "test.ADopt"), (2, "bind.ADopt.75")):
+        for r in golden["runs"][tag][:10]:
+            x, y = xy(golden["points"][r["name"]])
+            off = ref.solve(algo, x, y, r["kmax"], r["amax"], r["dmax"], True, False)
+            on = ref.solve(algo, x, y, r["kmax"], r["amax"], r["dmax"], True, True)
+            assert (on["found"], on["count"], on["area"], on["hull"], on["diam"]) == (off["found"], off["count"], off["area"], off["hull"], off["diam"]), r["name"]
+            assert (off["entries_alloc"], off["entries_required"]) == (r["entries_alloc"], r["entries_required"]), r["name"]
+            assert on["entries_required"] <= off["entries_required"] and on["entries_alloc"] <= off["entries_alloc"], r["name"]
+            smaller += on["entries_required"] < off["entries_required"]
+    assert smaller >= 1
