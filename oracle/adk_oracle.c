@@ -452,8 +452,28 @@ static double now_ms(void)
     return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
 }
 
+/* The anchors of one solve are independent (Eppstein.cpp:177-238 is a loop over them with a running best that only a strictly
+ * better (count, area) replaces), so a solve can be dealt over processes: shard s of nshards takes every nshards-th anchor of the
+ * bottom-up order, keeps its own best and the table of its own best anchor, and reports the position of that anchor in the order so
+ * that the merge can keep the first of equals as the loop does.  tests/golden/make_oracle_sharded.py --area. */
+static int area_solve_impl(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                           int reconstruct, adko_result* out, uint32_t* hull, uint32_t shard, uint32_t nshards, uint32_t* best_pos);
+
 int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
                     int reconstruct, adko_result* out, uint32_t* hull)
+{
+    return area_solve_impl(x, y, n, kmax, amax, reconstruct, out, hull, 0, 1, NULL);
+}
+
+int adko_solve_area_shard(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, int reconstruct,
+                          uint32_t shard, uint32_t nshards, adko_result* out, uint32_t* hull, uint32_t* best_anchor_pos)
+{
+    if (nshards == 0 || shard >= nshards) return 1;
+    return area_solve_impl(x, y, n, kmax, amax, reconstruct, out, hull, shard, nshards, best_anchor_pos);
+}
+
+static int area_solve_impl(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
+                           int reconstruct, adko_result* out, uint32_t* hull, uint32_t shard, uint32_t nshards, uint32_t* best_pos)
 {
     memset(out, 0, sizeof(*out));
     out->entries_alloc = -1; out->entries_required = -1;
@@ -491,8 +511,10 @@ int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax,
     double best_area = INFINITY;
     int best_i = -1, best_j = -1;
 
+    uint32_t best_a = 0;
     for (uint32_t a = 0; a < n; ++a)
     {
+        if (a % nshards != shard) continue;       /* another shard's anchor */
         const int i = byy[a];
         if (flip) { buf ^= 1; flip = 0; }         /* :180-184 */
         for (size_t t = 0; t < plane; ++t) TAB(2, buf, 0, t) = 0.0;   /* :191 */
@@ -530,7 +552,7 @@ int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax,
                             if (!have || m > best_m || (m == best_m && run < best_area))   /* :219 */
                             {
                                 flip |= !have || best_i != i;
-                                have = 1; best_m = m; best_area = run; best_i = i; best_j = j;
+                                have = 1; best_m = m; best_area = run; best_i = i; best_j = j; best_a = a;
                             }
                         }
                     }
@@ -541,6 +563,7 @@ int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax,
         }
     }
 
+    if (best_pos) *best_pos = best_a;
     if (have)
     {
         out->found = 1;

@@ -36,6 +36,12 @@ typedef struct adko_result
 int adko_solve_area(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax,
                     int reconstruct, adko_result* out, uint32_t* hull);
 
+/* The same solve restricted to every nshards-th anchor of the bottom-up anchor order (Eppstein.cpp:177): out is this shard's best
+ * (with its hull when reconstruct is set), cells / entries_required this shard's share, *best_anchor_pos the position of the best's
+ * anchor in that order.  Merge by (count desc, area asc, best_anchor_pos asc).  tests/golden/make_oracle_sharded.py --area. */
+int adko_solve_area_shard(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, int reconstruct,
+                          uint32_t shard, uint32_t nshards, adko_result* out, uint32_t* hull, uint32_t* best_anchor_pos);
+
 /* MT::AntipodalOptimizedAlgorithmWithBenchmarkInfo (AntipodalOptimized.cpp:452-545). */
 int adko_solve_area_diameter(const double* x, const double* y, uint32_t n, uint64_t kmax, double amax, double dmax,
                              int reconstruct, adko_result* out, uint32_t* hull);

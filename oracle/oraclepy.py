@@ -81,6 +81,33 @@ class Oracle:
         assert rc == 0, rc
         return self._pack(res, hull)
 
+    def solve_area_shard(self, x, y, kmax, amax, reconstruct, shard, nshards):
+        """Every nshards-th anchor of the bottom-up order only; merge with merge_area_shards."""
+        n = len(x)
+        res = _Res()
+        hull = (ctypes.c_uint32 * max(n + 2, 1))()
+        pos = ctypes.c_uint32(0)
+        rc = self.lib.adko_solve_area_shard(_arr(x), _arr(y), ctypes.c_uint32(n), ctypes.c_uint64(self._k(kmax)), ctypes.c_double(amax),
+                                            ctypes.c_int(int(reconstruct)), ctypes.c_uint32(shard), ctypes.c_uint32(nshards),
+                                            ctypes.byref(res), hull, ctypes.byref(pos))
+        assert rc == 0, rc
+        out = self._pack(res, hull)
+        out["anchor_pos"] = int(pos.value)
+        return out
+
+    @staticmethod
+    def merge_area_shards(parts):
+        """Best of the shards: count desc, area asc, anchor position asc (Eppstein.cpp:219 replaces the running best only by a strictly
+        better one, so the first anchor of equals stays); cells and entries_required add up."""
+        best = None
+        for p in parts:
+            if p["found"] and (best is None or (-p["count"], p["area"], p["anchor_pos"]) < (-best["count"], best["area"], best["anchor_pos"])):
+                best = p
+        out = dict(best) if best else {"found": 0, "count": 0, "area": 0.0, "hull": [], "diam": None}
+        out["cells"] = sum(p["cells"] for p in parts)
+        out["entries_required"] = sum(p["entries_required"] for p in parts)
+        return out
+
     @staticmethod
     def merge_shards(parts):
         """Best of the shards: count desc, area asc, pair in enumeration order asc (the strict comparisons of

@@ -181,3 +181,24 @@ def test_reference_optimisation_flag_changes_counters_only(golden):
             assert on["entries_required"] <= off["entries_required"] and on["entries_alloc"] <= off["entries_alloc"], r["name"]
             smaller += on["entries_required"] < off["entries_required"]
     assert smaller >= 1
+
+
+def test_sharded_oracle_area_solves_merge_to_the_whole_solve(golden, oracle):
+    """adko_solve_area_shard (every nshards-th anchor of the bottom-up order) + merge_area_shards == the whole solve: answer, hull
+    cycle, diameter pair, and the cell / prefix-minimum counters.  This is what lets make_oracle_sharded.py --area afford config 3's
+    n = 1000 set."""
+    from oracle.oraclepy import Oracle
+    done = 0
+    for r in golden["runs"]["test.A"][:40:2] + golden["runs"]["bench.A"][:4]:
+        x, y = xy(golden["points"][r["name"]])
+        if len(x) > 120:
+            continue
+        whole = oracle.solve_area(x, y, r["kmax"], r["amax"], True)
+        for nshards in (1, 3, 7):
+            parts = [oracle.solve_area_shard(x, y, r["kmax"], r["amax"], True, s, nshards) for s in range(nshards)]
+            m = Oracle.merge_area_shards(parts)
+            assert (m["found"], m["count"], m["hull"], m["diam"]) == (whole["found"], whole["count"], whole["hull"], whole["diam"]), (r["name"], nshards)
+            assert not whole["found"] or m["area"] == whole["area"], (r["name"], nshards)
+            assert (m["cells"], m["entries_required"]) == (whole["cells"], whole["entries_required"]), (r["name"], nshards)
+        done += 1
+    assert done >= 12
