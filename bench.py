@@ -743,6 +743,18 @@ def run_aux_workload(args):
             line["solve_ms_per_instance"] = res["dev_ms"] / args.steps
             line["nominal_cells_per_sec"] = nominal * args.steps / secs
             line["config"]["nominal_cells_per_step"] = nominal
+            # the binary64 oracle's answer for this very solve (anchors sharded over processes in the build container,
+            # tests/golden/make_oracle_sharded.py --area): count and hull cycle exact, area to 1e-9
+            opath = os.path.join(ROOT, "tests", "golden", "oracle_sharded_area.json")
+            if os.path.exists(opath):
+                with open(opath) as f:
+                    o = next((r_ for r_ in json.load(f)["runs"] if r_["tag"].startswith("area.n1000.K")), None)
+                if o is not None:
+                    hg, ho = list(last["hull"]), list(o["hull"])
+                    rot = hg.index(ho[0]) if ho and ho[0] in hg else -1
+                    assert last["count"] == o["count"] and rot >= 0 and hg[rot:] + hg[:rot] == ho, ("oracle", last["count"], hg, o["count"], ho)
+                    assert abs(last["area"] - float(o["area"])) <= 1e-9 * float(o["area"]), ("oracle", last["area"], o["area"])
+                    line["answer_checked_against_oracle"] = o["tag"]
             line["config"]["nominal_note"] = ("(K-2) n (n-1) (n-2) / 3 with K = n: what the reference's loops would execute (Eppstein.cpp:192-235); the kernels "
                                               "stop at the deepest reachable level, so `value` counts the executed updates only")
         else:

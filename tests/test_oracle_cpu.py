@@ -202,3 +202,19 @@ def test_sharded_oracle_area_solves_merge_to_the_whole_solve(golden, oracle):
             assert (m["cells"], m["entries_required"]) == (whole["cells"], whole["entries_required"]), (r["name"], nshards)
         done += 1
     assert done >= 12
+
+
+def test_recorded_gpu_answer_of_config3_equals_the_sharded_oracle():
+    """The answer the B200 printed for config 3 at full size (profiles/r2_bench_area_n1000_n1.json: area path, Gaussian n = 1000, K = inf)
+    against the binary64 oracle's answer for the same solve with the anchors sharded over processes
+    (tests/golden/oracle_sharded_area.json): count, hull cycle, area to 1e-9.  A check of RECORDED device output — the live one is the
+    -m gpu test test_config3_n1000_equals_the_sharded_oracle."""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "oracle_sharded_area.json")) as f:
+        o = next(r for r in json.load(f)["runs"] if r["tag"].startswith("area.n1000.K"))
+    with open(os.path.join(ROOT, "profiles", "r2_bench_area_n1000_n1.json")) as f:
+        line = [json.loads(l) for l in f if l.lstrip().startswith("{")][-1]
+    a = line["answers"][0]
+    assert o["count"] < o["kmax"] - 1                      # the cap of the oracle run did not bind
+    assert a["count"] == o["count"] and same_cycle(a["hull"], o["hull"]), (a, o["count"], o["hull"])
+    assert abs(a["area"] - o["area"]) <= 1e-9 * o["area"], (a["area"], o["area"])

@@ -464,6 +464,25 @@ def test_config3_n1000_K16_equals_the_frozen_reference(golden, solver):
     assert_same_solution(g, want, "area n1000 K16")
 
 
+def test_config3_n1000_equals_the_sharded_oracle(solver):
+    """BASELINE config 3 at full size (`bench.py --workload area_n1000`: Gaussian n = 1000, sigma = 2, seed 1000, A = 4, K = inf): the
+    binary64 oracle's answer, computed in the build container with the anchors sharded over processes
+    (tests/golden/make_oracle_sharded.py --area, tests/golden/oracle_sharded_area.json; K capped at 180 there because the
+    restatement's table holds K + 1 levels — the answer has 177 points and levels 178..180 are empty, so the cap does not bind).
+    Count, hull cycle and diameter pair exact, area to 1e-9, for the uncapped solve and for the solve with the same cap."""
+    import json
+    path = os.path.join(ROOT, "tests", "golden", "oracle_sharded_area.json")
+    with open(path) as f:
+        o = next(r for r in json.load(f)["runs"] if r["tag"].startswith("area.n1000.K"))
+    assert o["count"] < o["kmax"] - 1
+    pts = _synth().gaussian_points(o["n"], 2.0, 1000)
+    x, y = xy(pts)
+    for k in (None, o["kmax"]):
+        g = solver.solve_area(x, y, k, o["amax"], True)
+        assert_same_solution(g, o, ("area n1000", k))
+        check_witness(x, y, g, o["amax"])
+
+
 # ------------------------------------------------------------------------------------------------ several GPUs behind the C ABI
 def _device_count():
     import torch
