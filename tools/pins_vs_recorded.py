@@ -50,6 +50,21 @@ def main():
         ok = a["count"] == o["count"] and a["hull"] == o["hull"] and abs(a["area"] - o["area"]) <= 1e-9 * o["area"]
         rows.append(("A n=1000 sigma=2 K=inf (config 3)", "r2_bench_area_n1000_n1.json", a["count"], repr(a["area"]), f"hull of {len(a['hull'])}",
                      f"binary64 oracle, anchors sharded (K={o['kmax']})", o["count"], repr(o["area"]), "EQUAL (hull cycle too)" if ok else "DIFFERENT"))
+    cpath = os.path.join(ROOT, "profiles", "r2_bench_cells_batch_n1.json")
+    if os.path.exists(cpath):
+        ro = json.load(open(os.path.join(G, "ref_outputs.json")))
+        pins = {}
+        for r in ro["runs"] + ro.get("survey_recorded", []):
+            if r.get("algo") == 2 and str(r["name"]).startswith("real/") and float(r["dmax"]) == 4.0 and float(r["amax"]) == 4.0:
+                pins[r["name"]] = r
+        for i in range(1, 6):
+            if f"real.{i}.D4" in heavy:
+                pins[f"real/{i}/0"] = heavy[f"real.{i}.D4"]
+        for i, a in enumerate(last_line(cpath)["answers"]):
+            o = pins.get(f"real/{i}/0")
+            ok = o is not None and a["count"] == o["count"] and sorted(a["diam"]) == sorted(o["diam"]) and abs(a["area"] - o["area"]) <= 1e-9 * o["area"]
+            rows.append((f"AD cell sample real/{i} n={a['n']} A=4 D=4 (config 5)", "r2_bench_cells_batch_n1.json", a["count"], repr(a["area"]), tuple(a["diam"]),
+                         "x87 reference" if o else "- none -", o["count"] if o else "", repr(o["area"]) if o else "", "EQUAL" if ok else ("-" if o is None else "DIFFERENT")))
     print("solve | bench line under profiles/ | B200: count | area | diameter pair | pinned by | count | area | verdict")
     for r in rows:
         print(" | ".join(str(v) for v in r))
