@@ -4,7 +4,7 @@
  * largest-convex-subset solvers.  All citations are file:line relative to /root/reference/src/common/.
  * Differences from the reference that do not change results:
  *   - double instead of long double (the reference author's platform has long double == double; the
- *     x87 build in oracle/_ref is the arbiter and tests/test_oracle.py compares the two);
+ *     x87 build in oracle/_ref is the arbiter and tests/test_oracle_cpu.py compares the two);
  *   - the slope list of (anchor, centre) is computed once instead of once per level m (it does not depend on m);
  *   - per-layer open-addressing tables instead of std::unordered_map (iteration order only matters on exact ties);
  *   - stable merge sorts instead of std::sort (identical for strict orders).

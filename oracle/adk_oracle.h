@@ -4,7 +4,7 @@
  * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may call it.
  * Each function in adk_oracle.c cites the reference lines (relative to /root/reference) it follows.
  * Pinned against: the reference's 100 golden fixtures (data/samples/tests, via tests/golden/) and the
- * live outputs of the unmodified reference build oracle/_ref/libadkref.so (tests/test_oracle.py).
+ * live outputs of the unmodified reference build oracle/_ref/libadkref.so (tests/test_oracle_cpu.py).
  */
 #ifndef ADK_ORACLE_H
 #define ADK_ORACLE_H
