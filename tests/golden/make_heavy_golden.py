@@ -5,6 +5,7 @@
   bench.sigma1.5.D{3,4,5,6} : the headline sweep beyond the D = 2 sample (tests/golden/bench_n200.json holds D = 2)
   real.{1..5}.D4            : the cell samples at the real call shape (quality_of_results_comparison.py:194-197)
   bench.sigma{1.0,0.5}.D2   : the D = 2 solve of the denser sets of the bench fixture
+  bench.sigma1.0.D3         : the solve at which the sigma = 1.0 sweep reaches its final answer
   area.n1000.K16            : BASELINE config 3's point set (synth.gaussian_points(1000, 2.0, 1000)), area path, K = 16
 
 Each job writes tests/golden/heavy/<tag>.json when it ends; `--merge` folds whatever is there into
@@ -52,6 +53,11 @@ def job_list():
         pts = fx["sets"][sigma]["points"]
         jobs.append({"tag": f"bench.sigma{sigma}.D2", "name": f"bench_n200/{sigma}", "algo": 2, "kmax": KINF, "amax": fx["amax"],
                      "dmax": 2.0, "x": [float(q[0]) for q in pts], "y": [float(q[1]) for q in pts]})
+    # sigma = 1.0, D = 3: the first diameter at which the denser sweep reaches its final answer (110 points); ~3.4e9 hash entries,
+    # a couple of hours of one core
+    pts = fx["sets"]["1.0"]["points"]
+    jobs.append({"tag": "bench.sigma1.0.D3", "name": "bench_n200/1.0", "algo": 2, "kmax": KINF, "amax": fx["amax"],
+                 "dmax": 3.0, "x": [float(q[0]) for q in pts], "y": [float(q[1]) for q in pts]})
     return jobs
 
 
