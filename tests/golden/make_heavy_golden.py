@@ -6,6 +6,7 @@
   real.{1..5}.D4            : the cell samples at the real call shape (quality_of_results_comparison.py:194-197)
   bench.sigma{1.0,0.5}.D2   : the D = 2 solve of the denser sets of the bench fixture
   bench.sigma1.0.D3         : the solve at which the sigma = 1.0 sweep reaches its final answer
+  bench.sigma{2.0,3.0}.D{4,5,6} : the wider sets of the fixture beyond their D = 2, 3 samples
   area.n1000.K16            : BASELINE config 3's point set (synth.gaussian_points(1000, 2.0, 1000)), area path, K = 16
 
 Each job writes tests/golden/heavy/<tag>.json when it ends; `--merge` folds whatever is there into
@@ -58,6 +59,12 @@ def job_list():
     pts = fx["sets"]["1.0"]["points"]
     jobs.append({"tag": "bench.sigma1.0.D3", "name": "bench_n200/1.0", "algo": 2, "kmax": KINF, "amax": fx["amax"],
                  "dmax": 3.0, "x": [float(q[0]) for q in pts], "y": [float(q[1]) for q in pts]})
+    # the wider sets of the bench fixture (sigma = 2.0, 3.0) beyond the D = 2, 3 samples bench_n200.json holds: minutes each
+    for sigma in ("2.0", "3.0"):
+        pts = fx["sets"][sigma]["points"]
+        for d in (4.0, 5.0, 6.0):
+            jobs.append({"tag": f"bench.sigma{sigma}.D{int(d)}", "name": f"bench_n200/{sigma}", "algo": 2, "kmax": KINF, "amax": fx["amax"],
+                         "dmax": d, "x": [float(q[0]) for q in pts], "y": [float(q[1]) for q in pts]})
     return jobs
 
 

@@ -218,3 +218,27 @@ def test_recorded_gpu_answer_of_config3_equals_the_sharded_oracle():
     assert o["count"] < o["kmax"] - 1                      # the cap of the oracle run did not bind
     assert a["count"] == o["count"] and same_cycle(a["hull"], o["hull"]), (a, o["count"], o["hull"])
     assert abs(a["area"] - o["area"]) <= 1e-9 * o["area"], (a["area"], o["area"])
+
+
+def test_oracle_reproduces_the_frozen_reference_on_the_wider_bench_sweeps(golden, oracle):
+    """The wider sets of the bench fixture (Gaussian n = 200, sigma = 3.0 and 2.0): the oracle against the unmodified x87 reference on
+    every frozen solve of the sigma = 3.0 diameter sweep and on D = 2, 3 of sigma = 2.0 (D = 4, 5, 6 of sigma = 2.0 take minutes of one
+    core and were compared once when they were frozen: equal, entries included) — answer, hull cycle, diameter pair and hash entries."""
+    fx = golden["bench_n200"]
+    done = 0
+    for sigma, dmaxs in (("3.0", (2, 3, 4, 5, 6)), ("2.0", (2, 3))):
+        pts = fx["sets"][sigma]["points"]
+        x = [float(p[0]) for p in pts]
+        y = [float(p[1]) for p in pts]
+        for d in dmaxs:
+            smp = next((s_ for s_ in fx["sets"][sigma]["sample"] if float(s_["dmax"]) == d), None)
+            if smp is not None:
+                want = {"found": 1, "count": smp["count"], "area": float(smp["area"]), "hull": smp["hull"], "diam": smp["diam"],
+                        "entries_required": smp["ref_entries"]}
+            else:
+                want = golden["heavy"][f"bench.sigma{sigma}.D{d}"]
+            r = oracle.solve_area_diameter(x, y, None, fx["amax"], float(d), True)
+            assert_same_solution(r, want, (sigma, d))
+            assert r["entries_required"] == want["entries_required"], (sigma, d)
+            done += 1
+    assert done == 7

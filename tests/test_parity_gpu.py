@@ -412,6 +412,41 @@ def test_headline_sweep_equals_the_frozen_reference(golden, solver, d):
         assert g["entries_required"] == want["entries_required"], (d, g["entries_required"], want["entries_required"])
 
 
+def _wider_sweep_cases():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "bench_n200.json")) as f:
+        fx = json.load(f)
+    with open(os.path.join(ROOT, "tests", "golden", "heavy_outputs.json")) as f:
+        tags = {r["tag"] for r in json.load(f)["runs"]}
+    cases = []
+    for sigma in ("2.0", "3.0"):
+        held = {float(smp["dmax"]) for smp in fx["sets"][sigma]["sample"]} | {float(d) for d in (4, 5, 6) if f"bench.sigma{sigma}.D{d}" in tags}
+        cases += [(sigma, d) for d in sorted(held)]
+    return cases
+
+
+@pytest.mark.parametrize("sigma,d", _wider_sweep_cases())
+def test_wider_sweeps_equal_the_frozen_reference(golden, solver, sigma, d):
+    """The wider sets of the bench fixture (Gaussian n = 200, sigma = 2.0 and 3.0, A = 4; `bench.py --sigma 2.0`): every solve of
+    the diameter sweep the unmodified x87 reference has been frozen on (D = 2, 3 in bench_n200.json, D = 4, 5, 6 in
+    heavy_outputs.json): count, hull cycle, diameter pair exact, area to 1e-9, hash entries equal."""
+    fx = golden["bench_n200"]
+    pts = fx["sets"][sigma]["points"]
+    x = [float(p[0]) for p in pts]
+    y = [float(p[1]) for p in pts]
+    smp = next((s_ for s_ in fx["sets"][sigma]["sample"] if float(s_["dmax"]) == d), None)
+    if smp is not None:
+        want = {"found": 1, "count": smp["count"], "area": float(smp["area"]), "hull": smp["hull"], "diam": smp["diam"],
+                "entries_required": smp.get("ref_entries")}
+    else:
+        want = golden["heavy"][f"bench.sigma{sigma}.D{int(d)}"]
+    g = solver.solve_area_diameter(x, y, None, fx["amax"], d, True, counters=True)
+    assert_same_solution(g, want, ("sigma", sigma, d))
+    check_witness(x, y, g, fx["amax"], d)
+    if want.get("entries_required"):
+        assert g["entries_required"] == want["entries_required"], (sigma, d, g["entries_required"], want["entries_required"])
+
+
 def _oracle_sharded_runs():
     import json
     with open(os.path.join(ROOT, "tests", "golden", "oracle_sharded.json")) as f:
